@@ -1,0 +1,198 @@
+/*
+ * pdac_b200.h — C ABI of libpdac_b200.so: the B200 (sm_100a) kernels behind the drop-in nn.Module replacements
+ * for moksu27/PDAC_pathological_image_segmentation's hot path.
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer owned by the caller (PyTorch caching allocator); the library allocates
+ *     nothing. Activations are NHWC bf16 "views" (PdacView: channel stride 1, element strides for W/H/N), so
+ *     channel slices, parity sub-lattices (stride-2 convs, ConvTranspose k2s2) and concat halves are all views.
+ *   - Every entry is stream-ordered on `stream` (a cudaStream_t passed as void*), never synchronises (except
+ *     pdac_check_device_flag), and returns 0 or a negative PDAC_E_* code; pdac_last_error() gives the
+ *     thread-local message.
+ *   - No CPU fallback anywhere: host pointers or a missing GPU are errors.
+ *
+ * Reference interface each group replaces (paths relative to the reference repo; torchvision paths relative to
+ * site-packages/torchvision/models):
+ *   conv2d / conv-transpose       -> nn.Conv2d / nn.ConvTranspose2d built at models/resunet.py:12-21, run at :25-48;
+ *                                    torchvision resnet.py:59-106 (BasicBlock), :197-204 (stem); smp decoders
+ *                                    instantiated at train_worker.py:152-182
+ *   batchnorm / relu / residual   -> torchvision resnet.py:82-101 (bn1/bn2/relu/+=identity), resnet.py:199
+ *   maxpool                       -> torchvision resnet.py:200 (MaxPool2d 3x3 s2 p1), models/resunet.py:28
+ *   resize                        -> F.interpolate at models/resunet.py:51-56 (bilinear, align_corners=False);
+ *                                    smp UpsamplingBilinear2d (align_corners=True) and nearest x2
+ *   dice / mask                   -> util.py:10-19 (DiceLoss), util.py:22-26 (dice_score),
+ *                                    train_worker.py:24,72 and test.py:144 (sigmoid >= 0.5 mask)
+ *   adam                          -> torch.optim.Adam(model.parameters(), lr) at train_worker.py:184, step at :80
+ *   stitch                        -> visualize/predict_overlay.ipynb (missing blob) per configs/visualize_config.yaml:3-15
+ *   prep                          -> dataset.py:24-30 + train_main.py:70-75 (Normalize / flips / rot90)
+ */
+#ifndef PDAC_B200_H
+#define PDAC_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDAC_OK 0
+#define PDAC_E_INVALID (-1)  /* bad argument / unsupported shape */
+#define PDAC_E_CUDA (-2)     /* a CUDA runtime/driver call failed */
+#define PDAC_E_TIMEOUT (-3)  /* a device-side pipeline barrier timed out (see pdac_check_device_flag) */
+#define PDAC_E_NODEVICE (-4) /* no sm_100 device / driver entry point missing */
+
+/* NHWC view: element (n,h,w,c) lives at ptr + n*sN + h*sH + w*sW + c (in elements of the view's dtype). */
+typedef struct PdacView {
+  void* ptr;
+  int32_t N, H, W, C;
+  int64_t sN, sH, sW;
+} PdacView;
+
+/* 2-D convolution geometry (square kernel stride/dilation, as every conv on the path has). */
+typedef struct PdacConv {
+  int32_t R, S;      /* kernel height, width */
+  int32_t stride;    /* 1 or 2 */
+  int32_t pad;       /* symmetric zero padding */
+  int32_t dil;       /* dilation */
+  int32_t relu;      /* fuse max(x,0) into the epilogue */
+  int32_t wrows;     /* rows per tap in the packed weight matrix (>= rows used; lets a tap block be padded) */
+  int32_t reserved;
+} PdacConv;
+
+int pdac_version(void);
+const char* pdac_last_error(void);
+/* Reads (and clears) the device-side pipeline error flag; synchronises `stream`. Debug/tests only. */
+int pdac_check_device_flag(void* stream);
+
+/* ---- tensor-core implicit-GEMM convolutions (conv_tc.cu) ----------------------------------------------------
+ * Generalised "tap convolution": out[n,h,w,:] = act( sum_t W_t * cat_s(views[tap.src+s])[n, h+dh_t, w+dw_t, :]
+ *                                                    + bias + addend ).
+ * Every nn.Conv2d (any stride/dilation), its data gradient, ConvTranspose2d k2s2 and its data gradient are
+ * instances (strided cases read/write parity sub-lattice views).
+ * Packed weights: bf16 matrix [n_taps * wrows][Ktot], K contiguous (Ktot = sum of the n_cat source channels). */
+#define PDAC_MAX_TAPS 16
+typedef struct PdacTap {
+  int32_t src;    /* index of the tap's first source view */
+  int32_t dh, dw; /* pixel offset applied in that view's own lattice */
+} PdacTap;
+typedef struct PdacTapConv {
+  int32_t n_taps;
+  int32_t n_cat; /* 1 or 2 views concatenated along C per tap (torch.cat order) */
+  int32_t wrows; /* rows per tap in the packed weight matrix */
+  int32_t relu;
+  PdacTap taps[PDAC_MAX_TAPS];
+} PdacTapConv;
+/* stats: optional fp32 [2][out->C]: per-channel sum and sum of squares of the stored (bf16-rounded) outputs are
+ * atomically accumulated (BatchNorm batch statistics); caller zeroes it. */
+int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
+                     const float* bias, const PdacView* addend, const PdacView* out, float* stats, void* stream);
+/* dw[t*tap_stride + a*a_stride + b*b_stride] += sum_pixels cat(views)[p + off_t, a] * dy[p, b]  (fp32 atomics;
+ * caller zeroes dw). a runs over the concatenated source channels, b over dy->C. */
+int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy, float* dw,
+                       int64_t tap_stride, int64_t a_stride, int64_t b_stride, void* stream);
+
+/* nn.Conv2d forward: out = [relu](conv(cat(src[0..n_src-1]), w) + bias + addend). w_packed: [R*S*wrows][Ctot] with
+ * row (r*S+s)*wrows + cout. */
+int pdac_conv2d_fwd(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed, const float* bias,
+                    const PdacView* addend, const PdacView* out, float* stats, void* stream);
+/* dx = conv_transpose(dy, w) (+ addend): the data gradient of the conv described by cv. w_packed_t:
+ * [R*S*wrows][Cout] with row (r*S+s)*wrows + cin (taps un-flipped: the library derives the offsets). For
+ * stride 2 the four output parity classes are separate launches; classes no tap reaches get addend or zero. */
+int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const void* w_packed_t, const PdacView* addend,
+                      const PdacView* dx, void* stream);
+/* dw[(r*S+s)][cout][cin] += sum_pixels dy[p,cout] * cat(src)[p*stride + off, cin]; fp32 [R*S][Cout][Ctot]. */
+int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,
+                      void* stream);
+/* nn.ConvTranspose2d(k=2, s=2): out[2i+a,2j+b,:] = W[a,b] x[i,j,:] + bias. w_packed: [4*wrows][Cin], row
+ * (a*2+b)*wrows + cout; w_packed_t: [4*wrows][Cout], row (a*2+b)*wrows + cin; dw: fp32 [4][Cout][Cin]. */
+int pdac_convt2x2_fwd(const PdacView* x, const void* w_packed, int wrows, const float* bias, int relu,
+                      const PdacView* out, void* stream);
+int pdac_convt2x2_dgrad(const PdacView* dy, const void* w_packed_t, int wrows, const PdacView* dx, void* stream);
+int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, void* stream);
+
+/* ---- layout / packing (layout.cu) --------------------------------------------------------------------------- */
+/* x: fp32 NCHW (N,C,H,W) -> out: NHWC bf16 view with out->C >= C (extra channels zeroed). */
+int pdac_nchw_f32_to_nhwc_bf16(const float* x, int N, int C, int H, int W, const PdacView* out, void* stream);
+/* first C_used channels of an NHWC bf16 view -> fp32 NCHW (N,C_used,H,W). */
+int pdac_nhwc_bf16_to_nchw_f32(const PdacView* x, int C_used, float* out, void* stream);
+/* Stem input: fp32 NCHW (N,3,H,W) -> space-to-depth bf16 (N,H/2,W/2,16), channel (p*2+q)*3+c = x[c][2i+p][2j+q],
+ * channels 12..15 zero. The 7x7 s2 stem conv then is a 4x4 s1 conv over this tensor (pdac_pack_stem_weight). */
+int pdac_stem_prep_f32(const float* x, int N, int H, int W, void* out, void* stream);
+/* Same from uint8 HWC patches (N,H,W,3) with (x/255 - mean)/std fused (train_main.py:73) and a per-patch geometric
+ * augmentation code aug[n] (0 none, 1 hflip, 2 vflip, 3 rot90; may be NULL); the uint8 label mask (N,H,W) gets the
+ * same geometry (mask_in/mask_out may be NULL). mean/stdv are HOST pointers to 3 floats. */
+int pdac_stem_prep_u8(const uint8_t* img, const uint8_t* mask_in, const int32_t* aug, int N, int H, int W,
+                      const float* mean, const float* stdv, void* out, uint8_t* mask_out, void* stream);
+/* state_dict weight fp32 [O][I][R][S] -> wp_f bf16 [R*S][wrows_f][kf] (row = o, col = i; forward) and/or
+ * wp_t bf16 [R*S][wrows_t][kt] (row = i, col = o; data gradient). Padding rows/cols are zeroed. s2_pad >= 0 orders
+ * wp_t's taps by stride-2 output parity class (see pdac_conv2d_dgrad), -1 keeps (r,s) order.
+ * nn.ConvTranspose2d weights [Cin][Cout][2][2] pack with O=Cin, I=Cout: wp_f is then the dgrad matrix, wp_t the forward. */
+int pdac_pack_conv_weight(const float* w, int O, int I, int R, int S, int wrows_f, int kf, void* wp_f, int wrows_t,
+                          int kt, void* wp_t, int s2_pad, void* stream);
+/* stem weight fp32 [O][3][7][7] -> bf16 [16][O][16] for the 4x4 space-to-depth form; and its gradient back. */
+int pdac_pack_stem_weight(const float* w, int O, void* wp, void* stream);
+int pdac_unpack_stem_wgrad(const float* dwp, int O, float* dw, void* stream);
+
+/* ---- BatchNorm / ReLU / residual (bn.cu) -------------------------------------------------------------------- */
+/* stats: fp32 [2][C] sum / sum-of-squares over `count` values per channel (from the conv epilogue). Writes
+ * scale_shift [2][C] (y = x*scale + shift), mean_invstd [2][C] (saved for backward) and, when training, updates
+ * running_mean/var in place (momentum; unbiased variance). train=0 derives everything from the running stats. */
+int pdac_bn_prepare(const float* stats, double count, const float* gamma, const float* beta, float eps, float momentum,
+                    int train, float* running_mean, float* running_var, float* scale_shift, float* mean_invstd, int C,
+                    void* stream);
+/* y = [relu](x*scale[c] + shift[c] + residual); scale_shift / residual may be NULL. */
+int pdac_scale_shift_act(const PdacView* x, const float* scale_shift, const PdacView* residual, int relu,
+                         const PdacView* y, void* stream);
+/* BN backward pass 1: dz = dy * (y > 0) (y may be NULL = no ReLU); sums[c] += sum dz, sums[C+c] += sum dz*xhat. */
+int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd, float* sums,
+                       void* stream);
+/* BN backward pass 2: dx = gamma*invstd*(dz - sums0/count - xhat*sums1/count) (train) or gamma*invstd*dz (eval);
+ * optionally stores dz (the residual branch's gradient) and dgamma = sums1, dbeta = sums0. */
+int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
+                      const float* gamma, const float* sums, double count, int train, const PdacView* dx,
+                      const PdacView* dz_out, float* dgamma, float* dbeta, void* stream);
+/* dz = dy * (y > 0) (y, dz may be NULL); dbias[c] += sum dz (may be NULL; caller zeroes). */
+int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias, void* stream);
+
+/* ---- pooling / resampling (pool.cu) ------------------------------------------------------------------------- */
+/* idx: uint8 [N][Ho][Wo][C] arg-max tap (r*3+s), saved for backward (may be NULL in inference). */
+int pdac_maxpool3x3s2_fwd(const PdacView* x, const PdacView* y, uint8_t* idx, void* stream);
+int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, const PdacView* dx, void* stream);
+int pdac_upsample_nearest2x_fwd(const PdacView* x, const PdacView* y, void* stream);
+int pdac_upsample_nearest2x_bwd(const PdacView* dy, const PdacView* addend, const PdacView* dx, void* stream);
+int pdac_bilinear_fwd(const PdacView* x, int align_corners, const PdacView* y, void* stream);
+int pdac_bilinear_bwd(const PdacView* dy, int align_corners, const PdacView* dx, void* stream);
+/* first C_used channels of NHWC bf16 x, resized to (Ho,Wo) -> fp32 NCHW logits; and the gradient back (all dx->C
+ * channels are written, those >= C_used with zero). */
+int pdac_bilinear_head_fwd(const PdacView* x, int C_used, int align_corners, float* out, int Ho, int Wo, void* stream);
+int pdac_bilinear_head_bwd(const float* g, int C_used, int Ho, int Wo, int align_corners, const PdacView* dx,
+                           void* stream);
+int pdac_adaptive_avgpool_fwd(const PdacView* x, const PdacView* y, void* stream);
+int pdac_adaptive_avgpool_bwd(const PdacView* dy, const PdacView* dx, void* stream);
+int pdac_add(const PdacView* a, const PdacView* b, int relu, const PdacView* y, void* stream);
+
+/* ---- loss / metric / mask / stitch / optimiser (loss.cu) ---------------------------------------------------- */
+/* tgt_dtype: 0 = fp32, 1 = uint8. sums: 3 doubles (sum p*t, sum p, sum t), kept for backward. loss: 1 float. */
+int pdac_dice_fwd(const float* logits, const void* targets, int tgt_dtype, long long n, double* sums, float smooth,
+                  float* loss, void* stream);
+int pdac_dice_bwd(const float* logits, const void* targets, int tgt_dtype, long long n, const double* sums, float smooth,
+                  const float* grad_out, float* grad_logits, void* stream);
+/* mask = ge(sigmoid(x), 0.5) as fp32 {0,1} and/or uint8. */
+int pdac_sigmoid_mask(const float* logits, long long n, float* mask_f32, uint8_t* mask_u8, void* stream);
+/* pred_kind: 0 = fp32 hard mask, 1 = fp32 logits (mask rule applied on the fly), 2 = uint8 mask. counts: 3 uint64
+ * (intersection, pred, target). score = (2*I + smooth) / (pred + target + smooth). */
+int pdac_dice_score(const void* pred, int pred_kind, const void* target, int tgt_dtype, long long n,
+                    unsigned long long* counts, float smooth, float* score, void* stream);
+int pdac_argmax_nchw(const float* logits, int N, int C, long long HW, uint8_t* out, void* stream);
+/* tiles: uint8 [T][th][tw]; tile t lands at slide rows rows[t]*th - row0 .., columns cols[t]*tw ..; parts outside
+ * the (slide_h x slide_w) band are dropped. */
+int pdac_stitch_tiles(const uint8_t* tiles, const int32_t* rows, const int32_t* cols, int T, int th, int tw,
+                      uint8_t* slide, long long slide_h, long long slide_w, long long row0, void* stream);
+/* torch.optim.Adam semantics over one flat fp32 arena; grads are multiplied by grad_scale first. */
+int pdac_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                   float beta1, float beta2, float eps, int step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,116 @@
+"""ctypes binding of libpdac_b200.so (the C ABI declared in include/pdac_b200.h).
+
+The product path has no fallback: if the shared library is missing this module raises at import of any op, and every
+entry point raises ``RuntimeError(pdac_last_error())`` on a non-zero status.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpdac_b200.so")
+
+PDAC_MAX_TAPS = 16
+
+
+class PdacView(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32),
+                ("sN", C.c_int64), ("sH", C.c_int64), ("sW", C.c_int64)]
+
+
+class PdacConv(C.Structure):
+    _fields_ = [("R", C.c_int32), ("S", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32), ("dil", C.c_int32),
+                ("relu", C.c_int32), ("wrows", C.c_int32), ("reserved", C.c_int32)]
+
+
+class PdacTap(C.Structure):
+    _fields_ = [("src", C.c_int32), ("dh", C.c_int32), ("dw", C.c_int32)]
+
+
+class PdacTapConv(C.Structure):
+    _fields_ = [("n_taps", C.c_int32), ("n_cat", C.c_int32), ("wrows", C.c_int32), ("relu", C.c_int32),
+                ("taps", PdacTap * PDAC_MAX_TAPS)]
+
+
+_VP = C.POINTER(PdacView)
+_p, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
+
+# name -> argtypes; every function returns int status (except pdac_version / pdac_last_error)
+SIGNATURES = {
+    "pdac_check_device_flag": [_p],
+    "pdac_tapconv_fwd": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
+    "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _p],
+    "pdac_conv2d_fwd": [C.POINTER(PdacConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
+    "pdac_conv2d_dgrad": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, _p],
+    "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _p],
+    "pdac_convt2x2_fwd": [_VP, _p, _i, _p, _i, _VP, _p],
+    "pdac_convt2x2_dgrad": [_VP, _p, _i, _VP, _p],
+    "pdac_convt2x2_wgrad": [_VP, _VP, _p, _p],
+    "pdac_nchw_f32_to_nhwc_bf16": [_p, _i, _i, _i, _i, _VP, _p],
+    "pdac_nhwc_bf16_to_nchw_f32": [_VP, _i, _p, _p],
+    "pdac_stem_prep_f32": [_p, _i, _i, _i, _p, _p],
+    "pdac_stem_prep_u8": [_p, _p, _p, _i, _i, _i, C.POINTER(_f), C.POINTER(_f), _p, _p, _p],
+    "pdac_pack_conv_weight": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
+    "pdac_pack_stem_weight": [_p, _i, _p, _p],
+    "pdac_unpack_stem_wgrad": [_p, _i, _p, _p],
+    "pdac_bn_prepare": [_p, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _i, _p],
+    "pdac_scale_shift_act": [_VP, _p, _VP, _i, _VP, _p],
+    "pdac_bn_bwd_reduce": [_VP, _VP, _VP, _p, _p, _p],
+    "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],
+    "pdac_relu_bwd_bias": [_VP, _VP, _VP, _p, _p],
+    "pdac_maxpool3x3s2_fwd": [_VP, _VP, _p, _p],
+    "pdac_maxpool3x3s2_bwd": [_VP, _p, _VP, _p],
+    "pdac_upsample_nearest2x_fwd": [_VP, _VP, _p],
+    "pdac_upsample_nearest2x_bwd": [_VP, _VP, _VP, _p],
+    "pdac_bilinear_fwd": [_VP, _i, _VP, _p],
+    "pdac_bilinear_bwd": [_VP, _i, _VP, _p],
+    "pdac_bilinear_head_fwd": [_VP, _i, _i, _p, _i, _i, _p],
+    "pdac_bilinear_head_bwd": [_p, _i, _i, _i, _i, _VP, _p],
+    "pdac_adaptive_avgpool_fwd": [_VP, _VP, _p],
+    "pdac_adaptive_avgpool_bwd": [_VP, _VP, _p],
+    "pdac_add": [_VP, _VP, _i, _VP, _p],
+    "pdac_dice_fwd": [_p, _p, _i, _ll, _p, _f, _p, _p],
+    "pdac_dice_bwd": [_p, _p, _i, _ll, _p, _f, _p, _p, _p],
+    "pdac_sigmoid_mask": [_p, _ll, _p, _p, _p],
+    "pdac_dice_score": [_p, _i, _p, _i, _ll, _p, _f, _p, _p],
+    "pdac_argmax_nchw": [_p, _i, _i, _ll, _p, _p],
+    "pdac_stitch_tiles": [_p, _p, _p, _i, _i, _i, _p, _ll, _ll, _ll, _p],
+    "pdac_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _f, _p],
+}
+
+_lib = None
+launches = 0  # number of C-ABI calls that launch kernels (bench.py reports it as gpu_launches)
+
+
+def load():
+    """Loads the shared library (once). Raises if it has not been built: there is no fallback implementation."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C pdac_pathological_image_segmentation_b200/csrc`). There is no CPU/PyTorch fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.pdac_version.restype = C.c_int
+    lib.pdac_version.argtypes = []
+    lib.pdac_last_error.restype = C.c_char_p
+    lib.pdac_last_error.argtypes = []
+    for name, args in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = C.c_int
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def call(name, *args):
+    """Calls a status-returning entry point; raises RuntimeError with the library's message on failure."""
+    global launches
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    launches += 1
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {lib.pdac_last_error().decode()}")
+    return rc

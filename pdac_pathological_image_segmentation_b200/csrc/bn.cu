@@ -1,0 +1,307 @@
+// BatchNorm2d (train + eval, forward + backward), ReLU / residual-add / bias-gradient passes on NHWC bf16.
+// All kernels are HBM-bound: one thread owns 8 consecutive channels (16 bytes) of a pixel and keeps its per-channel
+// constants in registers (the thread->channel-group mapping is fixed across the grid-stride loop).
+// Reference: torchvision resnet.py:82-101 (bn1/relu/bn2/+=identity/relu) and nn.BatchNorm2d semantics (eps 1e-5,
+// momentum 0.1, biased variance to normalise, unbiased for running_var).
+#include "common.h"
+#include "vec.cuh"
+
+namespace pdac {
+
+static int flatten(const PdacView* v, Flat* f, const char* what) {
+  PDAC_REQUIRE(v && v->ptr, "%s: null view", what);
+  PDAC_REQUIRE(v->C % 8 == 0, "%s: channels (%d) must be a multiple of 8", what, v->C);
+  PDAC_REQUIRE((v->H == 1 || v->sH == (int64_t)v->W * v->sW) && (v->N == 1 || v->sN == (int64_t)v->H * v->W * v->sW),
+               "%s: view must be pixel-contiguous", what);
+  PDAC_REQUIRE(((uintptr_t)v->ptr & 15) == 0 && v->sW % 8 == 0, "%s: view must be 16-byte aligned", what);
+  f->ptr = (bf16*)v->ptr;
+  f->npix = (long long)v->N * v->H * v->W;
+  f->C = v->C;
+  f->ps = v->sW;
+  return PDAC_OK;
+}
+
+struct EwGrid {
+  int blocks, cg, ppb;
+};
+static EwGrid ew_grid(long long npix, int C) {
+  EwGrid g;
+  g.cg = C / 8;
+  g.ppb = 256 / g.cg;
+  if (g.ppb < 1) g.ppb = 1;
+  long long need = (npix + g.ppb - 1) / g.ppb;
+  long long cap = (long long)num_sms() * 8;
+  g.blocks = (int)(need < cap ? need : cap);
+  if (g.blocks < 1) g.blocks = 1;
+  return g;
+}
+#define EW_SETUP(cg_, ppb_)                                   \
+  const int g = threadIdx.x % (cg_), pl = threadIdx.x / (cg_); \
+  const bool active = pl < (ppb_) && g < (cg_);                \
+  const long long pstep = (long long)gridDim.x * (ppb_);       \
+  const long long pfirst = (long long)blockIdx.x * (ppb_) + pl;
+
+// ------------------------------------------------------------------------------------------------ bn_prepare
+__global__ void bn_prepare_kernel(const float* __restrict__ stats, double count, const float* __restrict__ gamma,
+                                  const float* __restrict__ beta, float eps, float momentum, int train,
+                                  float* running_mean, float* running_var, float* __restrict__ scale_shift,
+                                  float* __restrict__ mean_invstd, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float mean, var;
+  if (train) {
+    const double m = (double)stats[c] / count;
+    double v = (double)stats[C + c] / count - m * m;
+    if (v < 0) v = 0;
+    mean = (float)m;
+    var = (float)v;
+    if (running_mean) {
+      const double unb = count > 1 ? v * count / (count - 1) : v;
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unb;
+    }
+  } else {
+    mean = running_mean[c];
+    var = running_var[c];
+  }
+  const float invstd = rsqrtf(var + eps);
+  const float ga = gamma ? gamma[c] : 1.f, be = beta ? beta[c] : 0.f;
+  const float sc = ga * invstd;
+  scale_shift[c] = sc;
+  scale_shift[C + c] = be - mean * sc;
+  if (mean_invstd) {
+    mean_invstd[c] = mean;
+    mean_invstd[C + c] = invstd;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ y = act(x*s + b + r)
+__global__ void __launch_bounds__(256) scale_shift_act_kernel(Flat x, const float* __restrict__ ss, Flat res, int relu,
+                                                              Flat y, int cg, int ppb) {
+  EW_SETUP(cg, ppb)
+  if (!active) return;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    sc[i] = ss ? ss[g * 8 + i] : 1.f;
+    sh[i] = ss ? ss[x.C + g * 8 + i] : 0.f;
+  }
+  for (long long p = pfirst; p < x.npix; p += pstep) {
+    F8 a = unpack8(ld16_stream(x.ptr + p * x.ps + g * 8));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a.v[i] = fmaf(a.v[i], sc[i], sh[i]);
+    if (res.ptr) {
+      const F8 r = unpack8(ld16_stream(res.ptr + p * res.ps + g * 8));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a.v[i] += r.v[i];
+    }
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a.v[i] = fmaxf(a.v[i], 0.f);
+    }
+    st16(y.ptr + p * y.ps + g * 8, pack8(a));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ BN backward
+// pass 1: sums[c] = sum dz, sums[C+c] = sum dz * xhat, dz = dy * (y > 0)
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
+                                                            float* __restrict__ sums, int cg, int ppb) {
+  __shared__ float red[256][17];
+  EW_SETUP(cg, ppb)
+  float s0[8], s1[8], mean[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    s0[i] = 0.f;
+    s1[i] = 0.f;
+    mean[i] = (active && mi) ? mi[g * 8 + i] : 0.f;
+  }
+  if (active) {
+    for (long long p = pfirst; p < dy.npix; p += pstep) {
+      F8 d = unpack8(ld16_stream(dy.ptr + p * dy.ps + g * 8));
+      if (y.ptr) {
+        const F8 yy = unpack8(ld16_stream(y.ptr + p * y.ps + g * 8));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+      }
+      if (x.ptr) {
+        const F8 xx = unpack8(ld16_stream(x.ptr + p * x.ps + g * 8));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s1[i] = fmaf(d.v[i], xx.v[i] - mean[i], s1[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s0[i] += d.v[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    red[threadIdx.x][i] = s0[i];
+    red[threadIdx.x][8 + i] = s1[i];
+  }
+  __syncthreads();
+  // thread t < cg*16 reduces one (channel-group, slot) column over the ppb pixel lanes
+  for (int t = threadIdx.x; t < cg * 16; t += blockDim.x) {
+    const int gg = t / 16, slot = t % 16;
+    float acc = 0.f;
+    for (int q = 0; q < ppb; ++q) acc += red[q * cg + gg][slot];
+    const int c = gg * 8 + (slot & 7);
+    if (slot < 8)
+      atomicAdd(sums + c, acc);
+    else if (x.ptr)
+      atomicAdd(sums + dy.C + c, acc * (mi ? mi[dy.C + c] : 1.f));
+  }
+}
+
+// pass 2: dx = gamma*invstd*(dz - sum_dz/M - xhat * sum_dz_xhat/M)   (train)   |   gamma*invstd*dz   (eval)
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
+                                                           const float* __restrict__ gamma,
+                                                           const float* __restrict__ sums, float inv_count, int train,
+                                                           Flat dx, Flat dz, float* __restrict__ dgamma,
+                                                           float* __restrict__ dbeta, int cg, int ppb) {
+  EW_SETUP(cg, ppb)
+  if (!active) return;
+  float a[8], m1[8], m2[8], mean[8], invstd[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = g * 8 + i;
+    mean[i] = mi[c];
+    invstd[i] = mi[dy.C + c];
+    a[i] = (gamma ? gamma[c] : 1.f) * invstd[i];
+    m1[i] = train ? sums[c] * inv_count : 0.f;
+    m2[i] = train ? sums[dy.C + c] * inv_count : 0.f;
+    if (blockIdx.x == 0 && pl == 0) {
+      if (dgamma) dgamma[c] = sums[dy.C + c];
+      if (dbeta) dbeta[c] = sums[c];
+    }
+  }
+  for (long long p = pfirst; p < dy.npix; p += pstep) {
+    F8 d = unpack8(ld16_stream(dy.ptr + p * dy.ps + g * 8));
+    if (y.ptr) {
+      const F8 yy = unpack8(ld16_stream(y.ptr + p * y.ps + g * 8));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+    }
+    if (dz.ptr) st16(dz.ptr + p * dz.ps + g * 8, pack8(d));
+    F8 o;
+    if (train) {
+      const F8 xx = unpack8(ld16_stream(x.ptr + p * x.ps + g * 8));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o.v[i] = a[i] * (d.v[i] - m1[i] - (xx.v[i] - mean[i]) * invstd[i] * m2[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o.v[i] = a[i] * d.v[i];
+    }
+    st16(dx.ptr + p * dx.ps + g * 8, pack8(o));
+  }
+}
+
+// dz = dy * (y > 0); dbias[c] += sum dz  (conv+bias+ReLU layers without BatchNorm: models/resunet.py:36-46)
+__global__ void __launch_bounds__(256) relu_bwd_bias_kernel(Flat dy, Flat y, Flat dz, float* __restrict__ dbias, int cg,
+                                                            int ppb) {
+  __shared__ float red[256][9];
+  EW_SETUP(cg, ppb)
+  float s0[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s0[i] = 0.f;
+  if (active) {
+    for (long long p = pfirst; p < dy.npix; p += pstep) {
+      F8 d = unpack8(ld16_stream(dy.ptr + p * dy.ps + g * 8));
+      if (y.ptr) {
+        const F8 yy = unpack8(ld16_stream(y.ptr + p * y.ps + g * 8));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+      }
+      if (dz.ptr) st16(dz.ptr + p * dz.ps + g * 8, pack8(d));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s0[i] += d.v[i];
+    }
+  }
+  if (!dbias) return;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[threadIdx.x][i] = s0[i];
+  __syncthreads();
+  for (int t = threadIdx.x; t < cg * 8; t += blockDim.x) {
+    const int gg = t / 8, slot = t % 8;
+    float acc = 0.f;
+    for (int q = 0; q < ppb; ++q) acc += red[q * cg + gg][slot];
+    atomicAdd(dbias + gg * 8 + slot, acc);
+  }
+}
+
+}  // namespace pdac
+
+using namespace pdac;
+
+extern "C" int pdac_bn_prepare(const float* stats, double count, const float* gamma, const float* beta, float eps,
+                               float momentum, int train, float* running_mean, float* running_var, float* scale_shift,
+                               float* mean_invstd, int C, void* stream) {
+  PDAC_REQUIRE(scale_shift && C > 0, "bn_prepare: null/empty");
+  PDAC_REQUIRE(train ? (stats != nullptr) : (running_mean && running_var),
+               "bn_prepare: train needs stats, eval needs running stats");
+  if (train) PDAC_REQUIRE(count > 1.0, "Expected more than 1 value per channel when training (count=%g)", count);
+  bn_prepare_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
+      stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd, C);
+  PDAC_LAUNCH_CHECK("bn_prepare");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_scale_shift_act(const PdacView* x, const float* scale_shift, const PdacView* residual, int relu,
+                                    const PdacView* y, void* stream) {
+  Flat fx, fy, fr = {nullptr, 0, 0, 0};
+  PDAC_TRY(flatten(x, &fx, "x"));
+  PDAC_TRY(flatten(y, &fy, "y"));
+  if (residual) PDAC_TRY(flatten(residual, &fr, "residual"));
+  PDAC_REQUIRE(fy.npix == fx.npix && fy.C == fx.C && (!residual || (fr.npix == fx.npix && fr.C == fx.C)),
+               "scale_shift_act: shape mismatch");
+  PDAC_REQUIRE(fx.C <= 2048, "scale_shift_act: too many channels");
+  if (fx.npix == 0) return PDAC_OK;
+  const EwGrid g = ew_grid(fx.npix, fx.C);
+  scale_shift_act_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fx, scale_shift, fr, relu, fy, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("scale_shift_act");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
+                                  float* sums, void* stream) {
+  Flat fd, fy = {nullptr, 0, 0, 0}, fx = {nullptr, 0, 0, 0};
+  PDAC_TRY(flatten(dy, &fd, "dy"));
+  if (y) PDAC_TRY(flatten(y, &fy, "y"));
+  if (x) PDAC_TRY(flatten(x, &fx, "x"));
+  PDAC_REQUIRE(sums, "bn_bwd_reduce: null sums");
+  PDAC_REQUIRE(fd.C <= 2048, "bn_bwd_reduce: too many channels");
+  const EwGrid g = ew_grid(fd.npix, fd.C);
+  bn_bwd_reduce_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, sums, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("bn_bwd_reduce");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
+                                 const float* gamma, const float* sums, double count, int train, const PdacView* dx,
+                                 const PdacView* dz_out, float* dgamma, float* dbeta, void* stream) {
+  Flat fd, fy = {nullptr, 0, 0, 0}, fx = {nullptr, 0, 0, 0}, fdx, fdz = {nullptr, 0, 0, 0};
+  PDAC_TRY(flatten(dy, &fd, "dy"));
+  if (y) PDAC_TRY(flatten(y, &fy, "y"));
+  if (x) PDAC_TRY(flatten(x, &fx, "x"));
+  PDAC_TRY(flatten(dx, &fdx, "dx"));
+  if (dz_out) PDAC_TRY(flatten(dz_out, &fdz, "dz"));
+  PDAC_REQUIRE(mean_invstd && sums, "bn_bwd_apply: null stats");
+  PDAC_REQUIRE(!train || x, "bn_bwd_apply: training mode needs the conv output x");
+  const EwGrid g = ew_grid(fd.npix, fd.C);
+  bn_bwd_apply_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, sums,
+                                                                  (float)(1.0 / count), train, fdx, fdz, dgamma, dbeta,
+                                                                  g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("bn_bwd_apply");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias,
+                                  void* stream) {
+  Flat fd, fy = {nullptr, 0, 0, 0}, fdz = {nullptr, 0, 0, 0};
+  PDAC_TRY(flatten(dy, &fd, "dy"));
+  if (y) PDAC_TRY(flatten(y, &fy, "y"));
+  if (dz) PDAC_TRY(flatten(dz, &fdz, "dz"));
+  const EwGrid g = ew_grid(fd.npix, fd.C);
+  relu_bwd_bias_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fdz, dbias, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("relu_bwd_bias");
+  return PDAC_OK;
+}

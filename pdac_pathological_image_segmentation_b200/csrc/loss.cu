@@ -1,0 +1,296 @@
+// Loss / metric / mask reductions and the slide stitcher.
+//   DiceLoss.forward            util.py:10-19     1 - (2*sum(p*t) + s) / (sum(p) + sum(t) + s),  p = sigmoid(x), whole batch
+//   dice_score                  util.py:22-26     (2*sum(pred*t) + s) / (sum(pred) + sum(t) + s) on hard masks
+//   mask                        train_worker.py:24,72; test.py:144   ge(sigmoid(x), 0.5).float()
+//   softmax-argmax              BASELINE.json configs[0]/[4] (classes >= 2): argmax_c x_c, ties -> lowest index
+//   stitch                      visualize/predict_overlay.ipynb (missing) per configs/visualize_config.yaml:3-15
+//   Adam                        torch.optim.Adam(lr) at train_worker.py:184 (betas .9/.999, eps 1e-8, no weight decay)
+// Reductions accumulate per-thread in fp32, per-block and globally in fp64 (the reference's fp32 tree sum is only
+// approximately exact at 2^24+ elements), counts in int64.
+#include "common.h"
+#include "vec.cuh"
+
+namespace pdac {
+
+// The reference's sigmoid, as ATen computes it in fp32 on CUDA: 1 / (1 + exp(-x)).
+__device__ __forceinline__ float sigmoid_ref(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ double block_sum_d(double v, double* sh) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (warp == 0) {
+    r = lane < (int)(blockDim.x >> 5) ? sh[lane] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  }
+  __syncthreads();
+  return r;
+}
+
+template <typename T>
+__device__ __forceinline__ float tgt_val(const T* t, long long i) { return (float)t[i]; }
+
+// sums[0] = sum p*t, sums[1] = sum p, sums[2] = sum t
+template <typename T>
+__global__ void __launch_bounds__(256) dice_fwd_kernel(const float* __restrict__ x, const T* __restrict__ t, long long n,
+                                                       double* __restrict__ sums) {
+  __shared__ double sh[8];
+  float i0 = 0.f, p0 = 0.f, t0 = 0.f;
+  double I = 0, P = 0, Tt = 0;
+  int cnt = 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float p = sigmoid_ref(__ldg(x + i));
+    const float tv = tgt_val(t, i);
+    i0 = fmaf(p, tv, i0);
+    p0 += p;
+    t0 += tv;
+    if (++cnt == 64) {  // flush the fp32 partials before they lose bits
+      I += i0; P += p0; Tt += t0;
+      i0 = p0 = t0 = 0.f;
+      cnt = 0;
+    }
+  }
+  I += i0; P += p0; Tt += t0;
+  I = block_sum_d(I, sh);
+  P = block_sum_d(P, sh);
+  Tt = block_sum_d(Tt, sh);
+  if (threadIdx.x == 0) {
+    atomicAdd(sums, I);
+    atomicAdd(sums + 1, P);
+    atomicAdd(sums + 2, Tt);
+  }
+}
+__global__ void dice_finalize_kernel(const double* __restrict__ sums, float smooth, float* __restrict__ loss) {
+  const float I = (float)sums[0], P = (float)sums[1], T = (float)sums[2];
+  const float dice = (2.0f * I + smooth) / (P + T + smooth);
+  *loss = 1.0f - dice;
+}
+// dL/dx = -gout * [2 t D - (2I + s)] / D^2 * p (1 - p),  D = P + T + s
+template <typename T>
+__global__ void __launch_bounds__(256) dice_bwd_kernel(const float* __restrict__ x, const T* __restrict__ t, long long n,
+                                                       const double* __restrict__ sums, float smooth,
+                                                       const float* __restrict__ gout, float* __restrict__ gx) {
+  const double D = sums[1] + sums[2] + (double)smooth;
+  const double num = 2.0 * sums[0] + (double)smooth;
+  const float go = gout ? *gout : 1.f;
+  const float k1 = (float)(-2.0 / D) * go, k0 = (float)(num / (D * D)) * go;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float p = sigmoid_ref(__ldg(x + i));
+    const float tv = tgt_val(t, i);
+    gx[i] = (k1 * tv + k0) * p * (1.f - p);
+  }
+}
+
+// mask = ge(sigmoid(x), 0.5)
+__global__ void __launch_bounds__(256) sigmoid_mask_kernel(const float* __restrict__ x, long long n,
+                                                           float* __restrict__ mf, uint8_t* __restrict__ mu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const bool on = sigmoid_ref(__ldg(x + i)) >= 0.5f;
+    if (mf) mf[i] = on ? 1.f : 0.f;
+    if (mu) mu[i] = on ? 1 : 0;
+  }
+}
+
+// counts[0] = sum pred*t, counts[1] = sum pred, counts[2] = sum t  (pred from logits via the mask rule, or given)
+template <typename P, typename T>
+__global__ void __launch_bounds__(256) dice_count_kernel(const P* __restrict__ pred, int pred_is_logits,
+                                                         const T* __restrict__ t, long long n,
+                                                         unsigned long long* __restrict__ counts) {
+  __shared__ double sh[8];
+  unsigned int a = 0, b = 0, c = 0;
+  double A = 0, B = 0, Cc = 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float pv = (float)pred[i];
+    const bool on = pred_is_logits ? (sigmoid_ref(pv) >= 0.5f) : (pv != 0.f);
+    const bool tv = (float)t[i] != 0.f;
+    a += (on && tv);
+    b += on;
+    c += tv;
+  }
+  A = block_sum_d((double)a, sh);
+  B = block_sum_d((double)b, sh);
+  Cc = block_sum_d((double)c, sh);
+  if (threadIdx.x == 0) {
+    atomicAdd(counts, (unsigned long long)A);
+    atomicAdd(counts + 1, (unsigned long long)B);
+    atomicAdd(counts + 2, (unsigned long long)Cc);
+  }
+}
+__global__ void dice_score_finalize_kernel(const unsigned long long* __restrict__ counts, float smooth,
+                                           float* __restrict__ score) {
+  const float I = (float)counts[0], u = (float)counts[1] + (float)counts[2];
+  *score = (2.0f * I + smooth) / (u + smooth);
+}
+
+// argmax over the channel dim of NCHW fp32 logits; ties -> lowest index; NaN wins (torch semantics)
+__global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ x, int C, long long HW, long long NHW,
+                                                     uint8_t* __restrict__ out) {
+  for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < NHW; p += (long long)gridDim.x * blockDim.x) {
+    const long long n = p / HW, hw = p - n * HW;
+    const float* xp = x + n * C * HW + hw;
+    float best = __ldg(xp);
+    int bi = 0;
+    for (int c = 1; c < C; ++c) {
+      const float v = __ldg(xp + (long long)c * HW);
+      if (!(best != best) && (v > best || v != v)) {
+        best = v;
+        bi = c;
+      }
+    }
+    out[p] = (uint8_t)bi;
+  }
+}
+
+// tile t (th x tw bytes) -> slide[(rows[t]*th - row0) + y][cols[t]*tw + x]; tiles outside the band are skipped
+__global__ void __launch_bounds__(256) stitch_kernel(const uint8_t* __restrict__ tiles, const int32_t* __restrict__ rows,
+                                                     const int32_t* __restrict__ cols, int T, int th, int tw,
+                                                     uint8_t* __restrict__ slide, long long slide_h, long long slide_w,
+                                                     long long row0) {
+  const int vec = (tw % 16 == 0) ? 16 : 1;
+  const int wpr = tw / vec;  // work items per tile row
+  const long long per_tile = (long long)th * wpr;
+  const long long total = (long long)T * per_tile;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(e / per_tile);
+    const long long r = e - (long long)t * per_tile;
+    const int y = (int)(r / wpr), xw = (int)(r - (long long)y * wpr);
+    const long long sy = (long long)rows[t] * th - row0 + y;
+    const long long sx = (long long)cols[t] * tw + (long long)xw * vec;
+    if (sy < 0 || sy >= slide_h || sx < 0 || sx + vec > slide_w) continue;
+    const uint8_t* src = tiles + ((long long)t * th + y) * tw + (long long)xw * vec;
+    uint8_t* dst = slide + sy * slide_w + sx;
+    if (vec == 16 && (((uintptr_t)dst | (uintptr_t)src) & 15) == 0)
+      *reinterpret_cast<uint4*>(dst) = __ldg(reinterpret_cast<const uint4*>(src));
+    else
+      for (int k = 0; k < vec; ++k) dst[k] = src[k];
+  }
+}
+
+// Adam over one flat fp32 arena (parameters, gradients and both moments share the element index)
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                   float* __restrict__ m, float* __restrict__ v, long long n, float lr,
+                                                   float b1, float b2, float eps, float bc1, float bc2_sqrt,
+                                                   float grad_scale) {
+  const float step = lr / bc1;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i] * grad_scale;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step * mi / (sqrtf(vi) / bc2_sqrt + eps);
+  }
+}
+
+static int rblocks(long long n) {
+  long long b = (n + 255) / 256;
+  const long long cap = (long long)num_sms() * 8;
+  if (b > cap) b = cap;
+  return b < 1 ? 1 : (int)b;
+}
+
+}  // namespace pdac
+
+using namespace pdac;
+
+// tgt_dtype: 0 = fp32, 1 = uint8
+extern "C" int pdac_dice_fwd(const float* logits, const void* targets, int tgt_dtype, long long n, double* sums,
+                             float smooth, float* loss, void* stream) {
+  PDAC_REQUIRE(logits && targets && sums && loss && n >= 0, "dice_fwd: null argument");
+  PDAC_CUDA(cudaMemsetAsync(sums, 0, 3 * sizeof(double), (cudaStream_t)stream));
+  if (n > 0) {
+    if (tgt_dtype == 0)
+      dice_fwd_kernel<float><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const float*)targets, n, sums);
+    else
+      dice_fwd_kernel<uint8_t><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const uint8_t*)targets, n, sums);
+    PDAC_LAUNCH_CHECK("dice_fwd");
+  }
+  dice_finalize_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sums, smooth, loss);
+  PDAC_LAUNCH_CHECK("dice_finalize");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_dice_bwd(const float* logits, const void* targets, int tgt_dtype, long long n, const double* sums,
+                             float smooth, const float* grad_out, float* grad_logits, void* stream) {
+  PDAC_REQUIRE(logits && targets && sums && grad_logits, "dice_bwd: null argument");
+  if (n <= 0) return PDAC_OK;
+  if (tgt_dtype == 0)
+    dice_bwd_kernel<float><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const float*)targets, n, sums, smooth,
+                                                                          grad_out, grad_logits);
+  else
+    dice_bwd_kernel<uint8_t><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const uint8_t*)targets, n, sums,
+                                                                            smooth, grad_out, grad_logits);
+  PDAC_LAUNCH_CHECK("dice_bwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_sigmoid_mask(const float* logits, long long n, float* mask_f32, uint8_t* mask_u8, void* stream) {
+  PDAC_REQUIRE(logits && (mask_f32 || mask_u8), "sigmoid_mask: null argument");
+  if (n <= 0) return PDAC_OK;
+  sigmoid_mask_kernel<<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, n, mask_f32, mask_u8);
+  PDAC_LAUNCH_CHECK("sigmoid_mask");
+  return PDAC_OK;
+}
+
+// pred_kind: 0 = fp32 hard mask {0,1}, 1 = fp32 logits (mask rule applied on the fly), 2 = uint8 mask.
+// tgt_dtype: 0 = fp32, 1 = uint8. counts: 3 x uint64.
+extern "C" int pdac_dice_score(const void* pred, int pred_kind, const void* target, int tgt_dtype, long long n,
+                               unsigned long long* counts, float smooth, float* score, void* stream) {
+  PDAC_REQUIRE(pred && target && counts && score, "dice_score: null argument");
+  PDAC_CUDA(cudaMemsetAsync(counts, 0, 3 * sizeof(unsigned long long), (cudaStream_t)stream));
+  if (n > 0) {
+    const int b = rblocks(n);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (pred_kind == 2) {
+      if (tgt_dtype == 0)
+        dice_count_kernel<uint8_t, float><<<b, 256, 0, s>>>((const uint8_t*)pred, 0, (const float*)target, n, counts);
+      else
+        dice_count_kernel<uint8_t, uint8_t><<<b, 256, 0, s>>>((const uint8_t*)pred, 0, (const uint8_t*)target, n, counts);
+    } else {
+      if (tgt_dtype == 0)
+        dice_count_kernel<float, float><<<b, 256, 0, s>>>((const float*)pred, pred_kind == 1, (const float*)target, n,
+                                                          counts);
+      else
+        dice_count_kernel<float, uint8_t><<<b, 256, 0, s>>>((const float*)pred, pred_kind == 1, (const uint8_t*)target, n,
+                                                            counts);
+    }
+    PDAC_LAUNCH_CHECK("dice_count");
+  }
+  dice_score_finalize_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counts, smooth, score);
+  PDAC_LAUNCH_CHECK("dice_score_finalize");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_argmax_nchw(const float* logits, int N, int C, long long HW, uint8_t* out, void* stream) {
+  PDAC_REQUIRE(logits && out && C >= 1 && C <= 255, "argmax: bad arguments");
+  const long long nhw = (long long)N * HW;
+  if (nhw <= 0) return PDAC_OK;
+  argmax_kernel<<<rblocks(nhw), 256, 0, (cudaStream_t)stream>>>(logits, C, HW, nhw, out);
+  PDAC_LAUNCH_CHECK("argmax");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_stitch_tiles(const uint8_t* tiles, const int32_t* rows, const int32_t* cols, int T, int th, int tw,
+                                 uint8_t* slide, long long slide_h, long long slide_w, long long row0, void* stream) {
+  PDAC_REQUIRE(tiles && rows && cols && slide && th > 0 && tw > 0 && T >= 0, "stitch: bad arguments");
+  if (T == 0) return PDAC_OK;
+  const long long total = (long long)T * th * (tw % 16 == 0 ? tw / 16 : tw);
+  stitch_kernel<<<rblocks(total), 256, 0, (cudaStream_t)stream>>>(tiles, rows, cols, T, th, tw, slide, slide_h, slide_w,
+                                                                  row0);
+  PDAC_LAUNCH_CHECK("stitch");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                              float beta1, float beta2, float eps, int step, float grad_scale, void* stream) {
+  PDAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && step >= 1, "adam: bad arguments");
+  if (n <= 0) return PDAC_OK;
+  const float bc1 = 1.f - powf(beta1, (float)step);
+  const float bc2 = 1.f - powf(beta2, (float)step);
+  adam_kernel<<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
+                                                            bc1, sqrtf(bc2), grad_scale);
+  PDAC_LAUNCH_CHECK("adam");
+  return PDAC_OK;
+}

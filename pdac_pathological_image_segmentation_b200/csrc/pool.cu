@@ -1,0 +1,521 @@
+// Pooling / resampling passes on NHWC bf16 (all HBM-bound, 16-byte vectorised, gather-form backward = deterministic):
+//   MaxPool2d(3, stride 2, pad 1)                 torchvision resnet.py:200 (run at models/resunet.py:28)
+//   nearest x2 up-sampling                         smp UnetDecoder / FPNBlock
+//   bilinear resize, align_corners False / True    models/resunet.py:51-56; smp SegmentationHead / FPN / PSP / ASPP
+//   AdaptiveAvgPool2d                              smp PSPModule / ASPPPooling (App. B.4/B.5)
+#include "common.h"
+#include "vec.cuh"
+
+namespace pdac {
+
+struct V4 {  // device-side view
+  bf16* ptr;
+  int N, H, W, C;
+  long long sN, sH, sW;
+  __device__ __forceinline__ bf16* at(int n, int h, int w) const { return ptr + n * sN + h * sH + w * sW; }
+};
+static int to_v4(const PdacView* v, V4* o, const char* what) {
+  PDAC_REQUIRE(v && v->ptr, "%s: null view", what);
+  PDAC_REQUIRE(v->C % 8 == 0, "%s: channels (%d) must be a multiple of 8", what, v->C);
+  PDAC_REQUIRE(((uintptr_t)v->ptr & 15) == 0 && v->sW % 8 == 0 && v->sH % 8 == 0 && v->sN % 8 == 0,
+               "%s: view must be 16-byte aligned", what);
+  o->ptr = (bf16*)v->ptr;
+  o->N = v->N;
+  o->H = v->H;
+  o->W = v->W;
+  o->C = v->C;
+  o->sN = v->sN;
+  o->sH = v->sH;
+  o->sW = v->sW;
+  return PDAC_OK;
+}
+static int blocks_for(long long n) {
+  long long b = (n + 255) / 256;
+  const long long cap = (long long)num_sms() * 16;
+  if (b > cap) b = cap;
+  return b < 1 ? 1 : (int)b;
+}
+#define PIX_LOOP(total)                                                                               \
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < (total);                    \
+       e += (long long)gridDim.x * blockDim.x)
+#define DECODE(e, CG, Wd, Hd)            \
+  const int g = (int)((e) % (CG));       \
+  long long r_ = (e) / (CG);             \
+  const int w = (int)(r_ % (Wd));        \
+  r_ /= (Wd);                            \
+  const int h = (int)(r_ % (Hd));        \
+  const int n = (int)(r_ / (Hd));
+
+// ------------------------------------------------------------------------------------------------ maxpool 3x3 s2 p1
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(V4 x, V4 y, uint8_t* __restrict__ idx) {
+  const int cg = x.C / 8;
+  const long long total = (long long)y.N * y.H * y.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, y.W, y.H)
+    float best[8];
+    int bi[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      best[i] = -INFINITY;
+      bi[i] = 4;
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int ih = 2 * h - 1 + r;
+      if (ih < 0 || ih >= x.H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int iw = 2 * w - 1 + s;
+        if (iw < 0 || iw >= x.W) continue;
+        const F8 v = unpack8(ld16(x.at(n, ih, iw) + g * 8));
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (v.v[i] > best[i] || v.v[i] != v.v[i]) {
+            best[i] = v.v[i];
+            bi[i] = r * 3 + s;
+          }
+      }
+    }
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = best[i];
+    st16(y.at(n, h, w) + g * 8, pack8(o));
+    if (idx) {
+      uint2 p;
+      p.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+      p.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+      *reinterpret_cast<uint2*>(idx + (((long long)n * y.H + h) * y.W + w) * x.C + g * 8) = p;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(V4 dy, const uint8_t* __restrict__ idx, V4 dx) {
+  const int cg = dx.C / 8;
+  const long long total = (long long)dx.N * dx.H * dx.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, dx.W, dx.H)
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    const int oh_lo = h >> 1, oh_hi = (h + 1) >> 1;  // windows with 2*oh-1 <= h <= 2*oh+1
+    const int ow_lo = w >> 1, ow_hi = (w + 1) >> 1;
+    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+      if (oh >= dy.H) continue;
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        if (ow >= dy.W) continue;
+        const int tap = (h - (2 * oh - 1)) * 3 + (w - (2 * ow - 1));
+        const uint2 p = __ldg(reinterpret_cast<const uint2*>(idx + (((long long)n * dy.H + oh) * dy.W + ow) * dx.C + g * 8));
+        const F8 d = unpack8(ld16(dy.at(n, oh, ow) + g * 8));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int b = (int)(((i < 4 ? p.x : p.y) >> ((i & 3) * 8)) & 0xff);
+          if (b == tap) acc[i] += d.v[i];
+        }
+      }
+    }
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+    st16(dx.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ nearest x2
+__global__ void __launch_bounds__(256) up2_fwd_kernel(V4 x, V4 y) {
+  const int cg = x.C / 8;
+  const long long total = (long long)y.N * y.H * y.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, y.W, y.H)
+    st16(y.at(n, h, w) + g * 8, ld16(x.at(n, h >> 1, w >> 1) + g * 8));
+  }
+}
+// dx = sum of the 2x2 block of dy (+ addend)
+__global__ void __launch_bounds__(256) up2_bwd_kernel(V4 dy, V4 add, V4 dx) {
+  const int cg = dx.C / 8;
+  const long long total = (long long)dx.N * dx.H * dx.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, dx.W, dx.H)
+    const F8 a = unpack8(ld16_stream(dy.at(n, 2 * h, 2 * w) + g * 8));
+    const F8 b = unpack8(ld16_stream(dy.at(n, 2 * h, 2 * w + 1) + g * 8));
+    const F8 c = unpack8(ld16_stream(dy.at(n, 2 * h + 1, 2 * w) + g * 8));
+    const F8 d = unpack8(ld16_stream(dy.at(n, 2 * h + 1, 2 * w + 1) + g * 8));
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = (a.v[i] + b.v[i]) + (c.v[i] + d.v[i]);
+    if (add.ptr) {
+      const F8 z = unpack8(ld16_stream(add.at(n, h, w) + g * 8));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o.v[i] += z.v[i];
+    }
+    st16(dx.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ bilinear
+// Same index arithmetic as ATen's upsample_bilinear2d (area_pixel_compute_source_index).
+struct Lin {
+  float scale;  // align_corners ? (in-1)/(out-1) : in/out
+  int align;
+  int in;
+  __device__ __forceinline__ void src(int o, int& i0, int& i1, float& l1) const {
+    float s = align ? scale * o : fmaxf(scale * (o + 0.5f) - 0.5f, 0.f);
+    i0 = (int)s;
+    if (i0 > in - 1) i0 = in - 1;
+    i1 = i0 + (i0 < in - 1 ? 1 : 0);
+    l1 = s - (float)i0;
+  }
+};
+static Lin make_lin(int in, int out, int align) {
+  Lin l;
+  l.align = align;
+  l.in = in;
+  l.scale = align ? (out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.f) : (float)in / (float)out;
+  return l;
+}
+
+__global__ void __launch_bounds__(256) bilinear_fwd_kernel(V4 x, V4 y, Lin lh, Lin lw) {
+  const int cg = x.C / 8;
+  const long long total = (long long)y.N * y.H * y.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, y.W, y.H)
+    int h0, h1, w0, w1;
+    float a, b;
+    lh.src(h, h0, h1, a);
+    lw.src(w, w0, w1, b);
+    const F8 v00 = unpack8(ld16(x.at(n, h0, w0) + g * 8)), v01 = unpack8(ld16(x.at(n, h0, w1) + g * 8));
+    const F8 v10 = unpack8(ld16(x.at(n, h1, w0) + g * 8)), v11 = unpack8(ld16(x.at(n, h1, w1) + g * 8));
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      o.v[i] = (1.f - a) * ((1.f - b) * v00.v[i] + b * v01.v[i]) + a * ((1.f - b) * v10.v[i] + b * v11.v[i]);
+    st16(y.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+
+// candidate output range whose 2-tap footprint can touch input index i (checked exactly by the caller)
+__device__ __forceinline__ void out_range(const Lin& l, int i, int out, int& lo, int& hi) {
+  if (l.scale <= 0.f) {
+    lo = 0;
+    hi = out - 1;
+    return;
+  }
+  const float inv = 1.f / l.scale;
+  float flo, fhi;
+  if (l.align) {
+    flo = (i - 1) * inv;
+    fhi = (i + 1) * inv;
+  } else {
+    flo = (i - 1 + 0.5f) * inv - 0.5f;
+    fhi = (i + 1 + 0.5f) * inv - 0.5f;
+  }
+  lo = (int)floorf(flo) - 1;
+  hi = (int)ceilf(fhi) + 1;
+  if (lo < 0) lo = 0;
+  if (hi > out - 1) hi = out - 1;
+}
+
+__global__ void __launch_bounds__(256) bilinear_bwd_kernel(V4 dy, V4 dx, Lin lh, Lin lw) {
+  const int cg = dx.C / 8;
+  const long long total = (long long)dx.N * dx.H * dx.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, dx.W, dx.H)
+    int ohl, ohh, owl, owh;
+    out_range(lh, h, dy.H, ohl, ohh);
+    out_range(lw, w, dy.W, owl, owh);
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    for (int oh = ohl; oh <= ohh; ++oh) {
+      int h0, h1;
+      float a;
+      lh.src(oh, h0, h1, a);
+      const float wh = (h0 == h ? 1.f - a : 0.f) + (h1 == h ? a : 0.f);
+      if (wh == 0.f) continue;
+      for (int ow = owl; ow <= owh; ++ow) {
+        int w0, w1;
+        float b;
+        lw.src(ow, w0, w1, b);
+        const float ww = (w0 == w ? 1.f - b : 0.f) + (w1 == w ? b : 0.f);
+        if (ww == 0.f) continue;
+        const F8 d = unpack8(ld16(dy.at(n, oh, ow) + g * 8));
+        const float k = wh * ww;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(k, d.v[i], acc[i]);
+      }
+    }
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+    st16(dx.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+
+// head variants: NHWC bf16 (first Cu channels of a padded buffer) -> NCHW fp32 logits, and the gradient back
+__global__ void __launch_bounds__(256) bilinear_head_fwd_kernel(V4 x, int Cu, float* __restrict__ out, int Ho, int Wo,
+                                                                Lin lh, Lin lw) {
+  const long long total = (long long)x.N * Cu * Ho * Wo;
+  PIX_LOOP(total) {
+    const int w = (int)(e % Wo);
+    long long r = e / Wo;
+    const int h = (int)(r % Ho);
+    r /= Ho;
+    const int c = (int)(r % Cu);
+    const int n = (int)(r / Cu);
+    int h0, h1, w0, w1;
+    float a, b;
+    lh.src(h, h0, h1, a);
+    lw.src(w, w0, w1, b);
+    const float v00 = __bfloat162float(x.at(n, h0, w0)[c]), v01 = __bfloat162float(x.at(n, h0, w1)[c]);
+    const float v10 = __bfloat162float(x.at(n, h1, w0)[c]), v11 = __bfloat162float(x.at(n, h1, w1)[c]);
+    out[e] = (1.f - a) * ((1.f - b) * v00 + b * v01) + a * ((1.f - b) * v10 + b * v11);
+  }
+}
+__global__ void __launch_bounds__(256) bilinear_head_bwd_kernel(const float* __restrict__ g, int Cu, int Ho, int Wo,
+                                                                V4 dx, Lin lh, Lin lw) {
+  const long long total = (long long)dx.N * dx.H * dx.W;
+  PIX_LOOP(total) {
+    const int w = (int)(e % dx.W);
+    long long r = e / dx.W;
+    const int h = (int)(r % dx.H);
+    const int n = (int)(r / dx.H);
+    int ohl, ohh, owl, owh;
+    out_range(lh, h, Ho, ohl, ohh);
+    out_range(lw, w, Wo, owl, owh);
+    bf16* op = dx.at(n, h, w);
+    for (int c = 0; c < dx.C; ++c) {
+      float acc = 0.f;
+      if (c < Cu) {
+        const float* gp = g + ((long long)n * Cu + c) * Ho * Wo;
+        for (int oh = ohl; oh <= ohh; ++oh) {
+          int h0, h1;
+          float a;
+          lh.src(oh, h0, h1, a);
+          const float wh = (h0 == h ? 1.f - a : 0.f) + (h1 == h ? a : 0.f);
+          if (wh == 0.f) continue;
+          for (int ow = owl; ow <= owh; ++ow) {
+            int w0, w1;
+            float b;
+            lw.src(ow, w0, w1, b);
+            const float ww = (w0 == w ? 1.f - b : 0.f) + (w1 == w ? b : 0.f);
+            if (ww != 0.f) acc = fmaf(wh * ww, __ldg(gp + (long long)oh * Wo + ow), acc);
+          }
+        }
+      }
+      op[c] = __float2bfloat16(acc);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ adaptive avg pool
+__device__ __forceinline__ int bin_lo(int i, int in, int out) { return (i * in) / out; }
+__device__ __forceinline__ int bin_hi(int i, int in, int out) { return ((i + 1) * in + out - 1) / out; }
+
+__global__ void __launch_bounds__(256) adaptive_avgpool_fwd_kernel(V4 x, V4 y) {
+  const int cg = x.C / 8;
+  const long long total = (long long)y.N * y.H * y.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, y.W, y.H)
+    const int h0 = bin_lo(h, x.H, y.H), h1 = bin_hi(h, x.H, y.H), w0 = bin_lo(w, x.W, y.W), w1 = bin_hi(w, x.W, y.W);
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    for (int ih = h0; ih < h1; ++ih)
+      for (int iw = w0; iw < w1; ++iw) {
+        const F8 v = unpack8(ld16(x.at(n, ih, iw) + g * 8));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += v.v[i];
+      }
+    const float inv = 1.f / (float)((h1 - h0) * (w1 - w0));
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i] * inv;
+    st16(y.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+__global__ void __launch_bounds__(256) adaptive_avgpool_bwd_kernel(V4 dy, V4 dx) {
+  const int cg = dx.C / 8;
+  const long long total = (long long)dx.N * dx.H * dx.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, dx.W, dx.H)
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    for (int oh = 0; oh < dy.H; ++oh) {
+      const int h0 = bin_lo(oh, dx.H, dy.H), h1 = bin_hi(oh, dx.H, dy.H);
+      if (h < h0 || h >= h1) continue;
+      for (int ow = 0; ow < dy.W; ++ow) {
+        const int w0 = bin_lo(ow, dx.W, dy.W), w1 = bin_hi(ow, dx.W, dy.W);
+        if (w < w0 || w >= w1) continue;
+        const F8 d = unpack8(ld16(dy.at(n, oh, ow) + g * 8));
+        const float inv = 1.f / (float)((h1 - h0) * (w1 - w0));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] = fmaf(d.v[i], inv, acc[i]);
+      }
+    }
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+    st16(dx.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+
+// y = a + b (+ relu)  on arbitrary (same-shape) views
+__global__ void __launch_bounds__(256) add_kernel(V4 a, V4 b, V4 y, int relu) {
+  const int cg = y.C / 8;
+  const long long total = (long long)y.N * y.H * y.W * cg;
+  PIX_LOOP(total) {
+    DECODE(e, cg, y.W, y.H)
+    F8 u = unpack8(ld16_stream(a.at(n, h, w) + g * 8));
+    const F8 v = unpack8(ld16_stream(b.at(n, h, w) + g * 8));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      u.v[i] += v.v[i];
+      if (relu) u.v[i] = fmaxf(u.v[i], 0.f);
+    }
+    st16(y.at(n, h, w) + g * 8, pack8(u));
+  }
+}
+
+}  // namespace pdac
+
+using namespace pdac;
+
+extern "C" int pdac_maxpool3x3s2_fwd(const PdacView* x, const PdacView* y, uint8_t* idx, void* stream) {
+  V4 vx, vy;
+  PDAC_TRY(to_v4(x, &vx, "x"));
+  PDAC_TRY(to_v4(y, &vy, "y"));
+  PDAC_REQUIRE(vy.N == vx.N && vy.C == vx.C && vy.H == (vx.H - 1) / 2 + 1 && vy.W == (vx.W - 1) / 2 + 1,
+               "maxpool: output shape mismatch");
+  PDAC_REQUIRE(!idx || ((uintptr_t)idx & 7) == 0, "maxpool: idx must be 8-byte aligned");
+  const long long total = (long long)vy.N * vy.H * vy.W * (vx.C / 8);
+  if (!total) return PDAC_OK;
+  maxpool_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vx, vy, idx);
+  PDAC_LAUNCH_CHECK("maxpool_fwd");
+  return PDAC_OK;
+}
+extern "C" int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, const PdacView* dx, void* stream) {
+  V4 vdy, vdx;
+  PDAC_TRY(to_v4(dy, &vdy, "dy"));
+  PDAC_TRY(to_v4(dx, &vdx, "dx"));
+  PDAC_REQUIRE(idx, "maxpool bwd: null idx");
+  PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C && vdy.H == (vdx.H - 1) / 2 + 1 && vdy.W == (vdx.W - 1) / 2 + 1,
+               "maxpool bwd: shape mismatch");
+  const long long total = (long long)vdx.N * vdx.H * vdx.W * (vdx.C / 8);
+  if (!total) return PDAC_OK;
+  maxpool_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vdy, idx, vdx);
+  PDAC_LAUNCH_CHECK("maxpool_bwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_upsample_nearest2x_fwd(const PdacView* x, const PdacView* y, void* stream) {
+  V4 vx, vy;
+  PDAC_TRY(to_v4(x, &vx, "x"));
+  PDAC_TRY(to_v4(y, &vy, "y"));
+  PDAC_REQUIRE(vy.N == vx.N && vy.C == vx.C && vy.H == 2 * vx.H && vy.W == 2 * vx.W, "nearest2x: shape mismatch");
+  const long long total = (long long)vy.N * vy.H * vy.W * (vx.C / 8);
+  if (!total) return PDAC_OK;
+  up2_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vx, vy);
+  PDAC_LAUNCH_CHECK("up2_fwd");
+  return PDAC_OK;
+}
+extern "C" int pdac_upsample_nearest2x_bwd(const PdacView* dy, const PdacView* addend, const PdacView* dx,
+                                           void* stream) {
+  V4 vdy, vdx, va = {nullptr, 0, 0, 0, 0, 0, 0, 0};
+  PDAC_TRY(to_v4(dy, &vdy, "dy"));
+  PDAC_TRY(to_v4(dx, &vdx, "dx"));
+  if (addend) PDAC_TRY(to_v4(addend, &va, "addend"));
+  PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C && vdy.H == 2 * vdx.H && vdy.W == 2 * vdx.W,
+               "nearest2x bwd: shape mismatch");
+  const long long total = (long long)vdx.N * vdx.H * vdx.W * (vdx.C / 8);
+  if (!total) return PDAC_OK;
+  up2_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vdy, va, vdx);
+  PDAC_LAUNCH_CHECK("up2_bwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_bilinear_fwd(const PdacView* x, int align_corners, const PdacView* y, void* stream) {
+  V4 vx, vy;
+  PDAC_TRY(to_v4(x, &vx, "x"));
+  PDAC_TRY(to_v4(y, &vy, "y"));
+  PDAC_REQUIRE(vy.N == vx.N && vy.C == vx.C, "bilinear: shape mismatch");
+  const long long total = (long long)vy.N * vy.H * vy.W * (vx.C / 8);
+  if (!total) return PDAC_OK;
+  bilinear_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vx, vy, make_lin(vx.H, vy.H, align_corners),
+                                                                          make_lin(vx.W, vy.W, align_corners));
+  PDAC_LAUNCH_CHECK("bilinear_fwd");
+  return PDAC_OK;
+}
+extern "C" int pdac_bilinear_bwd(const PdacView* dy, int align_corners, const PdacView* dx, void* stream) {
+  V4 vdy, vdx;
+  PDAC_TRY(to_v4(dy, &vdy, "dy"));
+  PDAC_TRY(to_v4(dx, &vdx, "dx"));
+  PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C, "bilinear bwd: shape mismatch");
+  const long long total = (long long)vdx.N * vdx.H * vdx.W * (vdx.C / 8);
+  if (!total) return PDAC_OK;
+  bilinear_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(
+      vdy, vdx, make_lin(vdx.H, vdy.H, align_corners), make_lin(vdx.W, vdy.W, align_corners));
+  PDAC_LAUNCH_CHECK("bilinear_bwd");
+  return PDAC_OK;
+}
+extern "C" int pdac_bilinear_head_fwd(const PdacView* x, int C_used, int align_corners, float* out, int Ho, int Wo,
+                                      void* stream) {
+  V4 vx;
+  PDAC_TRY(to_v4(x, &vx, "x"));
+  PDAC_REQUIRE(out && C_used >= 1 && C_used <= vx.C && Ho > 0 && Wo > 0, "bilinear head: bad arguments");
+  const long long total = (long long)vx.N * C_used * Ho * Wo;
+  if (!total) return PDAC_OK;
+  bilinear_head_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(
+      vx, C_used, out, Ho, Wo, make_lin(vx.H, Ho, align_corners), make_lin(vx.W, Wo, align_corners));
+  PDAC_LAUNCH_CHECK("bilinear_head_fwd");
+  return PDAC_OK;
+}
+extern "C" int pdac_bilinear_head_bwd(const float* g, int C_used, int Ho, int Wo, int align_corners, const PdacView* dx,
+                                      void* stream) {
+  V4 vdx;
+  PDAC_TRY(to_v4(dx, &vdx, "dx"));
+  PDAC_REQUIRE(g && C_used >= 1 && C_used <= vdx.C, "bilinear head bwd: bad arguments");
+  const long long total = (long long)vdx.N * vdx.H * vdx.W;
+  if (!total) return PDAC_OK;
+  bilinear_head_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(
+      g, C_used, Ho, Wo, vdx, make_lin(vdx.H, Ho, align_corners), make_lin(vdx.W, Wo, align_corners));
+  PDAC_LAUNCH_CHECK("bilinear_head_bwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_adaptive_avgpool_fwd(const PdacView* x, const PdacView* y, void* stream) {
+  V4 vx, vy;
+  PDAC_TRY(to_v4(x, &vx, "x"));
+  PDAC_TRY(to_v4(y, &vy, "y"));
+  PDAC_REQUIRE(vy.N == vx.N && vy.C == vx.C, "adaptive_avgpool: shape mismatch");
+  const long long total = (long long)vy.N * vy.H * vy.W * (vx.C / 8);
+  if (!total) return PDAC_OK;
+  adaptive_avgpool_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vx, vy);
+  PDAC_LAUNCH_CHECK("adaptive_avgpool_fwd");
+  return PDAC_OK;
+}
+extern "C" int pdac_adaptive_avgpool_bwd(const PdacView* dy, const PdacView* dx, void* stream) {
+  V4 vdy, vdx;
+  PDAC_TRY(to_v4(dy, &vdy, "dy"));
+  PDAC_TRY(to_v4(dx, &vdx, "dx"));
+  PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C, "adaptive_avgpool bwd: shape mismatch");
+  const long long total = (long long)vdx.N * vdx.H * vdx.W * (vdx.C / 8);
+  if (!total) return PDAC_OK;
+  adaptive_avgpool_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vdy, vdx);
+  PDAC_LAUNCH_CHECK("adaptive_avgpool_bwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_add(const PdacView* a, const PdacView* b, int relu, const PdacView* y, void* stream) {
+  V4 va, vb, vy;
+  PDAC_TRY(to_v4(a, &va, "a"));
+  PDAC_TRY(to_v4(b, &vb, "b"));
+  PDAC_TRY(to_v4(y, &vy, "y"));
+  PDAC_REQUIRE(va.N == vy.N && va.H == vy.H && va.W == vy.W && va.C == vy.C && vb.N == vy.N && vb.H == vy.H &&
+                   vb.W == vy.W && vb.C == vy.C,
+               "add: shape mismatch");
+  const long long total = (long long)vy.N * vy.H * vy.W * (vy.C / 8);
+  if (!total) return PDAC_OK;
+  add_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(va, vb, vy, relu);
+  PDAC_LAUNCH_CHECK("add");
+  return PDAC_OK;
+}

@@ -1,0 +1,477 @@
+"""Thin torch-tensor wrappers over the C ABI (include/pdac_b200.h). PyTorch is used for device memory and streams
+only; every function here launches hand-written sm_100a kernels from libpdac_b200.so and raises if a tensor is not
+on a CUDA device (no CPU fallback).
+
+Activations are NHWC bf16 tensors of shape (N, H, W, C) whose last stride is 1 (channel slices are fine).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import PdacConv, PdacTapConv, PdacView, call
+
+BF16 = torch.bfloat16
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(t, what="tensor"):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f"pdac_b200: {what} must be a CUDA tensor (there is no CPU fallback)")
+
+
+def view(t):
+    """PdacView of an (N,H,W,C) bf16 tensor."""
+    _need_cuda(t, "activation")
+    if t.dtype != BF16 or t.dim() != 4 or (t.shape[3] > 1 and t.stride(3) != 1):
+        raise RuntimeError(f"pdac_b200: activation must be NHWC bf16 with unit channel stride, got {t.dtype} "
+                           f"{tuple(t.shape)} strides {t.stride()}")
+    return PdacView(t.data_ptr(), t.shape[0], t.shape[1], t.shape[2], t.shape[3], t.stride(0), t.stride(1),
+                    t.stride(2))
+
+
+def _vp(t):
+    return C.byref(view(t)) if t is not None else None
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    _need_cuda(t)
+    return C.c_void_p(t.data_ptr())
+
+
+def wrows_for(c):
+    """Rows per tap of a packed weight matrix whose row dimension has `c` used channels (matches the kernel's N tile)."""
+    return ((c + 15) // 16) * 16 if c <= 128 else ((c + 127) // 128) * 128
+
+
+def pad16(c):
+    return ((c + 15) // 16) * 16
+
+
+def empty_act(n, h, w, c, device):
+    return torch.empty((n, h, w, c), dtype=BF16, device=device)
+
+
+# ------------------------------------------------------------------------------------------------ convolutions
+def _conv_struct(R, S, stride, pad, dil, relu, wrows):
+    return PdacConv(R, S, stride, pad, dil, int(bool(relu)), wrows, 0)
+
+
+def conv_out_hw(h, w, R, S, stride, pad, dil):
+    return ((h + 2 * pad - dil * (R - 1) - 1) // stride + 1, (w + 2 * pad - dil * (S - 1) - 1) // stride + 1)
+
+
+def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=None, addend=None, stats=None,
+               out=None):
+    """out = [relu](conv(cat(srcs), w) + bias + addend); optional BN statistics (fp32 [2, cout], pre-zeroed)."""
+    x0 = srcs[0]
+    ho, wo = conv_out_hw(x0.shape[1], x0.shape[2], R, S, stride, pad, dil)
+    if out is None:
+        out = empty_act(x0.shape[0], ho, wo, cout, x0.device)
+    ktot = sum(s.shape[3] for s in srcs)
+    wrows = wp.shape[0] // (R * S)
+    assert wp.dtype == BF16 and wp.is_contiguous() and wp.shape[1] == ktot, (wp.shape, ktot)
+    cv = _conv_struct(R, S, stride, pad, dil, relu, wrows)
+    views = (PdacView * len(srcs))(*[view(s) for s in srcs])
+    call("pdac_conv2d_fwd", C.byref(cv), len(srcs), views, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
+         _stream())
+    return out
+
+
+def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None, out=None):
+    """dx (N, H, W, cin) = data gradient of the conv; `addend` (same shape as dx) is added (may alias `out`)."""
+    if out is None:
+        out = empty_act(dy.shape[0], in_hw[0], in_hw[1], cin, dy.device)
+    wrows = wpt.shape[0] // (R * S)
+    assert wpt.dtype == BF16 and wpt.is_contiguous() and wpt.shape[1] == dy.shape[3]
+    cv = _conv_struct(R, S, stride, pad, dil, False, wrows)
+    call("pdac_conv2d_dgrad", C.byref(cv), _vp(dy), _ptr(wpt), _vp(addend), _vp(out), _stream())
+    return out
+
+
+def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None):
+    """dw fp32 [R*S, dy.C, sum(src.C)] (accumulated into `out` if given, which must be pre-zeroed)."""
+    ktot = sum(s.shape[3] for s in srcs)
+    if out is None:
+        out = torch.zeros((R * S, dy.shape[3], ktot), dtype=torch.float32, device=dy.device)
+    cv = _conv_struct(R, S, stride, pad, dil, False, 0)
+    views = (PdacView * len(srcs))(*[view(s) for s in srcs])
+    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), _stream())
+    return out
+
+
+def convt2x2_fwd(x, wp, cout, bias=None, relu=False, out=None):
+    if out is None:
+        out = empty_act(x.shape[0], 2 * x.shape[1], 2 * x.shape[2], cout, x.device)
+    wrows = wp.shape[0] // 4
+    call("pdac_convt2x2_fwd", _vp(x), _ptr(wp), wrows, _ptr(bias), int(bool(relu)), _vp(out), _stream())
+    return out
+
+
+def convt2x2_dgrad(dy, wpt, cin, out=None):
+    if out is None:
+        out = empty_act(dy.shape[0], dy.shape[1] // 2, dy.shape[2] // 2, cin, dy.device)
+    wrows = wpt.shape[0] // 4
+    call("pdac_convt2x2_dgrad", _vp(dy), _ptr(wpt), wrows, _vp(out), _stream())
+    return out
+
+
+def convt2x2_wgrad(x, dy, out=None):
+    """dw fp32 [4, Cout, Cin]."""
+    if out is None:
+        out = torch.zeros((4, dy.shape[3], x.shape[3]), dtype=torch.float32, device=x.device)
+    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), _stream())
+    return out
+
+
+def _tapconv(taps, n_cat, wrows, relu):
+    tc = PdacTapConv()
+    tc.n_taps, tc.n_cat, tc.wrows, tc.relu = len(taps), n_cat, wrows, int(bool(relu))
+    for i, (src, dh, dw) in enumerate(taps):
+        tc.taps[i].src, tc.taps[i].dh, tc.taps[i].dw = src, dh, dw
+    return tc
+
+
+def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=None, stats=None):
+    """Generalised tap convolution (pdac_tapconv_fwd): taps = [(first view index, dh, dw), ...]."""
+    tc = _tapconv(taps, n_cat, wp.shape[0] // len(taps), relu)
+    vs = (PdacView * len(views))(*[view(v) for v in views])
+    call("pdac_tapconv_fwd", C.byref(tc), len(views), vs, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
+         _stream())
+    return out
+
+
+def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1):
+    tc = _tapconv(taps, n_cat, 0, False)
+    vs = (PdacView * len(views))(*[view(v) for v in views])
+    call("pdac_tapconv_wgrad", C.byref(tc), len(views), vs, _vp(dy), _ptr(dw), tap_stride, a_stride, b_stride, _stream())
+    return dw
+
+
+# The ResNet stem (7x7, stride 2, pad 3; torchvision resnet.py:197) as a 4x4 stride-1 convolution over the
+# space-to-depth input of stem_prep_*: tap (a, b) reads z[oh + a - 2, ow + b - 2].
+STEM_TAPS = [(0, a - 2, b - 2) for a in range(4) for b in range(4)]
+
+
+def stem_conv_fwd(z, wp, cout, stats=None, out=None):
+    if out is None:
+        out = empty_act(z.shape[0], z.shape[1], z.shape[2], cout, z.device)
+    return tapconv_fwd([z], STEM_TAPS, wp, out, stats=stats)
+
+
+def stem_conv_wgrad(z, dy, out=None):
+    """fp32 [16, Cout, 16] in the packed space-to-depth form (see unpack_stem_wgrad)."""
+    if out is None:
+        out = torch.zeros((16, dy.shape[3], 16), dtype=torch.float32, device=z.device)
+    return tapconv_wgrad([z], STEM_TAPS, dy, out, dy.shape[3] * 16, 1, 16)
+
+
+# ------------------------------------------------------------------------------------------------ packing / layout
+def pack_conv_weight(w, want_fwd=True, want_dgrad=True, stride=1, pad=0, cout_pad=None, wp_f=None, wp_t=None):
+    """fp32 [O, I, R, S] -> (wp_f bf16 [R*S*wrows_f, I], wp_t bf16 [R*S*wrows_t, O_pad])."""
+    _need_cuda(w, "weight")
+    w = w.detach()
+    assert w.dtype == torch.float32 and w.is_contiguous()
+    O, I, R, S = w.shape
+    opad = cout_pad or O
+    wrows_f, wrows_t = wrows_for(opad), wrows_for(I)
+    if want_fwd and wp_f is None:
+        wp_f = torch.empty((R * S * wrows_f, I), dtype=BF16, device=w.device)
+    if want_dgrad and wp_t is None:
+        wp_t = torch.empty((R * S * wrows_t, opad), dtype=BF16, device=w.device)
+    call("pdac_pack_conv_weight", _ptr(w), O, I, R, S, wrows_f, I, _ptr(wp_f) if want_fwd else None, wrows_t, opad,
+         _ptr(wp_t) if want_dgrad else None, pad if stride == 2 else -1, _stream())
+    return wp_f, wp_t
+
+
+def pack_convt_weight(w, wp_f=None, wp_t=None):
+    """nn.ConvTranspose2d weight fp32 [Cin, Cout, 2, 2] -> (forward matrix [4*wrows(Cout), Cin], dgrad matrix
+    [4*wrows(Cin), Cout])."""
+    _need_cuda(w, "weight")
+    w = w.detach()
+    cin, cout = w.shape[0], w.shape[1]
+    wr_f, wr_t = wrows_for(cout), wrows_for(cin)
+    if wp_f is None:
+        wp_f = torch.empty((4 * wr_f, cin), dtype=BF16, device=w.device)
+    if wp_t is None:
+        wp_t = torch.empty((4 * wr_t, cout), dtype=BF16, device=w.device)
+    # with O=Cin, I=Cout the "forward" packing [t][o=cin][i=cout] is the dgrad matrix and vice versa
+    call("pdac_pack_conv_weight", _ptr(w), cin, cout, 2, 2, wr_t, cout, _ptr(wp_t), wr_f, cin, _ptr(wp_f), -1,
+         _stream())
+    return wp_f, wp_t
+
+
+def pack_stem_weight(w, wp=None):
+    _need_cuda(w, "weight")
+    w = w.detach()
+    assert tuple(w.shape[1:]) == (3, 7, 7) and w.is_contiguous()
+    O = w.shape[0]
+    if wp is None:
+        wp = torch.empty((16 * wrows_for(O), 16), dtype=BF16, device=w.device)
+    assert wrows_for(O) == O, "stem Cout must be a multiple of 16"
+    call("pdac_pack_stem_weight", _ptr(w), O, _ptr(wp), _stream())
+    return wp
+
+
+def unpack_stem_wgrad(dwp, O, out=None):
+    if out is None:
+        out = torch.empty((O, 3, 7, 7), dtype=torch.float32, device=dwp.device)
+    call("pdac_unpack_stem_wgrad", _ptr(dwp), O, _ptr(out), _stream())
+    return out
+
+
+def nchw_to_nhwc(x, c_pad=None, out=None):
+    _need_cuda(x, "input")
+    x = x.contiguous()
+    assert x.dtype == torch.float32
+    n, c, h, w = x.shape
+    if out is None:
+        out = empty_act(n, h, w, c_pad or c, x.device)
+    call("pdac_nchw_f32_to_nhwc_bf16", _ptr(x), n, c, h, w, _vp(out), _stream())
+    return out
+
+
+def nhwc_to_nchw(x, c_used=None, out=None):
+    c_used = c_used or x.shape[3]
+    if out is None:
+        out = torch.empty((x.shape[0], c_used, x.shape[1], x.shape[2]), dtype=torch.float32, device=x.device)
+    call("pdac_nhwc_bf16_to_nchw_f32", _vp(x), c_used, _ptr(out), _stream())
+    return out
+
+
+def stem_prep_f32(x, out=None):
+    _need_cuda(x, "input")
+    x = x.contiguous()
+    assert x.dtype == torch.float32 and x.shape[1] == 3
+    n, _, h, w = x.shape
+    if out is None:
+        out = empty_act(n, h // 2, w // 2, 16, x.device)
+    call("pdac_stem_prep_f32", _ptr(x), n, h, w, _ptr(out), _stream())
+    return out
+
+
+IMAGENET_MEAN = (0.485, 0.456, 0.406)
+IMAGENET_STD = (0.229, 0.224, 0.225)
+
+
+def stem_prep_u8(img, mask=None, aug=None, mean=IMAGENET_MEAN, std=IMAGENET_STD, out=None, mask_out=None):
+    """uint8 (N,H,W,3) patches (+ optional uint8 (N,H,W) masks, int32 (N,) augmentation codes) -> stem input."""
+    _need_cuda(img, "image batch")
+    assert img.dtype == torch.uint8 and img.is_contiguous() and img.shape[3] == 3
+    n, h, w, _ = img.shape
+    if out is None:
+        out = empty_act(n, h // 2, w // 2, 16, img.device)
+    if mask is not None and mask_out is None:
+        mask_out = torch.empty_like(mask)
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*std)
+    call("pdac_stem_prep_u8", _ptr(img), _ptr(mask), _ptr(aug), n, h, w, m, s, _ptr(out), _ptr(mask_out), _stream())
+    return out, mask_out
+
+
+# ------------------------------------------------------------------------------------------------ BN / elementwise
+def bn_prepare(stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd):
+    c = scale_shift.shape[-1]
+    call("pdac_bn_prepare", _ptr(stats), float(count), _ptr(gamma), _ptr(beta), eps, momentum, int(bool(train)),
+         _ptr(running_mean), _ptr(running_var), _ptr(scale_shift), _ptr(mean_invstd), c, _stream())
+
+
+def scale_shift_act(x, scale_shift=None, residual=None, relu=False, out=None):
+    if out is None:
+        out = torch.empty_like(x)
+    call("pdac_scale_shift_act", _vp(x), _ptr(scale_shift), _vp(residual), int(bool(relu)), _vp(out), _stream())
+    return out
+
+
+def bn_bwd_reduce(dy, y, x, mean_invstd, sums):
+    call("pdac_bn_bwd_reduce", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(sums), _stream())
+    return sums
+
+
+def bn_bwd_apply(dy, y, x, mean_invstd, gamma, sums, count, train, dx=None, dz_out=None, dgamma=None, dbeta=None):
+    if dx is None:
+        dx = torch.empty_like(dy)
+    call("pdac_bn_bwd_apply", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(gamma), _ptr(sums), float(count),
+         int(bool(train)), _vp(dx), _vp(dz_out), _ptr(dgamma), _ptr(dbeta), _stream())
+    return dx
+
+
+def relu_bwd_bias(dy, y=None, dz=None, dbias=None):
+    call("pdac_relu_bwd_bias", _vp(dy), _vp(y), _vp(dz), _ptr(dbias), _stream())
+    return dz
+
+
+def add(a, b, relu=False, out=None):
+    if out is None:
+        out = torch.empty_like(a)
+    call("pdac_add", _vp(a), _vp(b), int(bool(relu)), _vp(out), _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ pooling / resize
+def maxpool_fwd(x, want_idx=True):
+    n, h, w, c = x.shape
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = empty_act(n, ho, wo, c, x.device)
+    idx = torch.empty((n, ho, wo, c), dtype=torch.uint8, device=x.device) if want_idx else None
+    call("pdac_maxpool3x3s2_fwd", _vp(x), _vp(y), _ptr(idx), _stream())
+    return y, idx
+
+
+def maxpool_bwd(dy, idx, in_hw):
+    dx = empty_act(dy.shape[0], in_hw[0], in_hw[1], dy.shape[3], dy.device)
+    call("pdac_maxpool3x3s2_bwd", _vp(dy), _ptr(idx), _vp(dx), _stream())
+    return dx
+
+
+def upsample_nearest2x_fwd(x, out=None):
+    if out is None:
+        out = empty_act(x.shape[0], 2 * x.shape[1], 2 * x.shape[2], x.shape[3], x.device)
+    call("pdac_upsample_nearest2x_fwd", _vp(x), _vp(out), _stream())
+    return out
+
+
+def upsample_nearest2x_bwd(dy, addend=None, out=None):
+    if out is None:
+        out = empty_act(dy.shape[0], dy.shape[1] // 2, dy.shape[2] // 2, dy.shape[3], dy.device)
+    call("pdac_upsample_nearest2x_bwd", _vp(dy), _vp(addend), _vp(out), _stream())
+    return out
+
+
+def bilinear_fwd(x, out_hw, align_corners, out=None):
+    if out is None:
+        out = empty_act(x.shape[0], out_hw[0], out_hw[1], x.shape[3], x.device)
+    call("pdac_bilinear_fwd", _vp(x), int(bool(align_corners)), _vp(out), _stream())
+    return out
+
+
+def bilinear_bwd(dy, in_hw, align_corners, out=None):
+    if out is None:
+        out = empty_act(dy.shape[0], in_hw[0], in_hw[1], dy.shape[3], dy.device)
+    call("pdac_bilinear_bwd", _vp(dy), int(bool(align_corners)), _vp(out), _stream())
+    return out
+
+
+def bilinear_head_fwd(x, c_used, out_hw, align_corners, out=None):
+    if out is None:
+        out = torch.empty((x.shape[0], c_used, out_hw[0], out_hw[1]), dtype=torch.float32, device=x.device)
+    call("pdac_bilinear_head_fwd", _vp(x), c_used, int(bool(align_corners)), _ptr(out), out_hw[0], out_hw[1], _stream())
+    return out
+
+
+def bilinear_head_bwd(g, in_shape, align_corners, out=None):
+    """g: fp32 (N, Cu, Ho, Wo) -> dx bf16 (N, h, w, Cpad) with in_shape = (h, w, Cpad)."""
+    _need_cuda(g, "gradient")
+    g = g.contiguous()
+    n, cu, ho, wo = g.shape
+    if out is None:
+        out = empty_act(n, in_shape[0], in_shape[1], in_shape[2], g.device)
+    call("pdac_bilinear_head_bwd", _ptr(g), cu, ho, wo, int(bool(align_corners)), _vp(out), _stream())
+    return out
+
+
+def adaptive_avgpool_fwd(x, out_hw):
+    y = empty_act(x.shape[0], out_hw[0], out_hw[1], x.shape[3], x.device)
+    call("pdac_adaptive_avgpool_fwd", _vp(x), _vp(y), _stream())
+    return y
+
+
+def adaptive_avgpool_bwd(dy, in_hw):
+    dx = empty_act(dy.shape[0], in_hw[0], in_hw[1], dy.shape[3], dy.device)
+    call("pdac_adaptive_avgpool_bwd", _vp(dy), _vp(dx), _stream())
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------ loss / metric
+def _tgt(t):
+    _need_cuda(t, "target")
+    if t.dtype == torch.float32:
+        return t.contiguous(), 0
+    if t.dtype in (torch.uint8, torch.bool):
+        return t.contiguous().view(torch.uint8), 1
+    raise RuntimeError(f"pdac_b200: targets must be float32 or uint8, got {t.dtype}")
+
+
+def dice_fwd(logits, targets, smooth=1e-6):
+    """-> (loss fp32 scalar tensor, sums fp64[3] saved for backward)."""
+    _need_cuda(logits, "logits")
+    logits = logits.contiguous()
+    assert logits.dtype == torch.float32
+    t, kind = _tgt(targets)
+    assert t.numel() == logits.numel(), "DiceLoss: inputs and targets must have the same number of elements"
+    sums = torch.empty(3, dtype=torch.float64, device=logits.device)
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    call("pdac_dice_fwd", _ptr(logits), _ptr(t), kind, logits.numel(), _ptr(sums), smooth, _ptr(loss), _stream())
+    return loss, sums
+
+
+def dice_bwd(logits, targets, sums, grad_out, smooth=1e-6):
+    logits = logits.contiguous()
+    t, kind = _tgt(targets)
+    g = torch.empty_like(logits)
+    go = grad_out.contiguous().to(torch.float32) if grad_out is not None else None
+    call("pdac_dice_bwd", _ptr(logits), _ptr(t), kind, logits.numel(), _ptr(sums), smooth, _ptr(go), _ptr(g), _stream())
+    return g
+
+
+def sigmoid_mask(logits, as_uint8=False):
+    _need_cuda(logits, "logits")
+    logits = logits.contiguous()
+    assert logits.dtype == torch.float32
+    out = torch.empty(logits.shape, dtype=torch.uint8 if as_uint8 else torch.float32, device=logits.device)
+    call("pdac_sigmoid_mask", _ptr(logits), logits.numel(), None if as_uint8 else _ptr(out),
+         _ptr(out) if as_uint8 else None, _stream())
+    return out
+
+
+def dice_score(pred, target, smooth=1e-6, pred_is_logits=False):
+    _need_cuda(pred, "pred")
+    pred = pred.contiguous()
+    if pred.dtype == torch.float32:
+        kind = 1 if pred_is_logits else 0
+    elif pred.dtype in (torch.uint8, torch.bool):
+        pred, kind = pred.view(torch.uint8), 2
+    else:
+        raise RuntimeError(f"pdac_b200: pred must be float32 or uint8, got {pred.dtype}")
+    t, tk = _tgt(target)
+    assert t.numel() == pred.numel()
+    counts = torch.empty(3, dtype=torch.int64, device=pred.device)
+    score = torch.empty((), dtype=torch.float32, device=pred.device)
+    call("pdac_dice_score", _ptr(pred), kind, _ptr(t), tk, pred.numel(), _ptr(counts), smooth, _ptr(score), _stream())
+    return score, counts
+
+
+def argmax_nchw(logits):
+    _need_cuda(logits, "logits")
+    logits = logits.contiguous()
+    n, c, h, w = logits.shape
+    out = torch.empty((n, h, w), dtype=torch.uint8, device=logits.device)
+    call("pdac_argmax_nchw", _ptr(logits), n, c, h * w, _ptr(out), _stream())
+    return out
+
+
+def stitch_tiles(tiles, rows, cols, slide, row0=0):
+    """tiles uint8 (T, th, tw); rows/cols int32 (T,) grid coordinates; slide uint8 (Hs, Ws) band starting at row0."""
+    _need_cuda(tiles, "tiles")
+    assert tiles.dtype == torch.uint8 and tiles.is_contiguous() and slide.dtype == torch.uint8 and slide.is_contiguous()
+    assert rows.dtype == torch.int32 and cols.dtype == torch.int32
+    t, th, tw = tiles.shape
+    call("pdac_stitch_tiles", _ptr(tiles), _ptr(rows), _ptr(cols), t, th, tw, _ptr(slide), slide.shape[0],
+         slide.shape[1], row0, _stream())
+    return slide
+
+
+def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0):
+    call("pdac_adam_step", _ptr(params), _ptr(grads), _ptr(exp_avg), _ptr(exp_avg_sq), params.numel(), lr, beta1, beta2,
+         eps, step, grad_scale, _stream())
+
+
+def check_device_flag():
+    call("pdac_check_device_flag", _stream())

@@ -1,0 +1,205 @@
+"""Parity of the tcgen05 implicit-GEMM convolutions (through the C ABI) against torch fp32 on bf16-rounded inputs.
+
+Tolerance: inputs/weights are exactly representable in bf16, accumulation is fp32, so the only error is the final
+bf16 rounding of the output (relative 2^-8) plus fp32 summation-order noise.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _rnd(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(torch.bfloat16).to(DEV)
+
+
+def _nhwc(x_nchw_bf16):
+    return x_nchw_bf16.permute(0, 2, 3, 1).contiguous()
+
+
+def _close(got, ref, what, rel=2.0 ** -7):
+    got, ref = got.float(), ref.float()
+    err = (got - ref).abs().max().item()
+    tol = rel * ref.abs().max().item() + 1e-6
+    assert err <= tol, f"{what}: max abs err {err:.4g} > tol {tol:.4g} (ref max {ref.abs().max().item():.4g})"
+
+
+FWD_CASES = [
+    # (N, H, W, [cins], cout, R, stride, pad, dil, relu, bias, addend)
+    (2, 16, 16, [64], 64, 3, 1, 1, 1, False, False, False),
+    (2, 32, 32, [32], 16, 3, 1, 1, 1, False, False, False),
+    (1, 32, 32, [16], 16, 3, 1, 1, 1, True, False, False),
+    (2, 16, 16, [128], 128, 3, 1, 1, 1, True, True, False),
+    (2, 16, 16, [64, 64], 64, 3, 1, 1, 1, False, True, True),
+    (2, 16, 16, [128, 64], 64, 3, 1, 1, 1, False, False, False),
+    (2, 16, 16, [64], 256, 1, 1, 0, 1, False, False, False),
+    (2, 32, 32, [64], 128, 3, 2, 1, 1, False, False, False),
+    (2, 32, 32, [64], 128, 1, 2, 0, 1, False, False, False),
+    (2, 16, 16, [64], 64, 3, 1, 2, 2, False, False, False),
+    (3, 10, 12, [64], 32, 3, 1, 1, 1, False, False, False),
+    (4, 8, 8, [128], 64, 3, 1, 1, 1, False, False, False),
+    (2, 2, 2, [128], 32, 1, 1, 0, 1, True, True, False),
+    (2, 3, 3, [128], 32, 1, 1, 0, 1, False, False, False),
+    (2, 16, 16, [16], 1, 3, 1, 1, 1, False, True, False),
+    (2, 16, 16, [304], 256, 1, 1, 0, 1, False, False, False),
+    (1, 16, 16, [512], 512, 3, 1, 1, 1, False, False, False),
+    (2, 16, 16, [64], 48, 1, 1, 0, 1, False, False, False),
+]
+
+
+@pytest.mark.parametrize("case", FWD_CASES, ids=[str(c) for c in FWD_CASES])
+def test_conv_fwd(case):
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W, cins, cout, R, stride, pad, dil, relu, use_bias, use_add = case
+    xs = [_rnd(N, c, H, W, seed=i + 1) for i, c in enumerate(cins)]
+    w = _rnd(cout, sum(cins), R, R, scale=0.05, seed=11)
+    bias = (torch.randn(cout, device=DEV) if use_bias else None)
+    ref = F.conv2d(torch.cat(xs, 1).float(), w.float(), bias, stride=stride, padding=pad, dilation=dil)
+    addend = None
+    if use_add:
+        addend = _rnd(*ref.shape, seed=21)
+        ref = ref + addend.float()
+    if relu:
+        ref = ref.relu()
+    cpad = ops.pad16(cout) if cout % 8 else cout
+    wp, _ = ops.pack_conv_weight(w.float().contiguous(), want_dgrad=False, cout_pad=cpad)
+    stats = torch.zeros(2, cpad, device=DEV)
+    bias_p = None
+    if bias is not None:
+        bias_p = torch.zeros(cpad, device=DEV)
+        bias_p[:cout] = bias
+    out = ops.conv2d_fwd([_nhwc(x) for x in xs], wp, cpad, R, R, stride, pad, dil, relu=relu, bias=bias_p,
+                         addend=_nhwc(addend) if addend is not None else None, stats=stats)
+    ops.check_device_flag()
+    got = out.permute(0, 3, 1, 2)[:, :cout]
+    _close(got, ref, "conv fwd")
+    # BN statistics of the stored values
+    o32 = out.float()[..., :cout]
+    s_ref = o32.sum((0, 1, 2))
+    q_ref = (o32 * o32).sum((0, 1, 2))
+    assert torch.allclose(stats[0, :cout], s_ref, rtol=1e-3, atol=1e-2 * o32.abs().max().item() + 1e-3)
+    assert torch.allclose(stats[1, :cout], q_ref, rtol=1e-3, atol=1e-3)
+
+
+DGRAD_CASES = [
+    # (N, H, W, cin, cout, R, stride, pad, dil, addend)
+    (2, 16, 16, 64, 64, 3, 1, 1, 1, False),
+    (2, 16, 16, 128, 64, 3, 1, 1, 1, True),
+    (2, 32, 32, 64, 128, 3, 2, 1, 1, False),
+    (2, 32, 32, 64, 128, 3, 2, 1, 1, True),
+    (2, 32, 32, 64, 128, 1, 2, 0, 1, False),
+    (2, 16, 16, 64, 64, 3, 1, 2, 2, False),
+    (2, 16, 16, 32, 16, 3, 1, 1, 1, False),
+    (2, 16, 16, 16, 1, 3, 1, 1, 1, False),
+    (2, 16, 16, 256, 64, 1, 1, 0, 1, False),
+]
+
+
+@pytest.mark.parametrize("case", DGRAD_CASES, ids=[str(c) for c in DGRAD_CASES])
+def test_conv_dgrad(case):
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W, cin, cout, R, stride, pad, dil, use_add = case
+    w = _rnd(cout, cin, R, R, scale=0.05, seed=3)
+    ho, wo = ops.conv_out_hw(H, W, R, R, stride, pad, dil)
+    dy = _rnd(N, cout, ho, wo, seed=4)
+    ref = torch.nn.grad.conv2d_input((N, cin, H, W), w.float(), dy.float(), stride=stride, padding=pad, dilation=dil)
+    addend = None
+    if use_add:
+        addend = _rnd(N, cin, H, W, seed=5)
+        ref = ref + addend.float()
+    cpad = ops.pad16(cout) if cout % 8 else cout
+    _, wpt = ops.pack_conv_weight(w.float().contiguous(), want_fwd=False, stride=stride, pad=pad, cout_pad=cpad)
+    dyp = torch.zeros(N, ho, wo, cpad, dtype=torch.bfloat16, device=DEV)
+    dyp[..., :cout] = _nhwc(dy)
+    dx = ops.conv2d_dgrad(dyp, wpt, cin, (H, W), R, R, stride, pad, dil,
+                          addend=_nhwc(addend) if addend is not None else None)
+    ops.check_device_flag()
+    _close(dx.permute(0, 3, 1, 2), ref, "conv dgrad")
+
+
+WGRAD_CASES = [
+    # (N, H, W, [cins], cout, R, stride, pad, dil)
+    (2, 16, 16, [64], 64, 3, 1, 1, 1),
+    (2, 32, 32, [32], 16, 3, 1, 1, 1),
+    (2, 32, 32, [16], 16, 3, 1, 1, 1),
+    (2, 16, 16, [128], 128, 3, 1, 1, 1),
+    (2, 16, 16, [256], 256, 3, 1, 1, 1),
+    (1, 16, 16, [64], 512, 3, 1, 1, 1),
+    (2, 16, 16, [128, 64], 64, 3, 1, 1, 1),
+    (2, 32, 32, [64], 128, 3, 2, 1, 1),
+    (2, 32, 32, [64], 128, 1, 2, 0, 1),
+    (2, 16, 16, [16], 1, 3, 1, 1, 1),
+    (3, 10, 12, [64], 32, 3, 1, 1, 1),
+    (2, 16, 16, [64], 48, 1, 1, 0, 1),
+    (4, 64, 64, [64], 64, 3, 1, 1, 1),
+]
+
+
+@pytest.mark.parametrize("case", WGRAD_CASES, ids=[str(c) for c in WGRAD_CASES])
+def test_conv_wgrad(case):
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W, cins, cout, R, stride, pad, dil = case
+    xs = [_rnd(N, c, H, W, seed=i + 1) for i, c in enumerate(cins)]
+    ho, wo = ops.conv_out_hw(H, W, R, R, stride, pad, dil)
+    dy = _rnd(N, cout, ho, wo, seed=7)
+    ref = torch.nn.grad.conv2d_weight(torch.cat(xs, 1).float(), (cout, sum(cins), R, R), dy.float(), stride=stride,
+                                      padding=pad, dilation=dil)
+    cpad = ops.pad16(cout) if cout % 16 else cout
+    dyp = torch.zeros(N, ho, wo, cpad, dtype=torch.bfloat16, device=DEV)
+    dyp[..., :cout] = _nhwc(dy)
+    dw = ops.conv2d_wgrad([_nhwc(x) for x in xs], dyp, R, R, stride, pad, dil)   # [RS, cpad, Ctot]
+    ops.check_device_flag()
+    got = dw.view(R, R, cpad, sum(cins)).permute(2, 3, 0, 1)[:cout]
+    err = (got - ref).abs().max().item()
+    tol = 1e-3 * ref.abs().max().item() + 1e-4
+    assert err <= tol, f"wgrad: max abs err {err:.4g} > {tol:.4g}"
+
+
+def test_convt2x2_all():
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W, cin, cout = 2, 16, 16, 128, 64
+    x = _rnd(N, cin, H, W, seed=1)
+    w = _rnd(cin, cout, 2, 2, scale=0.05, seed=2)
+    bias = torch.randn(cout, device=DEV)
+    ref = F.conv_transpose2d(x.float(), w.float(), bias, stride=2)
+    wp_f, wp_t = ops.pack_convt_weight(w.float().contiguous())
+    out = ops.convt2x2_fwd(_nhwc(x), wp_f, cout, bias=bias)
+    ops.check_device_flag()
+    _close(out.permute(0, 3, 1, 2), ref, "convT fwd")
+    dy = _rnd(N, cout, 2 * H, 2 * W, seed=3)
+    xr = x.float().requires_grad_(True)
+    wr = w.float().requires_grad_(True)
+    F.conv_transpose2d(xr, wr, None, stride=2).backward(dy.float())
+    dx = ops.convt2x2_dgrad(_nhwc(dy), wp_t, cin)
+    ops.check_device_flag()
+    _close(dx.permute(0, 3, 1, 2), xr.grad, "convT dgrad")
+    dw = ops.convt2x2_wgrad(_nhwc(x), _nhwc(dy))      # [4, Cout, Cin]
+    ops.check_device_flag()
+    got = dw.view(2, 2, cout, cin).permute(3, 2, 0, 1)
+    err = (got - wr.grad).abs().max().item()
+    assert err <= 1e-3 * wr.grad.abs().max().item() + 1e-4, f"convT wgrad err {err}"
+
+
+def test_stem_as_4x4_s2d():
+    """7x7 stride-2 stem == 4x4 stride-1 conv over the space-to-depth input (layout.cu packing)."""
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W = 2, 64, 64
+    x = _rnd(N, 3, H, W, seed=1)
+    w = _rnd(64, 3, 7, 7, scale=0.05, seed=2)
+    ref = F.conv2d(x.float(), w.float(), None, stride=2, padding=3)
+    z = ops.stem_prep_f32(x.float())
+    wp = ops.pack_stem_weight(w.float().contiguous())
+    out = ops.stem_conv_fwd(z, wp, 64)
+    ops.check_device_flag()
+    _close(out.permute(0, 3, 1, 2), ref, "stem fwd")
+    dy = _rnd(N, 64, H // 2, W // 2, seed=3)
+    ref_dw = torch.nn.grad.conv2d_weight(x.float(), (64, 3, 7, 7), dy.float(), stride=2, padding=3)
+    dwp = ops.stem_conv_wgrad(z, _nhwc(dy))
+    dw = ops.unpack_stem_wgrad(dwp, 64)
+    ops.check_device_flag()
+    err = (dw - ref_dw).abs().max().item()
+    assert err <= 1e-3 * ref_dw.abs().max().item() + 1e-4, f"stem wgrad err {err}"
