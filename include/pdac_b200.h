@@ -56,7 +56,7 @@ typedef struct PdacConv {
   int32_t dil;       /* dilation */
   int32_t relu;      /* fuse max(x,0) into the epilogue */
   int32_t wrows;     /* rows per tap in the packed weight matrix (>= rows used; lets a tap block be padded) */
-  int32_t reserved;
+  int32_t cout_valid; /* wgrad only: real channels of a channel-padded dY (0 = all of dy->C) */
 } PdacConv;
 
 int pdac_version(void);
@@ -87,9 +87,10 @@ typedef struct PdacTapConv {
 int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
                      const float* bias, const PdacView* addend, const PdacView* out, float* stats, void* stream);
 /* dw[t*tap_stride + a*a_stride + b*b_stride] += sum_pixels cat(views)[p + off_t, a] * dy[p, b]  (fp32 atomics;
- * caller zeroes dw). a runs over the concatenated source channels, b over dy->C. */
+ * caller zeroes dw). a runs over the concatenated source channels, b over the first b_valid channels of dy
+ * (0 = all; dy may be channel-padded). */
 int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy, float* dw,
-                       int64_t tap_stride, int64_t a_stride, int64_t b_stride, void* stream);
+                       int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, void* stream);
 
 /* nn.Conv2d forward: out = [relu](conv(cat(src[0..n_src-1]), w) + bias + addend). w_packed: [R*S*wrows][Ctot] with
  * row (r*S+s)*wrows + cout. */
@@ -100,15 +101,17 @@ int pdac_conv2d_fwd(const PdacConv* cv, int n_src, const PdacView* src, const vo
  * stride 2 the four output parity classes are separate launches; classes no tap reaches get addend or zero. */
 int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const void* w_packed_t, const PdacView* addend,
                       const PdacView* dx, void* stream);
-/* dw[(r*S+s)][cout][cin] += sum_pixels dy[p,cout] * cat(src)[p*stride + off, cin]; fp32 [R*S][Cout][Ctot]. */
+/* dw += sum_pixels dy[p,cout] * cat(src)[p*stride + off, cin]. dw_layout 0: fp32 [R*S][Cout][Ctot];
+ * dw_layout 1: the nn.Conv2d state_dict layout [cout_valid][Ctot][R][S] (gradients land where autograd wants them). */
 int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,
-                      void* stream);
+                      int dw_layout, void* stream);
 /* nn.ConvTranspose2d(k=2, s=2): out[2i+a,2j+b,:] = W[a,b] x[i,j,:] + bias. w_packed: [4*wrows][Cin], row
- * (a*2+b)*wrows + cout; w_packed_t: [4*wrows][Cout], row (a*2+b)*wrows + cin; dw: fp32 [4][Cout][Cin]. */
+ * (a*2+b)*wrows + cout; w_packed_t: [4*wrows][Cout], row (a*2+b)*wrows + cin. */
 int pdac_convt2x2_fwd(const PdacView* x, const void* w_packed, int wrows, const float* bias, int relu,
                       const PdacView* out, void* stream);
 int pdac_convt2x2_dgrad(const PdacView* dy, const void* w_packed_t, int wrows, const PdacView* dx, void* stream);
-int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, void* stream);
+/* dw_layout 0: [4][Cout][Cin]; 1: the nn.ConvTranspose2d state_dict layout [Cin][Cout][2][2]. */
+int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, int dw_layout, void* stream);
 
 /* ---- layout / packing (layout.cu) --------------------------------------------------------------------------- */
 /* x: fp32 NCHW (N,C,H,W) -> out: NHWC bf16 view with out->C >= C (extra channels zeroed). */
@@ -136,10 +139,11 @@ int pdac_unpack_stem_wgrad(const float* dwp, int O, float* dw, void* stream);
 /* ---- BatchNorm / ReLU / residual (bn.cu) -------------------------------------------------------------------- */
 /* stats: fp32 [2][C] sum / sum-of-squares over `count` values per channel (from the conv epilogue). Writes
  * scale_shift [2][C] (y = x*scale + shift), mean_invstd [2][C] (saved for backward) and, when training, updates
- * running_mean/var in place (momentum; unbiased variance). train=0 derives everything from the running stats. */
+ * running_mean/var in place (momentum; unbiased variance) and increments the int64 num_batches_tracked scalar (may be
+ * NULL). train=0 derives everything from the running stats. */
 int pdac_bn_prepare(const float* stats, double count, const float* gamma, const float* beta, float eps, float momentum,
-                    int train, float* running_mean, float* running_var, float* scale_shift, float* mean_invstd, int C,
-                    void* stream);
+                    int train, float* running_mean, float* running_var, long long* num_batches_tracked,
+                    float* scale_shift, float* mean_invstd, int C, void* stream);
 /* y = [relu](x*scale[c] + shift[c] + residual); scale_shift / residual may be NULL. */
 int pdac_scale_shift_act(const PdacView* x, const float* scale_shift, const PdacView* residual, int relu,
                          const PdacView* y, void* stream);

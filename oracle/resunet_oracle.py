@@ -92,6 +92,27 @@ def make_state(num_classes: int = 1, seed: int = 41, randomize_bn: bool = True) 
     return sd
 
 
+class _RoundBF16(torch.autograd.Function):
+    """x -> bf16 -> fp32 with a straight-through gradient that is itself rounded to bf16: emulates WHERE the product
+    stores activations / gradients in bf16 while keeping every multiply-add in fp32 (quantisation-aware oracle)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(torch.float32)
+
+
+def round_bf16(x):
+    return _RoundBF16.apply(x)
+
+
+def _id(x):
+    return x
+
+
 def _bn(x, sd, p, training):
     if training:
         sd[p + ".num_batches_tracked"] += 1
@@ -99,41 +120,46 @@ def _bn(x, sd, p, training):
                         training, BN_MOMENTUM, BN_EPS)
 
 
-def _basic_block(x, sd, p, stride, training):
-    out = F.conv2d(x, sd[p + ".conv1.weight"], None, stride=stride, padding=1)
-    out = F.relu(_bn(out, sd, p + ".bn1", training))
-    out = F.conv2d(out, sd[p + ".conv2.weight"], None, stride=1, padding=1)
+def _basic_block(x, sd, p, stride, training, q=_id):
+    out = q(F.conv2d(x, q(sd[p + ".conv1.weight"]), None, stride=stride, padding=1))
+    out = q(F.relu(_bn(out, sd, p + ".bn1", training)))
+    out = q(F.conv2d(out, q(sd[p + ".conv2.weight"]), None, stride=1, padding=1))
     out = _bn(out, sd, p + ".bn2", training)
     if (p + ".downsample.0.weight") in sd:
-        x = _bn(F.conv2d(x, sd[p + ".downsample.0.weight"], None, stride=stride), sd, p + ".downsample.1", training)
-    return F.relu(out + x)
+        x = q(F.conv2d(x, q(sd[p + ".downsample.0.weight"]), None, stride=stride))
+        x = q(_bn(x, sd, p + ".downsample.1", training))
+    return q(F.relu(out + x))
 
 
-def encoder_features(x, sd, training, prefix="encoder.", dilate_layer4=False):
+def encoder_features(x, sd, training, prefix="encoder.", q=_id):
     """-> [stem (64 @ /2), layer1 (/4), layer2 (/8), layer3 (/16), layer4 (/32)]."""
-    s = F.conv2d(x, sd[prefix + "conv1.weight"], None, stride=2, padding=3)
-    s = F.relu(_bn(s, sd, prefix + "bn1", training))
+    s = q(F.conv2d(q(x), q(sd[prefix + "conv1.weight"]), None, stride=2, padding=3))
+    s = q(F.relu(_bn(s, sd, prefix + "bn1", training)))
     f = F.max_pool2d(s, 3, 2, 1)
     feats = [s]
     for li in range(1, 5):
         for b in range(2):
             stride = 2 if (b == 0 and li > 1) else 1
-            f = _basic_block(f, sd, f"{prefix}layer{li}.{b}", stride, training)
+            f = _basic_block(f, sd, f"{prefix}layer{li}.{b}", stride, training, q)
         feats.append(f)
     return feats
 
 
-def forward(sd, x, output_size, training=False):
+def forward(sd, x, output_size, training=False, emulate_bf16=False):
     """ResUNet.forward (models/resunet.py:23-58). `sd` maps reference keys to tensors (leaf tensors with
-    requires_grad for the gradient oracle); BN running statistics in `sd` are updated in place when training."""
-    _, x2, x3, x4, x5 = encoder_features(x, sd, training)
-    y = F.conv_transpose2d(x5, sd["upconv1.weight"], sd["upconv1.bias"], stride=2)
-    y = F.relu(F.conv2d(torch.cat((y, x4), 1), sd["conv1.weight"], sd["conv1.bias"], padding=1))
-    y = F.conv_transpose2d(y, sd["upconv2.weight"], sd["upconv2.bias"], stride=2)
-    y = F.relu(F.conv2d(torch.cat((y, x3), 1), sd["conv2.weight"], sd["conv2.bias"], padding=1))
-    y = F.conv_transpose2d(y, sd["upconv3.weight"], sd["upconv3.bias"], stride=2)
-    y = F.relu(F.conv2d(torch.cat((y, x2), 1), sd["conv3.weight"], sd["conv3.bias"], padding=1))
-    y = F.conv2d(y, sd["conv4.weight"], sd["conv4.bias"])
+    requires_grad for the gradient oracle); BN running statistics in `sd` are updated in place when training.
+    emulate_bf16=True rounds weights and every stored activation (and its gradient) to bf16 at the points where the
+    CUDA product stores them, with all arithmetic still fp32: the oracle for kernel-level correctness of the
+    backward pass (ReLU masks then agree with the product's; the plain fp32 mode is the reference's arithmetic)."""
+    q = round_bf16 if emulate_bf16 else _id
+    _, x2, x3, x4, x5 = encoder_features(x, sd, training, q=q)
+    y = q(F.conv_transpose2d(x5, q(sd["upconv1.weight"]), sd["upconv1.bias"], stride=2))
+    y = q(F.relu(F.conv2d(torch.cat((y, x4), 1), q(sd["conv1.weight"]), sd["conv1.bias"], padding=1)))
+    y = q(F.conv_transpose2d(y, q(sd["upconv2.weight"]), sd["upconv2.bias"], stride=2))
+    y = q(F.relu(F.conv2d(torch.cat((y, x3), 1), q(sd["conv2.weight"]), sd["conv2.bias"], padding=1)))
+    y = q(F.conv_transpose2d(y, q(sd["upconv3.weight"]), sd["upconv3.bias"], stride=2))
+    y = q(F.relu(F.conv2d(torch.cat((y, x2), 1), q(sd["conv3.weight"]), sd["conv3.bias"], padding=1)))
+    y = q(F.conv2d(y, q(sd["conv4.weight"]), sd["conv4.bias"]))
     return F.interpolate(y, size=(output_size, output_size), mode="bilinear", align_corners=False)
 
 

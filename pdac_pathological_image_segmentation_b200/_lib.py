@@ -21,7 +21,7 @@ class PdacView(C.Structure):
 
 class PdacConv(C.Structure):
     _fields_ = [("R", C.c_int32), ("S", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32), ("dil", C.c_int32),
-                ("relu", C.c_int32), ("wrows", C.c_int32), ("reserved", C.c_int32)]
+                ("relu", C.c_int32), ("wrows", C.c_int32), ("cout_valid", C.c_int32)]
 
 
 class PdacTap(C.Structure):
@@ -40,13 +40,13 @@ _p, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
 SIGNATURES = {
     "pdac_check_device_flag": [_p],
     "pdac_tapconv_fwd": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
-    "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _p],
+    "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _i, _p],
     "pdac_conv2d_fwd": [C.POINTER(PdacConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
     "pdac_conv2d_dgrad": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, _p],
-    "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _p],
+    "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _i, _p],
     "pdac_convt2x2_fwd": [_VP, _p, _i, _p, _i, _VP, _p],
     "pdac_convt2x2_dgrad": [_VP, _p, _i, _VP, _p],
-    "pdac_convt2x2_wgrad": [_VP, _VP, _p, _p],
+    "pdac_convt2x2_wgrad": [_VP, _VP, _p, _i, _p],
     "pdac_nchw_f32_to_nhwc_bf16": [_p, _i, _i, _i, _i, _VP, _p],
     "pdac_nhwc_bf16_to_nchw_f32": [_VP, _i, _p, _p],
     "pdac_stem_prep_f32": [_p, _i, _i, _i, _p, _p],
@@ -54,7 +54,7 @@ SIGNATURES = {
     "pdac_pack_conv_weight": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
     "pdac_pack_stem_weight": [_p, _i, _p, _p],
     "pdac_unpack_stem_wgrad": [_p, _i, _p, _p],
-    "pdac_bn_prepare": [_p, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _i, _p],
+    "pdac_bn_prepare": [_p, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _p, _i, _p],
     "pdac_scale_shift_act": [_VP, _p, _VP, _i, _VP, _p],
     "pdac_bn_bwd_reduce": [_VP, _VP, _VP, _p, _p, _p],
     "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],

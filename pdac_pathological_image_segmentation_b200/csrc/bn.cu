@@ -44,10 +44,11 @@ static EwGrid ew_grid(long long npix, int C) {
 // ------------------------------------------------------------------------------------------------ bn_prepare
 __global__ void bn_prepare_kernel(const float* __restrict__ stats, double count, const float* __restrict__ gamma,
                                   const float* __restrict__ beta, float eps, float momentum, int train,
-                                  float* running_mean, float* running_var, float* __restrict__ scale_shift,
-                                  float* __restrict__ mean_invstd, int C) {
+                                  float* running_mean, float* running_var, long long* num_batches_tracked,
+                                  float* __restrict__ scale_shift, float* __restrict__ mean_invstd, int C) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
+  if (c == 0 && train && num_batches_tracked) *num_batches_tracked += 1;
   float mean, var;
   if (train) {
     const double m = (double)stats[c] / count;
@@ -233,14 +234,16 @@ __global__ void __launch_bounds__(256) relu_bwd_bias_kernel(Flat dy, Flat y, Fla
 using namespace pdac;
 
 extern "C" int pdac_bn_prepare(const float* stats, double count, const float* gamma, const float* beta, float eps,
-                               float momentum, int train, float* running_mean, float* running_var, float* scale_shift,
-                               float* mean_invstd, int C, void* stream) {
+                               float momentum, int train, float* running_mean, float* running_var,
+                               long long* num_batches_tracked, float* scale_shift, float* mean_invstd, int C,
+                               void* stream) {
   PDAC_REQUIRE(scale_shift && C > 0, "bn_prepare: null/empty");
   PDAC_REQUIRE(train ? (stats != nullptr) : (running_mean && running_var),
                "bn_prepare: train needs stats, eval needs running stats");
   if (train) PDAC_REQUIRE(count > 1.0, "Expected more than 1 value per channel when training (count=%g)", count);
   bn_prepare_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
-      stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd, C);
+      stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, num_batches_tracked, scale_shift,
+      mean_invstd, C);
   PDAC_LAUNCH_CHECK("bn_prepare");
   return PDAC_OK;
 }

@@ -611,8 +611,10 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
 }
 
 extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy,
-                                  float* dw, int64_t tap_stride, int64_t a_stride, int64_t b_stride, void* stream) {
+                                  float* dw, int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid,
+                                  void* stream) {
   PDAC_REQUIRE(tc && views && dy && dw, "null argument");
+  PDAC_REQUIRE(b_valid >= 0 && b_valid <= dy->C, "b_valid=%d out of range (dY has %d channels)", b_valid, dy->C);
   PDAC_TRY(check_dev_ptr(dw, "dw"));
   TcMaps maps;
   WgradKParams p;
@@ -660,7 +662,7 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
   p.tap_stride = tap_stride;
   p.a_stride = a_stride;
   p.b_stride = b_stride;
-  p.Cout = cout;
+  p.Cout = b_valid > 0 ? b_valid : cout;
   p.err = device_err_flag();
   const int b_tile = 128 * block_n * 2;
   int stages_a = (int)((220 * 1024 - 2 * b_tile) / (32 * 1024));
@@ -771,14 +773,18 @@ extern "C" int pdac_conv2d_fwd(const PdacConv* cv, int n_src, const PdacView* sr
 }
 
 extern "C" int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,
-                                 void* stream) {
+                                 int dw_layout, void* stream) {
   PDAC_REQUIRE(cv && src && dy && dw, "null argument");
   PdacTapConv tc;
   PdacView views[4];
   int nv = 0;
   PDAC_TRY(build_fwd_taps(cv, n_src, src, &tc, views, &nv));
   const int ctot = src[0].C + (n_src > 1 ? src[1].C : 0);
-  return pdac_tapconv_wgrad(&tc, nv, views, dy, dw, (int64_t)dy->C * ctot, 1, ctot, stream);
+  const int cv_valid = cv->cout_valid > 0 ? cv->cout_valid : dy->C;
+  if (dw_layout == 1)  // nn.Conv2d state_dict layout [Cout][Ctot][R][S]
+    return pdac_tapconv_wgrad(&tc, nv, views, dy, dw, 1, (int64_t)cv->R * cv->S, (int64_t)ctot * cv->R * cv->S,
+                              cv_valid, stream);
+  return pdac_tapconv_wgrad(&tc, nv, views, dy, dw, (int64_t)dy->C * ctot, 1, ctot, cv_valid, stream);
 }
 
 extern "C" int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const void* w_packed_t,
@@ -878,7 +884,7 @@ extern "C" int pdac_convt2x2_dgrad(const PdacView* dy, const void* w_packed_t, i
   return pdac_tapconv_fwd(&tc, 4, views, w_packed_t, nullptr, nullptr, dx, nullptr, stream);
 }
 
-extern "C" int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, void* stream) {
+extern "C" int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, int dw_layout, void* stream) {
   PDAC_REQUIRE(x && dy && dw, "null argument");
   // dW[a,b][cout][cin] = sum_{i,j} dy[2i+a, 2j+b, cout] * x[i, j, cin]: tapped operand = dy parity views, fixed = x.
   PdacTapConv tc;
@@ -891,5 +897,7 @@ extern "C" int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float*
       views[a * 2 + b] = parity_view(*dy, a, b);
       tc.taps[a * 2 + b].src = a * 2 + b;
     }
-  return pdac_tapconv_wgrad(&tc, 4, views, x, dw, (int64_t)dy->C * x->C, x->C, 1, stream);
+  if (dw_layout == 1)  // nn.ConvTranspose2d state_dict layout [Cin][Cout][2][2]
+    return pdac_tapconv_wgrad(&tc, 4, views, x, dw, 1, 4, (int64_t)dy->C * 4, 0, stream);
+  return pdac_tapconv_wgrad(&tc, 4, views, x, dw, (int64_t)dy->C * x->C, x->C, 1, 0, stream);
 }

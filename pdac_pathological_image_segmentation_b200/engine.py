@@ -1,0 +1,368 @@
+"""Execution engine of the drop-in modules: a tape of hand-written-kernel launches (ops.py -> libpdac_b200.so) with
+hand-derived backward steps. No torch.nn.functional, no cuDNN, no autograd inside: torch provides device memory
+(caching allocator) and the current stream only. The modules in resunet.py / smp.py write their forward as straight
+calls of the layer functions below; each call launches its kernels and, when gradients are wanted, records a closure
+that launches the matching backward kernels. Gradients of parameters are accumulated into a flat fp32 arena whose
+slots have the parameters' own (state_dict) layouts, so they can be handed to autograd / DDP / Adam as they are.
+
+Activations: NHWC bf16 torch tensors (N, H, W, C) with C a multiple of 16 (logit heads are zero-padded to 16)."""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .containers import BatchNorm2d, Conv2d, ConvTranspose2d
+
+F32 = torch.float32
+
+
+def pad16(c):
+    return (c + 15) // 16 * 16
+
+
+# ------------------------------------------------------------------------------------------------ packed weights
+class PackCache:
+    """bf16 K-major copies of the fp32 state_dict weights in the layouts the tcgen05 kernels read (ops.pack_*),
+    refreshed when a parameter's storage or version counter changes (optimizer.step / load_state_dict / .to())."""
+
+    def __init__(self):
+        self._c = {}
+
+    def _get(self, key, params, build):
+        sig = tuple((p.data_ptr(), p._version) for p in params if p is not None)
+        hit = self._c.get(key)
+        if hit is not None and hit[0] == sig:
+            return hit[1]
+        val = build()
+        self._c[key] = (sig, val)
+        return val
+
+    def conv(self, m: Conv2d, want_dgrad=True):
+        """-> (wp_f [R*S*wrows][Cin], wp_t [R*S*wrows_t][pad16(Cout)] or None, bias padded to pad16(Cout) or None)."""
+        def build():
+            w = m.weight.detach()
+            cpad = pad16(m.cout)
+            wp_f, wp_t = ops.pack_conv_weight(w.contiguous(), want_fwd=True, want_dgrad=want_dgrad, stride=m.stride,
+                                              pad=m.padding, cout_pad=cpad)
+            bias = None
+            if m.bias is not None:
+                bias = torch.zeros(cpad, dtype=F32, device=w.device)
+                bias[:m.cout].copy_(m.bias.detach())
+            return wp_f, wp_t, bias
+        return self._get((id(m), want_dgrad), (m.weight, m.bias), build)
+
+    def convt(self, m: ConvTranspose2d):
+        def build():
+            wp_f, wp_t = ops.pack_convt_weight(m.weight.detach().contiguous())
+            return wp_f, wp_t, m.bias.detach()
+        return self._get((id(m), "t"), (m.weight, m.bias), build)
+
+    def stem(self, m: Conv2d):
+        return self._get((id(m), "stem"), (m.weight,), lambda: ops.pack_stem_weight(m.weight.detach().contiguous()))
+
+
+# ------------------------------------------------------------------------------------------------ gradient arena
+class GradArena:
+    """One flat fp32 buffer with a slot per parameter (slot = the parameter's own layout, 256-byte aligned, at least
+    16 floats so channel-padded bias reductions stay inside their slot)."""
+
+    def __init__(self, params, device):
+        self.offsets = {}
+        off = 0
+        for p in params:
+            n = max(p.numel(), 16)
+            self.offsets[id(p)] = (off, p.numel(), tuple(p.shape))
+            off += (n + 63) // 64 * 64
+        self.size = off
+        self.flat = torch.zeros(max(off, 64), dtype=F32, device=device)
+        self._views = {}
+
+    def zero(self):
+        self.flat.zero_()
+
+    def slot(self, p, padded=False):
+        """fp32 view with the parameter's shape (or, padded=True, the raw >=16-float slot as 1-D)."""
+        off, n, shape = self.offsets[id(p)]
+        if padded:
+            return self.flat[off:off + max(n, 16)]
+        v = self._views.get(id(p))
+        if v is None:
+            v = self.flat[off:off + n].view(shape)
+            self._views[id(p)] = v
+        return v
+
+
+# ------------------------------------------------------------------------------------------------ tape
+class Tape:
+    def __init__(self, packs: PackCache, training: bool, arena: GradArena | None):
+        self.packs = packs
+        self.training = training
+        self.arena = arena
+        self.enabled = arena is not None
+        self.steps = []
+        self.grads = {}
+        self.nograd = set()
+
+    def record(self, fn):
+        if self.enabled:
+            self.steps.append(fn)
+
+    def no_grad_for(self, t):
+        self.nograd.add(id(t))
+
+    def wants(self, t):
+        return id(t) not in self.nograd
+
+    def put(self, t, g):
+        if id(t) in self.nograd:
+            return
+        k = id(t)
+        old = self.grads.get(k)
+        if old is None:
+            self.grads[k] = g
+        else:
+            ops.add(old, g, out=old)
+
+    def pop(self, t):
+        return self.grads.pop(id(t), None)
+
+    def backward(self):
+        for fn in reversed(self.steps):
+            fn()
+        self.steps = []
+        self.grads = {}
+
+
+# ------------------------------------------------------------------------------------------------ layer functions
+def _conv_backward(tape, m: Conv2d, srcs, dy, wp_t):
+    """wgrad into the arena slot (state_dict layout) and dgrad to the sources; dy has pad16(Cout) channels."""
+    k = m.k
+    ops.conv2d_wgrad(srcs, dy, k, k, m.stride, m.padding, m.dilation, out=tape.arena.slot(m.weight), oihw=True,
+                     cout_valid=m.cout)
+    need = [tape.wants(s) for s in srcs]
+    if not any(need):
+        return
+    h, w = srcs[0].shape[1], srcs[0].shape[2]
+    if len(srcs) == 1:
+        old = tape.pop(srcs[0])
+        dx = ops.conv2d_dgrad(dy, wp_t, srcs[0].shape[3], (h, w), k, k, m.stride, m.padding, m.dilation, addend=old,
+                              out=old)
+        tape.put(srcs[0], dx)
+    else:
+        ctot = sum(s.shape[3] for s in srcs)
+        dx = ops.conv2d_dgrad(dy, wp_t, ctot, (h, w), k, k, m.stride, m.padding, m.dilation)
+        c0 = 0
+        for s in srcs:
+            tape.put(s, dx[..., c0:c0 + s.shape[3]])
+            c0 += s.shape[3]
+
+
+def conv_bias_act(tape: Tape, m: Conv2d, srcs, relu):
+    """[relu](conv(cat(srcs)) + bias) with everything fused in the GEMM epilogue (models/resunet.py:38,42,46,48)."""
+    wp_f, wp_t, bias = tape.packs.conv(m)
+    k = m.k
+    y = ops.conv2d_fwd(srcs, wp_f, pad16(m.cout), k, k, m.stride, m.padding, m.dilation, relu=relu, bias=bias)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is None:
+            return
+        if relu or m.bias is not None:
+            dbias = tape.arena.slot(m.bias, padded=True)[:dy.shape[3]] if m.bias is not None else None
+            ops.relu_bwd_bias(dy, y if relu else None, dy if relu else None, dbias)
+        _conv_backward(tape, m, srcs, dy, wp_t)
+    tape.record(bwd)
+    return y
+
+
+class _BNState:
+    __slots__ = ("ss", "mi", "count")
+
+
+def _bn_prepare(tape, bn: BatchNorm2d, stats, count, device):
+    st = _BNState()
+    c = bn.num_features
+    st.ss = torch.empty((2, c), dtype=F32, device=device)
+    st.mi = torch.empty((2, c), dtype=F32, device=device)
+    st.count = count
+    if tape.training and count <= 1:
+        raise ValueError(f"Expected more than 1 value per channel when training, got input size [{count}, {c}]")
+    ops.bn_prepare(stats, count, bn.weight.detach(), bn.bias.detach(), bn.eps, bn.momentum, tape.training,
+                   bn.running_mean, bn.running_var, st.ss, st.mi,
+                   num_batches_tracked=bn.num_batches_tracked if tape.training else None)
+    return st
+
+
+def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residual=None):
+    """[relu](BN(conv(cat(srcs))) + residual): conv with per-channel sum / sum-of-squares in its epilogue, a finalize
+    kernel, then one fused normalise(+residual)(+ReLU) pass (torchvision resnet.py:92-103; smp Conv2dReLU)."""
+    wp_f, wp_t, _ = tape.packs.conv(m)
+    k = m.k
+    dev = srcs[0].device
+    stats = torch.zeros((2, m.cout), dtype=F32, device=dev) if tape.training else None
+    x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, stats=stats)
+    st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
+    keep_x = tape.enabled
+    y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=None if keep_x else x)
+    training = tape.training
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is None:
+            return
+        sums = torch.zeros((2, m.cout), dtype=F32, device=dev)
+        ops.bn_bwd_reduce(dy, y if relu else None, x, st.mi, sums)
+        want_res = residual is not None and tape.wants(residual)
+        dxr = torch.empty_like(dy) if want_res else dy
+        ops.bn_bwd_apply(dy, y if relu else None, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dxr,
+                         dz_out=dy if (want_res and relu) else None, dgamma=tape.arena.slot(bn.weight),
+                         dbeta=tape.arena.slot(bn.bias))
+        if want_res:
+            tape.put(residual, dy)
+        _conv_backward(tape, m, srcs, dxr, wp_t)
+    tape.record(bwd)
+    return y
+
+
+def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
+    """7x7 s2 p3 conv + BN + ReLU on the space-to-depth input z (N, H/2, W/2, 16) as a 4x4 s1 tap convolution."""
+    wp = tape.packs.stem(m)
+    dev = z.device
+    stats = torch.zeros((2, m.cout), dtype=F32, device=dev) if tape.training else None
+    x = ops.stem_conv_fwd(z, wp, m.cout, stats=stats)
+    st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
+    y = ops.scale_shift_act(x, st.ss, None, relu=True, out=None if tape.enabled else x)
+    training = tape.training
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is None:
+            return
+        sums = torch.zeros((2, m.cout), dtype=F32, device=dev)
+        ops.bn_bwd_reduce(dy, y, x, st.mi, sums)
+        ops.bn_bwd_apply(dy, y, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dy,
+                         dgamma=tape.arena.slot(bn.weight), dbeta=tape.arena.slot(bn.bias))
+        dwp = ops.stem_conv_wgrad(z, dy)
+        ops.unpack_stem_wgrad(dwp, m.cout, out=tape.arena.slot(m.weight))
+    tape.record(bwd)
+    return y
+
+
+def maxpool(tape: Tape, x):
+    y, idx = ops.maxpool_fwd(x, want_idx=tape.enabled)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is not None:
+            tape.put(x, ops.maxpool_bwd(dy, idx, (x.shape[1], x.shape[2])))
+    tape.record(bwd)
+    return y
+
+
+def convt2x2(tape: Tape, m: ConvTranspose2d, x):
+    """ConvTranspose2d(k=2, s=2) + bias: four parity-class GEMMs with pixel-shuffle stores (models/resunet.py:36,40,44)."""
+    wp_f, wp_t, bias = tape.packs.convt(m)
+    y = ops.convt2x2_fwd(x, wp_f, m.cout, bias=bias)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is None:
+            return
+        ops.relu_bwd_bias(dy, None, None, tape.arena.slot(m.bias))
+        ops.convt2x2_wgrad(x, dy, out=tape.arena.slot(m.weight), iohw=True)
+        if tape.wants(x):
+            tape.put(x, ops.convt2x2_dgrad(dy, wp_t, m.cin))
+    tape.record(bwd)
+    return y
+
+
+def nearest2x(tape: Tape, x):
+    y = ops.upsample_nearest2x_fwd(x)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is not None:
+            old = tape.pop(x)
+            tape.put(x, ops.upsample_nearest2x_bwd(dy, old, out=old))
+    tape.record(bwd)
+    return y
+
+
+def bilinear(tape: Tape, x, out_hw, align_corners):
+    y = ops.bilinear_fwd(x, out_hw, align_corners)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is not None:
+            tape.put(x, ops.bilinear_bwd(dy, (x.shape[1], x.shape[2]), align_corners))
+    tape.record(bwd)
+    return y
+
+
+def add(tape: Tape, a, b):
+    y = ops.add(a, b)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is not None:
+            tape.put(a, dy)
+            tape.put(b, dy.clone() if tape.wants(a) and tape.wants(b) else dy)
+    tape.record(bwd)
+    return y
+
+
+def logits_head(tape: Tape, x, n_classes, out_hw, align_corners):
+    """NHWC bf16 (channel-padded) -> fp32 NCHW logits, bilinearly resized to out_hw when it differs
+    (models/resunet.py:51-56; smp SegmentationHead upsampling). Returns (logits, feed_grad(g))."""
+    h, w, cpad = x.shape[1], x.shape[2], x.shape[3]
+    same = (h, w) == tuple(out_hw)
+    if same:
+        out = ops.nhwc_to_nchw(x, n_classes)
+    else:
+        out = ops.bilinear_head_fwd(x, n_classes, out_hw, align_corners)
+
+    def feed(g):
+        if same:
+            dx = ops.nchw_to_nhwc(g.contiguous(), c_pad=cpad)
+        else:
+            dx = ops.bilinear_head_bwd(g, (h, w, cpad), align_corners)
+        tape.put(x, dx)
+    return out, feed
+
+
+# ------------------------------------------------------------------------------------------------ ResNet18 encoder
+def basic_block(tape: Tape, blk, x):
+    """torchvision BasicBlock.forward (resnet.py:89-106): relu(bn2(conv2(relu(bn1(conv1 x)))) + shortcut(x))."""
+    out = conv_bn_act(tape, blk.conv1, blk.bn1, [x], relu=True)
+    if blk.downsample is not None:
+        ds = blk.downsample
+        identity = conv_bn_act(tape, getattr(ds, "0"), getattr(ds, "1"), [x], relu=False)
+    else:
+        identity = x
+    return conv_bn_act(tape, blk.conv2, blk.bn2, [out], relu=True, residual=identity)
+
+
+def stem_input(tape: Tape, x):
+    """fp32 NCHW (B,3,H,W) -> the stem's space-to-depth bf16 input; a bf16 (B,H/2,W/2,16) tensor passes through
+    (already prepared on the GPU from uint8 patches by ops.stem_prep_u8)."""
+    if x.dtype == torch.bfloat16:
+        z = x
+    else:
+        z = ops.stem_prep_f32(x)
+    tape.no_grad_for(z)
+    return z
+
+
+def resnet18_features(tape: Tape, enc, x, depth=5):
+    """-> [stem (64 @ H/2), layer1 (64 @ H/4), layer2 (128 @ H/8), layer3 (256 @ H/16), layer4 (512 @ H/32)][:depth]
+    (models/resunet.py:25-33; smp ResNetEncoder.forward stages 1..depth)."""
+    z = stem_input(tape, x)
+    s = stem(tape, enc.conv1, enc.bn1, z)
+    feats = [s]
+    if depth >= 2:
+        f = maxpool(tape, s)
+        for li in range(1, depth):
+            for blk in enc.blocks(li):
+                f = basic_block(tape, blk, f)
+            feats.append(f)
+    return feats

@@ -31,8 +31,12 @@ def view(t):
     if t.dtype != BF16 or t.dim() != 4 or (t.shape[3] > 1 and t.stride(3) != 1):
         raise RuntimeError(f"pdac_b200: activation must be NHWC bf16 with unit channel stride, got {t.dtype} "
                            f"{tuple(t.shape)} strides {t.stride()}")
-    return PdacView(t.data_ptr(), t.shape[0], t.shape[1], t.shape[2], t.shape[3], t.stride(0), t.stride(1),
-                    t.stride(2))
+    n, h, w, c = t.shape
+    # torch leaves the stride of an extent-1 dimension arbitrary: give the library the canonical one
+    sw = t.stride(2) if w > 1 else c
+    sh = t.stride(1) if h > 1 else w * sw
+    sn = t.stride(0) if n > 1 else h * sh
+    return PdacView(t.data_ptr(), n, h, w, c, sn, sh, sw)
 
 
 def _vp(t):
@@ -60,8 +64,8 @@ def empty_act(n, h, w, c, device):
 
 
 # ------------------------------------------------------------------------------------------------ convolutions
-def _conv_struct(R, S, stride, pad, dil, relu, wrows):
-    return PdacConv(R, S, stride, pad, dil, int(bool(relu)), wrows, 0)
+def _conv_struct(R, S, stride, pad, dil, relu, wrows, cout_valid=0):
+    return PdacConv(R, S, stride, pad, dil, int(bool(relu)), wrows, cout_valid)
 
 
 def conv_out_hw(h, w, R, S, stride, pad, dil):
@@ -96,14 +100,16 @@ def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None,
     return out
 
 
-def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None):
-    """dw fp32 [R*S, dy.C, sum(src.C)] (accumulated into `out` if given, which must be pre-zeroed)."""
+def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None, oihw=False, cout_valid=0):
+    """dw fp32 [R*S, dy.C, sum(src.C)] (or, with oihw=True, the state_dict layout [cout, sum(src.C), R, S]),
+    accumulated into `out` if given (which must be pre-zeroed). cout_valid: real channels of a padded dy."""
     ktot = sum(s.shape[3] for s in srcs)
     if out is None:
-        out = torch.zeros((R * S, dy.shape[3], ktot), dtype=torch.float32, device=dy.device)
-    cv = _conv_struct(R, S, stride, pad, dil, False, 0)
+        shape = ((cout_valid or dy.shape[3]), ktot, R, S) if oihw else (R * S, dy.shape[3], ktot)
+        out = torch.zeros(shape, dtype=torch.float32, device=dy.device)
+    cv = _conv_struct(R, S, stride, pad, dil, False, 0, cout_valid)
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
-    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), _stream())
+    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), int(bool(oihw)), _stream())
     return out
 
 
@@ -123,11 +129,12 @@ def convt2x2_dgrad(dy, wpt, cin, out=None):
     return out
 
 
-def convt2x2_wgrad(x, dy, out=None):
-    """dw fp32 [4, Cout, Cin]."""
+def convt2x2_wgrad(x, dy, out=None, iohw=False):
+    """dw fp32 [4, Cout, Cin], or with iohw=True the nn.ConvTranspose2d layout [Cin, Cout, 2, 2]."""
     if out is None:
-        out = torch.zeros((4, dy.shape[3], x.shape[3]), dtype=torch.float32, device=x.device)
-    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), _stream())
+        shape = (x.shape[3], dy.shape[3], 2, 2) if iohw else (4, dy.shape[3], x.shape[3])
+        out = torch.zeros(shape, dtype=torch.float32, device=x.device)
+    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), int(bool(iohw)), _stream())
     return out
 
 
@@ -148,10 +155,11 @@ def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=Non
     return out
 
 
-def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1):
+def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1, b_valid=0):
     tc = _tapconv(taps, n_cat, 0, False)
     vs = (PdacView * len(views))(*[view(v) for v in views])
-    call("pdac_tapconv_wgrad", C.byref(tc), len(views), vs, _vp(dy), _ptr(dw), tap_stride, a_stride, b_stride, _stream())
+    call("pdac_tapconv_wgrad", C.byref(tc), len(views), vs, _vp(dy), _ptr(dw), tap_stride, a_stride, b_stride, b_valid,
+         _stream())
     return dw
 
 
@@ -277,10 +285,12 @@ def stem_prep_u8(img, mask=None, aug=None, mean=IMAGENET_MEAN, std=IMAGENET_STD,
 
 
 # ------------------------------------------------------------------------------------------------ BN / elementwise
-def bn_prepare(stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd):
+def bn_prepare(stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd,
+               num_batches_tracked=None):
     c = scale_shift.shape[-1]
     call("pdac_bn_prepare", _ptr(stats), float(count), _ptr(gamma), _ptr(beta), eps, momentum, int(bool(train)),
-         _ptr(running_mean), _ptr(running_var), _ptr(scale_shift), _ptr(mean_invstd), c, _stream())
+         _ptr(running_mean), _ptr(running_var), _ptr(num_batches_tracked), _ptr(scale_shift), _ptr(mean_invstd), c,
+         _stream())
 
 
 def scale_shift_act(x, scale_shift=None, residual=None, relu=False, out=None):
