@@ -1,0 +1,288 @@
+"""bench.py — the reference's headline metric on the B200: smp Unet-ResNet18 512x512 bf16 training, patches/s
+(BASELINE.json metric; configs[1]: batch 64 per GPU, data-parallel, weak scaling).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (hand-written sm_100a kernels)
+  python bench.py --impl reference ...                           the reference arm: the same network / step on the host
+                                                                 CPU cores (oracle port of the reference's torch code)
+For N > 1 launch under torchrun (one rank per GPU, NCCL); rank 0 prints ONE JSON line.
+
+A "step" = train_worker.py:68-80 on one batch: uint8 HWC patches -> GPU decode/normalise -> forward -> sigmoid mask +
+dice score -> Dice loss -> backward -> gradient allreduce (N > 1) -> Adam. `value` is timed with the uint8 batch already
+in HBM; `e2e` copies each batch from pinned host memory and reads the loss back every step.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "smp Unet-ResNet18 512x512 bf16 train patches/s"
+UNIT = "patches/s"
+TRAIN_GF_PER_PATCH = 128.321      # SURVEY 8d / BASELINE.md: 2*MACs of all convs, fwd + dgrad + wgrad, classes=1
+FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="patches per GPU (BASELINE config 2: 64)")
+    ap.add_argument("--size", type=int, default=512)
+    ap.add_argument("--cpu-batch", type=int, default=2, help="patches per CPU-baseline step (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return p, "measured"
+    except Exception:
+        return dict(FALLBACK_PEAKS), "fallback"
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm / baseline
+def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None):
+    """The reference's step (train_worker.py:68-80) on the host cores: oracle restatement of smp.Unet(resnet18) +
+    DiceLoss + Adam in stock torch fp32 (smp is absent from the reference tree, see oracle/smp_oracle.py)."""
+    import torch
+
+    from oracle import resunet_oracle as R
+    from oracle import smp_oracle as S
+    from oracle import util_oracle as U
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(cores)
+    torch.manual_seed(41)
+    model = S.Unet(classes=1).train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    img, mask = R.synthetic_batch(batch, size, seed=41)
+    x = R.normalize(img)
+    label = mask.unsqueeze(1)
+    for _ in range(warmup):
+        U.train_step(model, opt, x, label)
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        U.train_step(model, opt, x, label)
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return done * batch / dt, cores, done, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, args.size, args.steps, min(args.warmup, 1))
+    sample = (f"{done} steps x {args.cpu_batch} patches of {args.size}x{args.size} on {cores} host threads "
+              f"(oracle port of the reference step, torch fp32 CPU)")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
+            "warmup": min(args.warmup, 1), "ms_per_step": 1000 * dt / max(done, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"smp Unet-ResNet18 train step, {args.size}x{args.size} RGB patches, 1 class, CPU "
+                                   f"sample of {args.cpu_batch} patches/step"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from pdac_pathological_image_segmentation_b200 import _lib
+    from pdac_pathological_image_segmentation_b200.smp import Unet
+    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
+    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (ours) needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    B, S = args.batch, args.size
+    torch.manual_seed(41)
+    model = Unet(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None)
+    model.to(dev).train()
+    ts = TrainStep(model, lr=1e-4)
+    ts.broadcast_parameters()
+
+    # synthetic uint8 HWC patches + blobby masks, a few distinct batches, pinned on the host
+    n_host = 2
+    host = []
+    for i in range(n_host):
+        img, mask = synthetic_batch(B, S, seed=41 + rank * 100 + i)
+        host.append((img.pin_memory(), mask.pin_memory()))
+    dev_batches = [(i.to(dev), m.to(dev)) for i, m in host]
+    img_d = torch.empty_like(dev_batches[0][0])
+    mask_d = torch.empty_like(dev_batches[0][1])
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        ts.step(*dev_batches[i % n_host])
+    sync_all()
+
+    # ---- timed region 1: inputs resident in HBM -------------------------------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _lib.trace = []
+    l0 = _lib.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record()
+    for i in range(args.steps):
+        loss, score = ts.step(*dev_batches[i % n_host])
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    trace, _lib.trace = _lib.trace, None
+    launches = _lib.launches - l0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = t.item()
+    value = world * B * args.steps / (ms / 1000)
+
+    # ---- timed region 2: end to end through TrainStep with host buffers ---------------------------------------
+    sync_all()
+    w0 = time.perf_counter()
+    e0.record()
+    last = 0.0
+    for i in range(args.steps):
+        ih, mh = host[i % n_host]
+        img_d.copy_(ih, non_blocking=True)
+        mask_d.copy_(mh, non_blocking=True)
+        loss, score = ts.step(img_d, mask_d)
+        last = loss.item()                       # device -> host read of the step's result (train_worker.py:83)
+    e1.record()
+    sync_all()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - w0) * 1000)      # device span or host wall, the larger
+    t = torch.tensor([ms_e2e], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e = world * B * args.steps / (t.item() / 1000)
+    h2d = B * S * S * 3 + B * S * S
+    d2h = 4
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel group (CUDA events recorded on the launching stream, timed region 1) ----
+    pk, pk_src = peaks()
+    groups = {}
+    for name, a, b, fl, nb in trace:
+        kind = "wgrad_tc_kernel" if "wgrad" in name else "conv_tc_kernel"
+        g = groups.setdefault(kind, [0.0, 0.0, 0.0, 0])
+        g[0] += a.elapsed_time(b)
+        g[1] += fl
+        g[2] += nb
+        g[3] += 1
+    dom = max(groups, key=lambda k: groups[k][0])
+    gms, gfl, gnb, gcalls = groups[dom]
+    tc_peak = pk.get("bf16_tflops_sustained") or pk.get("bf16_tflops")
+    achieved = gfl / (gms / 1000) / 1e12
+    roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": tc_peak, "unit": "TFLOP/s",
+                "frac": achieved / tc_peak, "traffic": None, "peak_source": f"{pk_src} bf16_tflops_sustained",
+                "calls_per_step": gcalls / args.steps, "ms_per_step_in_kernel": gms / args.steps,
+                "share_of_step": gms / ms,
+                "groups": {k: {"ms_per_step": v[0] / args.steps, "tflops": v[1] / (v[0] / 1000) / 1e12,
+                               "act_gbs": v[2] / (v[0] / 1000) / 1e9} for k, v in groups.items()}}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"smp Unet-ResNet18 train step (fwd + Dice loss + bwd + allreduce + Adam), "
+                                   f"{S}x{S} RGB uint8 patches, 1 class, batch {B}/GPU",
+                       "global_batch": B * world, "parallelism": f"dp{world}",
+                       "l2": "inputs and activations (GBs per step) far exceed the 126 MB L2; no explicit flush"},
+            "tc_fraction_of_step": TRAIN_GF_PER_PATCH * 1e9 * value / world / (tc_peak * 1e12) if S == 512 else None,
+            "loss": last, "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "roofline": roofline}
+    if not args.no_cpu_baseline and world == 1:
+        v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, S, 1000, 1, budget_s=15.0)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{done} steps x {args.cpu_batch} patches ({dt:.1f} s) of the same train step, "
+                                          f"oracle torch fp32 on {cores} host threads"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

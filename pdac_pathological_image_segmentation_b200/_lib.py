@@ -105,11 +105,23 @@ def load():
     return lib
 
 
-def call(name, *args):
-    """Calls a status-returning entry point; raises RuntimeError with the library's message on failure."""
+trace = None  # bench.py sets this to a list: (name, start_event, end_event, flops, bytes) per traced call
+
+
+def call(name, *args, flops=0, nbytes=0):
+    """Calls a status-returning entry point; raises RuntimeError with the library's message on failure.
+    flops / nbytes: algorithmic work of the call, recorded with CUDA events on the current stream when tracing."""
     global launches
     lib = load()
-    rc = getattr(lib, name)(*args)
+    if trace is not None and (flops or nbytes):
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(lib, name)(*args)
+        e1.record()
+        trace.append((name, e0, e1, flops, nbytes))
+    else:
+        rc = getattr(lib, name)(*args)
     launches += 1
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.pdac_last_error().decode()}")

@@ -28,6 +28,10 @@ class PackCache:
     def __init__(self):
         self._c = {}
 
+    def invalidate(self):
+        """Forget every packed copy (the trainer updates parameters through raw pointers, which bumps no version)."""
+        self._c.clear()
+
     def _get(self, key, params, build):
         sig = tuple((p.data_ptr(), p._version) for p in params if p is not None)
         hit = self._c.get(key)
@@ -46,8 +50,14 @@ class PackCache:
                                               pad=m.padding, cout_pad=cpad)
             bias = None
             if m.bias is not None:
-                bias = torch.zeros(cpad, dtype=F32, device=w.device)
-                bias[:m.cout].copy_(m.bias.detach())
+                if m.cout == cpad:
+                    bias = m.bias.detach()
+                elif getattr(m.bias, "_pdac_padded_slot", False):
+                    # the trainer keeps parameters in zero-padded >= 16-float arena slots: read the pad in place
+                    bias = torch.as_strided(m.bias.detach(), (cpad,), (1,))
+                else:
+                    bias = torch.zeros(cpad, dtype=F32, device=w.device)
+                    bias[:m.cout].copy_(m.bias.detach())
             return wp_f, wp_t, bias
         return self._get((id(m), want_dgrad), (m.weight, m.bias), build)
 
@@ -146,11 +156,11 @@ def _conv_backward(tape, m: Conv2d, srcs, dy, wp_t):
     if len(srcs) == 1:
         old = tape.pop(srcs[0])
         dx = ops.conv2d_dgrad(dy, wp_t, srcs[0].shape[3], (h, w), k, k, m.stride, m.padding, m.dilation, addend=old,
-                              out=old)
+                              out=old, c_real=m.cout)
         tape.put(srcs[0], dx)
     else:
         ctot = sum(s.shape[3] for s in srcs)
-        dx = ops.conv2d_dgrad(dy, wp_t, ctot, (h, w), k, k, m.stride, m.padding, m.dilation)
+        dx = ops.conv2d_dgrad(dy, wp_t, ctot, (h, w), k, k, m.stride, m.padding, m.dilation, c_real=m.cout)
         c0 = 0
         for s in srcs:
             tape.put(s, dx[..., c0:c0 + s.shape[3]])
@@ -161,7 +171,8 @@ def conv_bias_act(tape: Tape, m: Conv2d, srcs, relu):
     """[relu](conv(cat(srcs)) + bias) with everything fused in the GEMM epilogue (models/resunet.py:38,42,46,48)."""
     wp_f, wp_t, bias = tape.packs.conv(m)
     k = m.k
-    y = ops.conv2d_fwd(srcs, wp_f, pad16(m.cout), k, k, m.stride, m.padding, m.dilation, relu=relu, bias=bias)
+    y = ops.conv2d_fwd(srcs, wp_f, pad16(m.cout), k, k, m.stride, m.padding, m.dilation, relu=relu, bias=bias,
+                       c_real=m.cout)
 
     def bwd():
         dy = tape.pop(y)

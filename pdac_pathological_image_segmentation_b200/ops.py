@@ -72,8 +72,12 @@ def conv_out_hw(h, w, R, S, stride, pad, dil):
     return ((h + 2 * pad - dil * (R - 1) - 1) // stride + 1, (w + 2 * pad - dil * (S - 1) - 1) // stride + 1)
 
 
+def _act_bytes(*ts):
+    return sum(t.numel() * t.element_size() for t in ts if t is not None)
+
+
 def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=None, addend=None, stats=None,
-               out=None):
+               out=None, c_real=None):
     """out = [relu](conv(cat(srcs), w) + bias + addend); optional BN statistics (fp32 [2, cout], pre-zeroed)."""
     x0 = srcs[0]
     ho, wo = conv_out_hw(x0.shape[1], x0.shape[2], R, S, stride, pad, dil)
@@ -85,18 +89,21 @@ def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=No
     cv = _conv_struct(R, S, stride, pad, dil, relu, wrows)
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
     call("pdac_conv2d_fwd", C.byref(cv), len(srcs), views, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
-         _stream())
+         _stream(), flops=2 * x0.shape[0] * ho * wo * (c_real or cout) * ktot * R * S,
+         nbytes=_act_bytes(out, addend, *srcs))
     return out
 
 
-def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None, out=None):
+def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None, out=None, c_real=None):
     """dx (N, H, W, cin) = data gradient of the conv; `addend` (same shape as dx) is added (may alias `out`)."""
     if out is None:
         out = empty_act(dy.shape[0], in_hw[0], in_hw[1], cin, dy.device)
     wrows = wpt.shape[0] // (R * S)
     assert wpt.dtype == BF16 and wpt.is_contiguous() and wpt.shape[1] == dy.shape[3]
     cv = _conv_struct(R, S, stride, pad, dil, False, wrows)
-    call("pdac_conv2d_dgrad", C.byref(cv), _vp(dy), _ptr(wpt), _vp(addend), _vp(out), _stream())
+    call("pdac_conv2d_dgrad", C.byref(cv), _vp(dy), _ptr(wpt), _vp(addend), _vp(out), _stream(),
+         flops=2 * dy.shape[0] * dy.shape[1] * dy.shape[2] * (c_real or dy.shape[3]) * cin * R * S,
+         nbytes=_act_bytes(dy, out, addend))
     return out
 
 
@@ -109,7 +116,9 @@ def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None, oihw=False, c
         out = torch.zeros(shape, dtype=torch.float32, device=dy.device)
     cv = _conv_struct(R, S, stride, pad, dil, False, 0, cout_valid)
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
-    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), int(bool(oihw)), _stream())
+    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), int(bool(oihw)), _stream(),
+         flops=2 * dy.shape[0] * dy.shape[1] * dy.shape[2] * (cout_valid or dy.shape[3]) * ktot * R * S,
+         nbytes=_act_bytes(dy, *srcs))
     return out
 
 
@@ -117,7 +126,8 @@ def convt2x2_fwd(x, wp, cout, bias=None, relu=False, out=None):
     if out is None:
         out = empty_act(x.shape[0], 2 * x.shape[1], 2 * x.shape[2], cout, x.device)
     wrows = wp.shape[0] // 4
-    call("pdac_convt2x2_fwd", _vp(x), _ptr(wp), wrows, _ptr(bias), int(bool(relu)), _vp(out), _stream())
+    call("pdac_convt2x2_fwd", _vp(x), _ptr(wp), wrows, _ptr(bias), int(bool(relu)), _vp(out), _stream(),
+         flops=8 * x.numel() * cout, nbytes=_act_bytes(x, out))
     return out
 
 
@@ -125,7 +135,8 @@ def convt2x2_dgrad(dy, wpt, cin, out=None):
     if out is None:
         out = empty_act(dy.shape[0], dy.shape[1] // 2, dy.shape[2] // 2, cin, dy.device)
     wrows = wpt.shape[0] // 4
-    call("pdac_convt2x2_dgrad", _vp(dy), _ptr(wpt), wrows, _vp(out), _stream())
+    call("pdac_convt2x2_dgrad", _vp(dy), _ptr(wpt), wrows, _vp(out), _stream(),
+         flops=2 * dy.numel() * cin, nbytes=_act_bytes(dy, out))
     return out
 
 
@@ -134,7 +145,8 @@ def convt2x2_wgrad(x, dy, out=None, iohw=False):
     if out is None:
         shape = (x.shape[3], dy.shape[3], 2, 2) if iohw else (4, dy.shape[3], x.shape[3])
         out = torch.zeros(shape, dtype=torch.float32, device=x.device)
-    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), int(bool(iohw)), _stream())
+    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), int(bool(iohw)), _stream(),
+         flops=2 * dy.numel() * x.shape[3], nbytes=_act_bytes(x, dy))
     return out
 
 
@@ -146,20 +158,20 @@ def _tapconv(taps, n_cat, wrows, relu):
     return tc
 
 
-def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=None, stats=None):
+def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=None, stats=None, flops=0):
     """Generalised tap convolution (pdac_tapconv_fwd): taps = [(first view index, dh, dw), ...]."""
     tc = _tapconv(taps, n_cat, wp.shape[0] // len(taps), relu)
     vs = (PdacView * len(views))(*[view(v) for v in views])
     call("pdac_tapconv_fwd", C.byref(tc), len(views), vs, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
-         _stream())
+         _stream(), flops=flops, nbytes=_act_bytes(out, addend, *views[:n_cat]))
     return out
 
 
-def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1, b_valid=0):
+def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1, b_valid=0, flops=0):
     tc = _tapconv(taps, n_cat, 0, False)
     vs = (PdacView * len(views))(*[view(v) for v in views])
     call("pdac_tapconv_wgrad", C.byref(tc), len(views), vs, _vp(dy), _ptr(dw), tap_stride, a_stride, b_stride, b_valid,
-         _stream())
+         _stream(), flops=flops, nbytes=_act_bytes(dy, *views[:n_cat]))
     return dw
 
 
@@ -171,14 +183,16 @@ STEM_TAPS = [(0, a - 2, b - 2) for a in range(4) for b in range(4)]
 def stem_conv_fwd(z, wp, cout, stats=None, out=None):
     if out is None:
         out = empty_act(z.shape[0], z.shape[1], z.shape[2], cout, z.device)
-    return tapconv_fwd([z], STEM_TAPS, wp, out, stats=stats)
+    return tapconv_fwd([z], STEM_TAPS, wp, out, stats=stats,
+                       flops=2 * out.shape[0] * out.shape[1] * out.shape[2] * cout * 147)
 
 
 def stem_conv_wgrad(z, dy, out=None):
     """fp32 [16, Cout, 16] in the packed space-to-depth form (see unpack_stem_wgrad)."""
     if out is None:
         out = torch.zeros((16, dy.shape[3], 16), dtype=torch.float32, device=z.device)
-    return tapconv_wgrad([z], STEM_TAPS, dy, out, dy.shape[3] * 16, 1, 16)
+    return tapconv_wgrad([z], STEM_TAPS, dy, out, dy.shape[3] * 16, 1, 16,
+                         flops=2 * dy.shape[0] * dy.shape[1] * dy.shape[2] * dy.shape[3] * 147)
 
 
 # ------------------------------------------------------------------------------------------------ packing / layout
