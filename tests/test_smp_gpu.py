@@ -1,0 +1,146 @@
+"""smp-compatible drop-in modules (Unet / FPN / PSPNet / DeepLabV3+ with the resnet18 encoder) against the fp32 torch.nn
+restatement of smp v0.3.x in oracle/smp_oracle.py. smp itself is absent (PARITY UNPINNED upstream, see that file's
+header): these tests pin the product to stock torch arithmetic on the restated topology and to smp's state_dict layout.
+
+Tolerances: logits max-abs <= 2e-2 (BASELINE.json north_star); gradients self-calibrated against the bf16-storage
+emulation of the oracle (tests/test_resunet_gpu.py header explains why)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _pair(name, **kw):
+    from oracle import smp_oracle as S
+    from oracle.emulate import round_parameters_to_bf16_
+    from pdac_pathological_image_segmentation_b200 import smp as P
+    torch.manual_seed(41)
+    ref = S.build(name, dropout=0.0, **kw)
+    g = torch.Generator().manual_seed(5)
+    with torch.no_grad():                       # non-trivial norm parameters / running statistics
+        for m in ref.modules():
+            if isinstance(m, (torch.nn.BatchNorm2d, torch.nn.GroupNorm)):
+                m.weight.copy_(1 + 0.2 * torch.rand(m.weight.shape, generator=g) - 0.1)
+                m.bias.copy_(0.05 * torch.randn(m.bias.shape, generator=g))
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.copy_(0.1 * torch.randn(m.running_mean.shape, generator=g))
+                m.running_var.copy_(0.5 + torch.rand(m.running_var.shape, generator=g))
+            if isinstance(m, torch.nn.Conv2d) and m.bias is not None:
+                m.bias.copy_(0.1 * torch.randn(m.bias.shape, generator=g))
+    round_parameters_to_bf16_(ref)
+    cls = {"unet_smp": P.Unet, "fpn": getattr(P, "FPN", None), "pspnet": getattr(P, "PSPNet", None),
+           "deeplabv3+": getattr(P, "DeepLabV3Plus", None)}[name]
+    extra = {}
+    if name == "deeplabv3+":
+        extra["decoder_atrous_rates"] = kw.get("dilations", (3, 6, 9))
+    if name == "pspnet":
+        extra["psp_use_batchnorm"] = True
+    ours = cls(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None, **extra)
+    assert [(k, tuple(v.shape), v.dtype) for k, v in ours.state_dict().items()] == \
+           [(k, tuple(v.shape), v.dtype) for k, v in ref.state_dict().items()], "state_dict layout differs from smp's"
+    ours.load_state_dict(ref.state_dict(), strict=True)
+    return ref, ours.to(DEV)
+
+
+def _inputs(size=64, batch=2):
+    from oracle import resunet_oracle as R
+    img, mask = R.synthetic_batch(batch, size, seed=41)
+    return R.normalize(img), mask
+
+
+MODELS = ["unet_smp"]
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_eval_logits_match_oracle(name):
+    ref, ours = _pair(name)
+    x, _ = _inputs()
+    ref.eval()
+    ours.eval()
+    with torch.no_grad():
+        a = ref(x)
+        b = ours(x.to(DEV)).cpu()
+    assert a.shape == b.shape and b.dtype == torch.float32
+    err = (a - b).abs().max().item()
+    assert err <= 2e-2, f"{name}: eval logits max-abs err {err} (|ref| max {a.abs().max().item():.3f})"
+
+
+@pytest.mark.parametrize("name", MODELS)
+@pytest.mark.parametrize("train", [True, False])
+def test_train_step_matches_oracle(name, train):
+    import copy
+
+    from oracle import util_oracle as U
+    from oracle.emulate import bf16_storage
+    from pdac_pathological_image_segmentation_b200.util import DiceLoss
+    ref, ours = _pair(name)
+    x, mask = _inputs()
+    t = mask.float()
+    ref.train(train)
+    ours.train(train)
+    emu = copy.deepcopy(ref)
+    out = ours(x.to(DEV))
+    loss = DiceLoss()(torch.squeeze(out), t.to(DEV))
+    loss.backward()
+    a = ref(x)
+    la = U.dice_loss(torch.squeeze(a), t)
+    la.backward()
+    with bf16_storage(emu):
+        U.dice_loss(torch.squeeze(emu(x)), t).backward()
+    err = (out.detach().cpu() - a.detach()).abs().max().item()
+    assert err <= 2e-2, f"{name}: logits max-abs err {err}"
+    assert abs(loss.item() - la.item()) <= 2e-3
+    pa, pe = dict(ref.named_parameters()), dict(emu.named_parameters())
+    bad = []
+    for k, p in ours.named_parameters():
+        if pa[k].grad is None:
+            assert p.grad is None, f"{k}: the reference leaves this parameter without a gradient"
+            continue
+        assert p.grad is not None, k
+        r = pa[k].grad.double()
+        rel = ((p.grad.cpu().double() - r).norm() / (r.norm() + 1e-30)).item()
+        cal = ((pe[k].grad.double() - r).norm() / (r.norm() + 1e-30)).item()
+        if not rel <= 1.5 * cal + 2e-2:
+            bad.append((k, round(rel, 4), round(cal, 4)))
+    assert not bad, f"{name}: gradients farther from fp32 than bf16 storage explains (param, ours, calibrated): {bad}"
+    if train:
+        sa, so = ref.state_dict(), ours.state_dict()
+        for k in sa:
+            if k.endswith("running_var") or k.endswith("running_mean"):
+                assert torch.allclose(so[k].cpu(), sa[k], rtol=5e-2, atol=5e-3), k
+            if k.endswith("num_batches_tracked"):
+                assert int(so[k]) == int(sa[k]), k
+
+
+def test_trainstep_matches_autograd_path():
+    """The fused training harness (uint8 patches -> ... -> Adam) computes the same loss and parameter update as the
+    drop-in module under torch autograd + torch.optim.Adam (train_worker.py:68-80)."""
+    import copy
+
+    from pdac_pathological_image_segmentation_b200 import ops
+    from pdac_pathological_image_segmentation_b200.smp import Unet
+    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
+    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
+    from pdac_pathological_image_segmentation_b200.util import DiceLoss
+    torch.manual_seed(3)
+    m1 = Unet(encoder_weights=None).to(DEV).train()
+    m2 = copy.deepcopy(m1)
+    img, mask = synthetic_batch(2, 64, seed=7)
+    img, mask = img.to(DEV), mask.to(DEV)
+    ts = TrainStep(m1, lr=1e-3)
+    loss1, score1 = ts.step(img, mask)
+    mean = torch.tensor(ops.IMAGENET_MEAN, device=DEV)
+    std = torch.tensor(ops.IMAGENET_STD, device=DEV)
+    x = ((img.float() / 255 - mean) / std).permute(0, 3, 1, 2).contiguous()
+    opt = torch.optim.Adam(m2.parameters(), lr=1e-3)
+    out = m2(x)
+    loss2 = DiceLoss()(torch.squeeze(out), mask.float())
+    loss2.backward()
+    opt.step()
+    assert abs(loss1.item() - loss2.item()) <= 1e-5
+    for (k, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
+        d = (p1 - p2).abs().max().item()
+        assert d <= 2e-4, (k, d)          # Adam's first step moves every weight by ~lr: sign agreement of the gradient
+    ts.step(img, mask)                    # second step runs on re-packed weights
+    assert torch.isfinite(ts.flat_params).all()
