@@ -7,9 +7,9 @@ still running (DistributedDataParallel semantics: mean over ranks, train_worker.
 from __future__ import annotations
 
 import torch
-import torch.distributed as dist
 
 from . import ops
+from .ddp import BucketReducer, make_buckets
 from .engine import GradArena, Tape
 
 
@@ -34,45 +34,17 @@ class TrainStep:
             p._pdac_padded_slot = True
         self.exp_avg = torch.zeros_like(self.arena.flat)
         self.exp_avg_sq = torch.zeros_like(self.arena.flat)
-        self.world = 1
-        self.pg = process_group
-        if dist.is_available() and dist.is_initialized():
-            self.world = dist.get_world_size(process_group)
-        self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
-        self._buckets = self._make_buckets(bucket_mb)
+        offsets = [self.arena.offsets[id(p)][0] for p in self.params]
+        self.reducer = BucketReducer(self.arena.flat, make_buckets(offsets, self.arena.size, bucket_mb), process_group)
+        self.world = self.reducer.world
         model._packs.invalidate()
-
-    # DDP-style buckets: contiguous ranges of the arena, built from the LAST registered parameter backwards (the
-    # decoder / head gradients are complete first), each <= bucket_mb
-    def _make_buckets(self, bucket_mb):
-        cap = int(bucket_mb * 1024 * 1024 / 4)
-        spans, hi, lo = [], self.arena.size, self.arena.size
-        for p in reversed(self.params):
-            off, _, _ = self.arena.offsets[id(p)]
-            if hi - off > cap and lo < hi:
-                spans.append((lo, hi))
-                hi = lo
-            lo = off
-        if lo < hi:
-            spans.append((lo, hi))
-        return spans
 
     def broadcast_parameters(self, src=0):
         """DDP's construction-time parameter / buffer broadcast (train_worker.py:204)."""
-        if self.world > 1:
-            dist.broadcast(self.flat_params, src, group=self.pg)
-            for b in self.model.buffers():
-                dist.broadcast(b, src, group=self.pg)
+        self.reducer.broadcast([self.flat_params] + list(self.model.buffers()), src)
 
     def _allreduce(self):
-        if self.world == 1:
-            return
-        cur = torch.cuda.current_stream(self.device)
-        self.comm_stream.wait_stream(cur)
-        with torch.cuda.stream(self.comm_stream):
-            for lo, hi in self._buckets:
-                dist.all_reduce(self.arena.flat[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
-        cur.wait_stream(self.comm_stream)
+        self.reducer.allreduce_sum()
 
     def forward_backward(self, img_u8, mask_u8, aug=None):
         """-> (loss, dice score) as 0-d device tensors. img_u8 (B,H,W,3) uint8, mask_u8 (B,H,W) uint8 {0,1}."""

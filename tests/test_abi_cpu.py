@@ -1,0 +1,117 @@
+"""CPU-only checks of the drop-in boundary: libpdac_b200.so loads without a GPU, exports every symbol that
+include/pdac_b200.h declares (and the ctypes table binds the same set), rejects host pointers / missing devices with
+an error instead of falling back, and the Python modules keep the reference's constructor / state_dict contracts."""
+import ctypes
+import os
+import re
+import warnings
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "pdac_b200.h")
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as g
+    from pdac_pathological_image_segmentation_b200 import _lib
+    if not os.path.exists(_lib.LIB_PATH):
+        g.build()
+    return _lib.load()
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(pdac_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported_and_bound(lib):
+    from pdac_pathological_image_segmentation_b200 import _lib
+    names = _declared()
+    assert len(names) >= 40
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/pdac_b200.h but not exported by libpdac_b200.so"
+    bound = set(_lib.SIGNATURES) | {"pdac_version", "pdac_last_error"}
+    assert bound == set(names), f"ctypes table and header disagree: {bound ^ set(names)}"
+    assert lib.pdac_version() >= 100
+
+
+def test_struct_layouts_match_header():
+    from pdac_pathological_image_segmentation_b200._lib import PdacConv, PdacTap, PdacTapConv, PdacView
+    assert ctypes.sizeof(PdacView) == 8 + 4 * 4 + 3 * 8
+    assert ctypes.sizeof(PdacConv) == 8 * 4
+    assert ctypes.sizeof(PdacTap) == 12
+    assert ctypes.sizeof(PdacTapConv) == 16 + 16 * 12
+
+
+def test_no_cpu_fallback_at_the_abi(lib):
+    """Host pointers / no device: every compute entry returns an error code and a message (never computes)."""
+    from pdac_pathological_image_segmentation_b200._lib import PdacView
+    x = torch.zeros(1, 4, 4, 16, dtype=torch.bfloat16)
+    v = PdacView(x.data_ptr(), 1, 4, 4, 16, 256, 64, 16)
+    rc = lib.pdac_add(ctypes.byref(v), ctypes.byref(v), 0, ctypes.byref(v), None)
+    assert rc != 0
+    assert len(lib.pdac_last_error()) > 0
+    rc = lib.pdac_dice_fwd(None, None, 0, 0, None, ctypes.c_float(1e-6), None, None)
+    assert rc == -1 and b"null" in lib.pdac_last_error()
+
+
+def test_modules_refuse_cpu_tensors():
+    from pdac_pathological_image_segmentation_b200.resunet import ResUNet
+    from pdac_pathological_image_segmentation_b200.util import DiceLoss
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        m = ResUNet(1, 64)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        m(torch.zeros(1, 3, 64, 64))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        DiceLoss()(torch.zeros(4), torch.zeros(4))
+    with pytest.raises(RuntimeError, match="container"):
+        m.conv1(torch.zeros(1, 512, 4, 4))
+
+
+def test_state_dict_layouts_match_reference_and_smp_restatement():
+    from oracle import smp_oracle as S
+    from pdac_pathological_image_segmentation_b200 import smp as P
+    from pdac_pathological_image_segmentation_b200.resunet import ResUNet
+    gold = torch.load(os.path.join(ROOT, "tests", "golden", "state_keys.pt"), weights_only=False)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for nc in (1, 2):
+            m = ResUNet(nc, 512)
+            got = [(k, tuple(v.shape), str(v.dtype)) for k, v in m.state_dict().items()]
+            want = [(k, (nc,) + tuple(s[1:]) if k.startswith("conv4") else tuple(s), d) for k, s, d in gold]
+            assert got == want
+    pairs = [("unet_smp", "Unet", {})]
+    for extra in (("fpn", "FPN", {}), ("pspnet", "PSPNet", {"psp_use_batchnorm": True}),
+                  ("deeplabv3+", "DeepLabV3Plus", {"decoder_atrous_rates": (3, 6, 9)})):
+        if hasattr(P, extra[1]):
+            pairs.append(extra)
+    for oname, pname, kw in pairs:
+        ref = S.build(oname)
+        ours = getattr(P, pname)(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1,
+                                 activation=None, **kw)
+        assert [(k, tuple(v.shape), v.dtype) for k, v in ours.state_dict().items()] == \
+               [(k, tuple(v.shape), v.dtype) for k, v in ref.state_dict().items()], pname
+        ours.load_state_dict(ref.state_dict(), strict=True)
+
+
+def test_reference_constructor_calls_are_accepted():
+    """train_worker.py:150-182 / test.py:79-111 keyword sets."""
+    from pdac_pathological_image_segmentation_b200 import smp as P
+    with pytest.raises(RuntimeError, match="ImageNet"):
+        P.Unet(encoder_name="resnet18", encoder_weights="imagenet", in_channels=3, classes=1, activation=None)
+    with pytest.raises(ValueError):
+        P.Unet(encoder_name="resnet50", encoder_weights=None)
+    with pytest.raises(ValueError):
+        P.Unet(encoder_name="resnet18", encoder_weights=None, activation="sigmoid")
+
+
+def test_synthetic_generators_agree():
+    from oracle import resunet_oracle as R
+    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
+    a, b = R.synthetic_batch(2, 64, seed=5), synthetic_batch(2, 64, seed=5)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
