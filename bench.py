@@ -242,7 +242,7 @@ def run_ours(args):
     # ---- roofline of the dominant kernel group (CUDA events recorded on the launching stream, timed region 1) ----
     pk, pk_src = peaks()
     groups = {}
-    for name, a, b, fl, nb in trace:
+    for name, a, b, fl, nb, _tag in trace:
         kind = "wgrad_tc_kernel" if "wgrad" in name else "conv_tc_kernel"
         g = groups.setdefault(kind, [0.0, 0.0, 0.0, 0])
         g[0] += a.elapsed_time(b)

@@ -108,7 +108,7 @@ def load():
 trace = None  # bench.py sets this to a list: (name, start_event, end_event, flops, bytes) per traced call
 
 
-def call(name, *args, flops=0, nbytes=0):
+def call(name, *args, flops=0, nbytes=0, tag=""):
     """Calls a status-returning entry point; raises RuntimeError with the library's message on failure.
     flops / nbytes: algorithmic work of the call, recorded with CUDA events on the current stream when tracing."""
     global launches
@@ -119,7 +119,7 @@ def call(name, *args, flops=0, nbytes=0):
         e0.record()
         rc = getattr(lib, name)(*args)
         e1.record()
-        trace.append((name, e0, e1, flops, nbytes))
+        trace.append((name, e0, e1, flops, nbytes, tag))
     else:
         rc = getattr(lib, name)(*args)
     launches += 1

@@ -43,7 +43,7 @@ struct ConvKParams {
   int ck, ksub;   // channels per sub-tile, sub-tiles per pipeline stage (ck*ksub == 64)
   int wrows, block_n, stages;
   uint32_t tmem_cols, idesc, layout_type, pitch;
-  int tw_log2, th_log2, tiles_w, tiles_h;
+  int tw_log2, th_log2, tiles_w, tiles_h, tiles_c, total_tiles;
   int N, H, W, Cout;
   bf16* out;
   long long osN, osH, osW;
@@ -55,7 +55,9 @@ struct ConvKParams {
   int* err;
 };
 
-static constexpr int kThreads = 192;
+static constexpr int kEpiWG = 2;                  // epilogue warpgroups of conv_tc_kernel
+static constexpr int kThreads = 64 + kEpiWG * 128;  // conv_tc_kernel: TMA warp, MMA warp, 2 x 4 epilogue warps
+static constexpr int kWgradThreads = 192;
 static constexpr int kMaxStages = 8;
 
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
@@ -65,14 +67,19 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-__global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant__ TcMaps maps,
-                                                           const __grid_constant__ ConvKParams p) {
+// Persistent: one CTA per SM loops over output tiles (tile = n-tile fastest, then w, h, image group). The TMEM accumulator
+// is double buffered and the two epilogue warpgroups alternate tiles, so the TMA / MMA main loop of tile i+1 overlaps the
+// epilogue of tile i; barrier setup, TMEM allocation and descriptor prefetch are paid once per CTA; BatchNorm partial
+// sums live in registers across tiles and are flushed with one atomic per channel per CTA.
+__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_constant__ TcMaps maps,
+                                                              const __grid_constant__ ConvKParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
-  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ long long s_rowoff[128];
+  __shared__ long long s_rowoff[kEpiWG][128];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -83,23 +90,17 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   const int stage_bytes = a_stage + b_sub * p.ksub;
   const int total_sub = p.n_taps * (p.chunks[0] + (p.n_cat > 1 ? p.chunks[1] : 0));
   const int n_iters = (total_sub + p.ksub - 1) / p.ksub;
-
-  // tile coordinates
   const int TW = 1 << p.tw_log2, TH = 1 << p.th_log2;
-  int bx = blockIdx.x;
-  const int tile_w = bx % p.tiles_w;
-  bx /= p.tiles_w;
-  const int tile_h = bx % p.tiles_h;
-  const int tile_n = bx / p.tiles_h;
-  const int w0 = tile_w * TW, h0 = tile_h * TH, img0 = tile_n << (7 - p.tw_log2 - p.th_log2);
-  const int n0 = blockIdx.y * p.block_n;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < p.stages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    mbar_init(&tmem_full_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full_bar[i], 1);
+      mbar_init(&tmem_empty_bar[i], 128);
+    }
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -115,26 +116,41 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
+#define DECODE_TILE(tile)                                                         \
+  int bx_ = (tile);                                                               \
+  const int n_tile = bx_ % p.tiles_c;                                             \
+  bx_ /= p.tiles_c;                                                               \
+  const int tile_w = bx_ % p.tiles_w;                                             \
+  bx_ /= p.tiles_w;                                                               \
+  const int tile_h = bx_ % p.tiles_h;                                             \
+  const int tile_n = bx_ / p.tiles_h;                                             \
+  const int w0 = tile_w * TW, h0 = tile_h * TH, img0 = tile_n << (7 - p.tw_log2 - p.th_log2); \
+  const int n0 = n_tile * p.block_n;
+
   if (warp == 0) {
     if (lane == 0) {
-      int t = 0, s = 0, c = 0;
-      for (int it = 0; it < n_iters; ++it) {
-        const int stage = it % p.stages;
-        mbar_wait(&empty_bar[stage], ((it / p.stages) & 1) ^ 1, p.err);
-        const int nsub = min(p.ksub, total_sub - it * p.ksub);
-        mbar_expect_tx(&full_bar[stage], (uint32_t)(nsub * (a_sub + b_sub)));
-        uint8_t* a_dst = smem + (size_t)stage * stage_bytes;
-        uint8_t* b_dst = a_dst + a_stage;
-        for (int j = 0; j < nsub; ++j) {
-          const int mi = p.taps.map[t] + s;
-          tma_load_4d(a_dst + j * a_sub, &maps.a[mi], &full_bar[stage], c * p.ck, w0 + p.taps.dw[t],
-                      h0 + p.taps.dh[t], img0);
-          tma_load_2d(b_dst + j * b_sub, &maps.w, &full_bar[stage], (s ? p.c0 : 0) + c * p.ck, t * p.wrows + n0);
-          if (++c == p.chunks[s]) {
-            c = 0;
-            if (++s == p.n_cat) {
-              s = 0;
-              ++t;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        DECODE_TILE(tile)
+        int t = 0, s = 0, c = 0;
+        for (int k = 0; k < n_iters; ++k, ++it) {
+          const int stage = it % p.stages;
+          mbar_wait(&empty_bar[stage], ((it / p.stages) & 1) ^ 1, p.err);
+          const int nsub = min(p.ksub, total_sub - k * p.ksub);
+          mbar_expect_tx(&full_bar[stage], (uint32_t)(nsub * (a_sub + b_sub)));
+          uint8_t* a_dst = smem + (size_t)stage * stage_bytes;
+          uint8_t* b_dst = a_dst + a_stage;
+          for (int j = 0; j < nsub; ++j) {
+            const int mi = p.taps.map[t] + s;
+            tma_load_4d(a_dst + j * a_sub, &maps.a[mi], &full_bar[stage], c * p.ck, w0 + p.taps.dw[t],
+                        h0 + p.taps.dh[t], img0);
+            tma_load_2d(b_dst + j * b_sub, &maps.w, &full_bar[stage], (s ? p.c0 : 0) + c * p.ck, t * p.wrows + n0);
+            if (++c == p.chunks[s]) {
+              c = 0;
+              if (++s == p.n_cat) {
+                s = 0;
+                ++t;
+              }
             }
           }
         }
@@ -143,125 +159,156 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   } else if (warp == 1) {
     if (lane == 0) {
       const uint32_t sbo = 8 * p.pitch;
-      uint32_t accum = 0;
-      for (int it = 0; it < n_iters; ++it) {
-        const int stage = it % p.stages;
-        mbar_wait(&full_bar[stage], (it / p.stages) & 1, p.err);
+      int it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
+        const int as = lt & 1;
+        mbar_wait(&tmem_empty_bar[as], ((lt >> 1) & 1) ^ 1, p.err);
         tc_fence_after();
-        const int nsub = min(p.ksub, total_sub - it * p.ksub);
-        const uint32_t a_base = smem_u32(smem + (size_t)stage * stage_bytes);
-        const uint32_t b_base = a_base + a_stage;
-        for (int j = 0; j < nsub; ++j) {
-          for (int k = 0; k < p.ck / 16; ++k) {
-            const uint64_t da = make_smem_desc(a_base + j * a_sub + k * 32, 16, sbo, p.layout_type);
-            const uint64_t db = make_smem_desc(b_base + j * b_sub + k * 32, 16, sbo, p.layout_type);
-            umma_bf16(tmem_base, da, db, p.idesc, accum);
-            accum = 1;
+        const uint32_t tacc = tmem_base + (uint32_t)(as * p.block_n);
+        uint32_t accum = 0;
+        for (int k = 0; k < n_iters; ++k, ++it) {
+          const int stage = it % p.stages;
+          mbar_wait(&full_bar[stage], (it / p.stages) & 1, p.err);
+          tc_fence_after();
+          const int nsub = min(p.ksub, total_sub - k * p.ksub);
+          const uint32_t a_base = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t b_base = a_base + a_stage;
+          for (int j = 0; j < nsub; ++j) {
+            for (int kk = 0; kk < p.ck / 16; ++kk) {
+              const uint64_t da = make_smem_desc(a_base + j * a_sub + kk * 32, 16, sbo, p.layout_type);
+              const uint64_t db = make_smem_desc(b_base + j * b_sub + kk * 32, 16, sbo, p.layout_type);
+              umma_bf16(tacc, da, db, p.idesc, accum);
+              accum = 1;
+            }
           }
+          umma_commit(&empty_bar[stage]);
         }
-        umma_commit(&empty_bar[stage]);
+        umma_commit(&tmem_full_bar[as]);
       }
-      umma_commit(&tmem_full_bar);
     }
     __syncwarp();
   } else {
-    // ---------------- epilogue: warps 2..5, TMEM lane quarter = warp % 4
+    // ---------------- epilogue: two warpgroups (warps 2..5 and 6..9) alternate tiles; TMEM lane quarter = warp % 4
+    const int wg = (warp - 2) >> 2;
     const int q = warp & 3;
     const int m = q * 32 + lane;
-    const int e = threadIdx.x - 64;  // 0..127 cooperative index
+    const int e = (threadIdx.x - 64) & 127;  // cooperative index inside the warpgroup
+    const int spitch = p.block_n * 2 + 16;   // staging row pitch in bytes (padded against bank conflicts)
+    uint8_t* stg = smem + (size_t)p.stages * stage_bytes + (size_t)wg * 128 * spitch;
     const int tw = m & (TW - 1), th = (m >> p.tw_log2) & (TH - 1), tn = m >> (p.tw_log2 + p.th_log2);
-    const int w = w0 + tw, h = h0 + th, img = img0 + tn;
-    const bool valid = (w < p.W) && (h < p.H) && (img < p.N);
-    const long long ooff = (long long)img * p.osN + (long long)h * p.osH + (long long)w * p.osW;
-    const long long aoff = (long long)img * p.asN + (long long)h * p.asH + (long long)w * p.asW;
-    s_rowoff[m] = valid ? ooff : -1;
-    const int nch = min(p.block_n, p.Cout - n0);  // valid channels of this N tile
-    const int spitch = p.block_n * 2 + 16;        // staging row pitch in bytes (padded against bank conflicts)
-    uint8_t* stg = smem;
+    const uint32_t bar_id = 1 + wg;
+    // BatchNorm partial sums of this thread's channel pair, kept across tiles
+    const int pairs = p.block_n >> 1;
+    const int groups = 128 / pairs > 0 ? 128 / pairs : 1;
+    const int pr = e % pairs, sg = e / pairs;
+    const bool stat_thread = p.stats && sg < groups && pairs <= 128;
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    int stat_n0 = -1;
 
-    mbar_wait(&tmem_full_bar, 0, p.err);
-    tc_fence_after();
-    for (int c = 0; c < p.block_n; c += 16) {
-      uint32_t v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-      tmem_ld_wait();
-      float f[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-      if (p.bias) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-          if (c + i < nch) f[i] += __ldg(p.bias + n0 + c + i);
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
+      if ((lt & 1) != wg) continue;
+      DECODE_TILE(tile)
+      const int w = w0 + tw, h = h0 + th, img = img0 + tn;
+      const bool valid = (w < p.W) && (h < p.H) && (img < p.N);
+      const long long ooff = (long long)img * p.osN + (long long)h * p.osH + (long long)w * p.osW;
+      const long long aoff = (long long)img * p.asN + (long long)h * p.asH + (long long)w * p.asW;
+      const int nch = min(p.block_n, p.Cout - n0);  // valid channels of this N tile
+      if (stat_thread && stat_n0 != n0) {
+        if (stat_n0 >= 0 && 2 * pr < min(p.block_n, p.Cout - stat_n0)) {
+          float* st = p.stats + stat_n0 + 2 * pr;
+          atomicAdd(st, s0);
+          atomicAdd(st + 1, s1);
+          atomicAdd(st + p.Cout, q0);
+          atomicAdd(st + p.Cout + 1, q1);
+        }
+        s0 = s1 = q0 = q1 = 0.f;
+        stat_n0 = n0;
       }
-      if (p.addend && valid) {
-        const bf16* ap = p.addend + aoff + n0 + c;
-        if ((p.Cout & 7) == 0) {
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // previous tile's staging fully consumed
+      s_rowoff[wg][m] = valid ? ooff : -1;
+
+      mbar_wait(&tmem_full_bar[wg], (lt >> 1) & 1, p.err);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(wg * p.block_n);
+      for (int c = 0; c < p.block_n; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(tacc + (uint32_t)c, v);
+        tmem_ld_wait();
+        float f[16];
 #pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            if (c + hh * 8 < nch) {
-              const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + hh * 8));
-              const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                f[hh * 8 + 2 * i] += bf16lo(uu[i]);
-                f[hh * 8 + 2 * i + 1] += bf16hi(uu[i]);
-              }
-            }
-          }
-        } else {
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        if (p.bias) {
 #pragma unroll
           for (int i = 0; i < 16; ++i)
-            if (c + i < nch) f[i] += __bfloat162float(ap[i]);
+            if (c + i < nch) f[i] += __ldg(p.bias + n0 + c + i);
+        }
+        if (p.addend && valid) {
+          const bf16* ap = p.addend + aoff + n0 + c;
+          if ((p.Cout & 7) == 0) {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+              if (c + hh * 8 < nch) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + hh * 8));
+                const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  f[hh * 8 + 2 * i] += bf16lo(uu[i]);
+                  f[hh * 8 + 2 * i + 1] += bf16hi(uu[i]);
+                }
+              }
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (c + i < nch) f[i] += __bfloat162float(ap[i]);
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+        }
+        uint4 o0, o1;
+        o0.x = pack_bf16(f[0], f[1]);
+        o0.y = pack_bf16(f[2], f[3]);
+        o0.z = pack_bf16(f[4], f[5]);
+        o0.w = pack_bf16(f[6], f[7]);
+        o1.x = pack_bf16(f[8], f[9]);
+        o1.y = pack_bf16(f[10], f[11]);
+        o1.z = pack_bf16(f[12], f[13]);
+        o1.w = pack_bf16(f[14], f[15]);
+        uint4* sp = reinterpret_cast<uint4*>(stg + (size_t)m * spitch + c * 2);
+        sp[0] = o0;
+        sp[1] = o1;
+      }
+      // the accumulator stage is free for the MMA warp as soon as every thread has drained its TMEM lanes
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[wg]);
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+
+      // cooperative coalesced write-out
+      if ((p.Cout & 7) == 0) {
+        const int cpr = p.block_n >> 3;
+        const int cvalid = nch >> 3;
+        for (int id = e; id < 128 * cpr; id += 128) {
+          const int row = id / cpr, ch = id - row * cpr;
+          const long long off = s_rowoff[wg][row];
+          if (off < 0 || ch >= cvalid) continue;
+          const uint4 val = *reinterpret_cast<const uint4*>(stg + (size_t)row * spitch + ch * 16);
+          *reinterpret_cast<uint4*>(p.out + off + n0 + ch * 8) = val;
+        }
+      } else {
+        for (int id = e; id < 128 * nch; id += 128) {
+          const int row = id / nch, ch = id - row * nch;
+          const long long off = s_rowoff[wg][row];
+          if (off < 0) continue;
+          p.out[off + n0 + ch] = *reinterpret_cast<const bf16*>(stg + (size_t)row * spitch + ch * 2);
         }
       }
-      if (p.relu) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
-      }
-      uint4 o0, o1;
-      o0.x = pack_bf16(f[0], f[1]);
-      o0.y = pack_bf16(f[2], f[3]);
-      o0.z = pack_bf16(f[4], f[5]);
-      o0.w = pack_bf16(f[6], f[7]);
-      o1.x = pack_bf16(f[8], f[9]);
-      o1.y = pack_bf16(f[10], f[11]);
-      o1.z = pack_bf16(f[12], f[13]);
-      o1.w = pack_bf16(f[14], f[15]);
-      uint4* sp = reinterpret_cast<uint4*>(stg + (size_t)m * spitch + c * 2);
-      sp[0] = o0;
-      sp[1] = o1;
-    }
-    tc_fence_before();
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-
-    // cooperative coalesced write-out
-    if ((p.Cout & 7) == 0) {
-      const int cpr = p.block_n >> 3;
-      const int cvalid = nch >> 3;
-      for (int id = e; id < 128 * cpr; id += 128) {
-        const int row = id / cpr, ch = id - row * cpr;
-        const long long off = s_rowoff[row];
-        if (off < 0 || ch >= cvalid) continue;
-        const uint4 val = *reinterpret_cast<const uint4*>(stg + (size_t)row * spitch + ch * 16);
-        *reinterpret_cast<uint4*>(p.out + off + n0 + ch * 8) = val;
-      }
-    } else {
-      for (int id = e; id < 128 * nch; id += 128) {
-        const int row = id / nch, ch = id - row * nch;
-        const long long off = s_rowoff[row];
-        if (off < 0) continue;
-        p.out[off + n0 + ch] = *reinterpret_cast<const bf16*>(stg + (size_t)row * spitch + ch * 2);
-      }
-    }
-    // per-channel sum / sum of squares of the stored values (BatchNorm batch statistics)
-    if (p.stats && (nch & 1) == 0) {
-      const int pairs = p.block_n >> 1;
-      const int groups = 128 / pairs > 0 ? 128 / pairs : 1;
-      const int pr = e % pairs, g = e / pairs;
-      if (g < groups && pairs <= 128 && 2 * pr < nch) {
-        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-        for (int row = g; row < 128; row += groups) {
-          if (s_rowoff[row] < 0) continue;
+      // per-channel sum / sum of squares of the stored values (BatchNorm batch statistics)
+      if (stat_thread && (nch & 1) == 0 && 2 * pr < nch) {
+        for (int row = sg; row < 128; row += groups) {
+          if (s_rowoff[wg][row] < 0) continue;
           const uint32_t u = *reinterpret_cast<const uint32_t*>(stg + (size_t)row * spitch + pr * 4);
           const float x0 = bf16lo(u), x1 = bf16hi(u);
           s0 += x0;
@@ -269,14 +316,17 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
           s1 += x1;
           q1 += x1 * x1;
         }
-        float* st = p.stats + n0 + 2 * pr;
-        atomicAdd(st, s0);
-        atomicAdd(st + 1, s1);
-        atomicAdd(st + p.Cout, q0);
-        atomicAdd(st + p.Cout + 1, q1);
       }
     }
+    if (stat_thread && stat_n0 >= 0 && 2 * pr < min(p.block_n, p.Cout - stat_n0)) {
+      float* st = p.stats + stat_n0 + 2 * pr;
+      atomicAdd(st, s0);
+      atomicAdd(st + 1, s1);
+      atomicAdd(st + p.Cout, q0);
+      atomicAdd(st + p.Cout + 1, q1);
+    }
   }
+#undef DECODE_TILE
 
   tc_fence_before();
   __syncthreads();
@@ -305,7 +355,7 @@ struct WgradKParams {
   int* err;
 };
 
-__global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constant__ TcMaps maps,
+__global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_constant__ TcMaps maps,
                                                             const __grid_constant__ WgradKParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t fullA[kMaxStages];
@@ -552,10 +602,11 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
   p.pitch = ck * 2;
   p.layout_type = swizzle_layout_type(p.pitch);
   p.idesc = make_idesc_bf16(128, block_n, 0, 0);
-  p.tmem_cols = pow2_ceil(block_n < 32 ? 32 : block_n);
+  p.tmem_cols = pow2_ceil(2 * block_n < 32 ? 32 : 2 * block_n);  // double-buffered accumulator
   const int stage_bytes = 128 * 128 + block_n * 128;
-  int stages = (96 * 1024) / stage_bytes;
-  if (stages > 6) stages = 6;
+  const int staging = kEpiWG * 128 * (block_n * 2 + 16);
+  int stages = (200 * 1024 - staging) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) stages = 2;
   p.stages = stages;
   const Tiling tl = pick_tiling(out->N, out->H, out->W);
@@ -595,17 +646,17 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
     uint32_t box[2] = {(uint32_t)ck, (uint32_t)block_n};
     PDAC_TRY(encode_tiled_bf16(&maps.w, w_packed, 2, dims, strides, box, p.pitch));
   }
-  int staging = 128 * (block_n * 2 + 16);
-  size_t smem = (size_t)stages * stage_bytes;
-  if (smem < (size_t)staging) smem = staging;
-  smem += 1024;
-  static size_t attr_set = 0;
-  if (smem > attr_set) {
-    PDAC_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024)));
-    attr_set = 200 * 1024;
+  p.tiles_c = ceil_div(cout, block_n);
+  p.total_tiles = tl.tiles_w * tl.tiles_h * tl.tiles_n * p.tiles_c;
+  size_t smem = (size_t)stages * stage_bytes + staging + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PDAC_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(210 * 1024)));
+    attr_set = true;
   }
-  dim3 grid(tl.tiles_w * tl.tiles_h * tl.tiles_n, ceil_div(cout, block_n), 1);
-  conv_tc_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(maps, p);
+  int ctas = num_sms();
+  if (ctas > p.total_tiles) ctas = p.total_tiles;
+  conv_tc_kernel<<<ctas, kThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_tc_kernel");
   return PDAC_OK;
 }
@@ -682,7 +733,7 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
     attr_set = true;
   }
   dim3 grid(splits, y, z);
-  wgrad_tc_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(maps, p);
+  wgrad_tc_kernel<<<grid, kWgradThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_tc_kernel");
   return PDAC_OK;
 }

@@ -90,7 +90,8 @@ def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=No
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
     call("pdac_conv2d_fwd", C.byref(cv), len(srcs), views, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
          _stream(), flops=2 * x0.shape[0] * ho * wo * (c_real or cout) * ktot * R * S,
-         nbytes=_act_bytes(out, addend, *srcs))
+         nbytes=_act_bytes(out, addend, *srcs),
+         tag=f"fwd {R}x{S}s{stride}d{dil} {x0.shape[0]}x{ho}x{wo} {ktot}->{cout}")
     return out
 
 
@@ -103,7 +104,8 @@ def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None,
     cv = _conv_struct(R, S, stride, pad, dil, False, wrows)
     call("pdac_conv2d_dgrad", C.byref(cv), _vp(dy), _ptr(wpt), _vp(addend), _vp(out), _stream(),
          flops=2 * dy.shape[0] * dy.shape[1] * dy.shape[2] * (c_real or dy.shape[3]) * cin * R * S,
-         nbytes=_act_bytes(dy, out, addend))
+         nbytes=_act_bytes(dy, out, addend),
+         tag=f"dgrad {R}x{S}s{stride}d{dil} {dy.shape[0]}x{dy.shape[1]}x{dy.shape[2]} {dy.shape[3]}->{cin}")
     return out
 
 
@@ -118,7 +120,8 @@ def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None, oihw=False, c
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
     call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), int(bool(oihw)), _stream(),
          flops=2 * dy.shape[0] * dy.shape[1] * dy.shape[2] * (cout_valid or dy.shape[3]) * ktot * R * S,
-         nbytes=_act_bytes(dy, *srcs))
+         nbytes=_act_bytes(dy, *srcs),
+         tag=f"wgrad {R}x{S}s{stride}d{dil} {dy.shape[0]}x{dy.shape[1]}x{dy.shape[2]} {ktot}->{dy.shape[3]}")
     return out
 
 
