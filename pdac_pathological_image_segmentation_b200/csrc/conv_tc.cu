@@ -560,6 +560,9 @@ static int fill_taps(const PdacTapConv* tc, int n_views, const PdacView* views, 
   return PDAC_OK;
 }
 
+int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed, const float* bias,
+                  const PdacView* addend, const PdacView* out, float* stats, void* stream, int* handled);
+
 static int check_dev_ptr(const void* p, const char* what) {
   cudaPointerAttributes at;
   cudaError_t e = cudaPointerGetAttributes(&at, p);
@@ -582,6 +585,12 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
   ConvKParams p;
   memset(&p, 0, sizeof(p));
   PDAC_TRY(fill_taps(tc, n_views, views, out, &p.taps));
+  {
+    // stride-1 multi-tap convolutions whose taps share one source lattice take the halo-tile kernel (conv_halo.cu)
+    int handled = 0;
+    PDAC_TRY(conv_halo_try(tc, n_views, views, w_packed, bias, addend, out, stats, stream, &handled));
+    if (handled) return PDAC_OK;
+  }
   const PdacView* v0 = views + tc->taps[0].src;
   const int ck = pick_ck(tc->n_cat, v0);
   PDAC_REQUIRE(ck >= 16, "input channels must be multiples of 16 (got %d%s)", v0[0].C, tc->n_cat > 1 ? " + cat" : "");

@@ -48,6 +48,20 @@ FWD_CASES = [
     (2, 16, 16, [304], 256, 1, 1, 0, 1, False, False, False),
     (1, 16, 16, [512], 512, 3, 1, 1, 1, False, False, False),
     (2, 16, 16, [64], 48, 1, 1, 0, 1, False, False, False),
+    # halo-tile kernel (conv_halo.cu): many tiles per image, partial tiles, every swizzle width, resident and
+    # streamed weights, concatenated sources, several N tiles, dilation, fused addend/bias/ReLU
+    (2, 96, 80, [16], 16, 3, 1, 1, 1, True, True, False),
+    (1, 128, 128, [32], 16, 3, 1, 1, 1, False, False, True),
+    (2, 70, 66, [64], 64, 3, 1, 1, 1, False, False, False),
+    (1, 64, 64, [64, 64], 32, 3, 1, 1, 1, True, False, False),
+    (1, 64, 64, [32], 128, 3, 1, 1, 1, False, False, True),
+    (1, 48, 48, [128], 128, 3, 1, 1, 1, False, True, False),
+    (1, 32, 32, [256, 128], 128, 3, 1, 1, 1, True, False, False),
+    (1, 32, 32, [64], 192, 3, 1, 1, 1, False, False, False),
+    (1, 32, 32, [256], 256, 3, 1, 1, 1, False, False, True),
+    (1, 40, 40, [128], 64, 3, 1, 3, 3, False, False, False),
+    (1, 33, 47, [512], 256, 3, 1, 2, 2, False, False, False),
+    (3, 256, 256, [16], 16, 3, 1, 1, 1, False, False, False),
 ]
 
 
