@@ -28,11 +28,15 @@ struct HaloMaps {
 
 struct HaloParams {
   int n_taps, n_chunks, chunks0, ck;
-  int tap_shift[PDAC_MAX_TAPS];  // (dh - dh_min) * PW + (dw - dw_min), in pixel rows of the halo buffer
+  // taps form an affine grid: tap t = r * tap_S + s reads the halo tap_base + r * tap_step_r + s * tap_step_s pixel rows
+  // further on ((dh - dh_min) * PW + (dw - dw_min))
+  int tap_R, tap_S, tap_base, tap_step_r, tap_step_s;
   int dh_min, dw_min;
   uint32_t pitch, layout_type, idesc, tmem_cols;
   int block_n, tiles_c, wrows;
   int nacc, TW, TH, PW, R;
+  uint32_t inv_pw;  // ceil(2^20 / PW): o / PW == (o * inv_pw) >> 20 for o < 1024
+  int n_wg;         // epilogue warpgroups in use (2 or 4)
   int tiles_w, tiles_h, tiles_sp;  // spatial tiles per image row / column, total over the batch
   int a_buf, sa;                   // bytes per halo stage, stages
   int b_resident, sb, b_sub;       // weights resident? else ring stages; bytes per (tap, chunk) weight tile
@@ -47,17 +51,44 @@ struct HaloParams {
   int* err;
 };
 
-static constexpr int kHaloThreads = 352;
-static constexpr int kHaloMaxSA = 6;
+static constexpr int kHaloThreads = 64 + 4 * 128 + 32;  // TMA warp, MMA warp, up to 4 epilogue warpgroups, weight warp
+static constexpr int kHaloMaxSA = 12;
 static constexpr int kHaloMaxSB = 8;
 
 __device__ __forceinline__ float h_bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float h_bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned short lds16(uint32_t addr) {
+  unsigned short v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ uint32_t h_pack(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// The NACC x KS MMAs of one (tap, channel chunk): accumulator j reads the halo 128 pixel rows further on.
+template <int NACC, int KS>
+__device__ __forceinline__ void halo_issue(uint32_t tacc, uint32_t acc_step, uint32_t a_lo, uint32_t j_step, uint32_t b_lo,
+                                           uint32_t desc_hi, uint32_t idesc, uint32_t acc) {
+#pragma unroll
+  for (int j = 0; j < NACC; ++j) {
+#pragma unroll
+    for (int kk = 0; kk < KS; ++kk)  // +2 in the 16-byte-unit address field = 16 bf16 along K
+      umma_bf16_lohi(tacc + (uint32_t)j * acc_step, a_lo + (uint32_t)j * j_step + 2 * kk, desc_hi, b_lo + 2 * kk, desc_hi,
+                     idesc, kk ? 1u : acc);
+  }
+}
+
+template <int NACC, int KS>
 __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid_constant__ HaloMaps maps,
                                                                     const __grid_constant__ HaloParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -68,7 +99,8 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
-  __shared__ long long s_rowoff[2][128];
+  __shared__ long long s_rowoff[4][128];
+  __shared__ float s_stats[256];  // per-CTA BatchNorm partial sums: [0..127] sum, [128..255] sum of squares
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -95,10 +127,11 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full_bar[i], 1);
-      mbar_init(&tmem_empty_bar[i], 256);
+      mbar_init(&tmem_empty_bar[i], 128 * p.n_wg);
     }
     fence_barrier_init();
   }
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + 256) s_stats[threadIdx.x - 64] = 0.f;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.a[0]);
     tma_prefetch_desc(&maps.w);
@@ -137,7 +170,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
         }
       }
     }
-  } else if (warp == 10) {
+  } else if (warp == 18) {
     // ------------------------------------------------------------------ weight producer
     if (lane == 0 && sp0 < sp_step) {
       if (p.b_resident) {
@@ -162,72 +195,99 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && sp0 < sp_step) {
-      const uint32_t sbo = 8 * p.pitch;
-      const int ksteps = p.ck >> 4;
+    // The whole warp walks the loops (warp-uniform control flow: descriptors and TMEM addresses live in uniform
+    // registers); one elected lane issues. Measured (scripts/probe/mma_rate.cu): one M=128 K=16 MMA executes in
+    // ~32 + N/4 cycles, so the issue path must stay well below ~40 cycles per instruction: the (accumulator, k-step)
+    // block is compile-time unrolled and the taps are walked as an affine (r, s) grid with no table look-ups.
+    if (sp0 < sp_step) {
+      const uint32_t leader = elect_one();
+      const uint32_t idesc = p.idesc;
+      const uint32_t desc_hi = (uint32_t)(make_smem_desc(0, 16, 8 * p.pitch, p.layout_type) >> 32);
+      const uint32_t lbo_lo = (16u >> 4) << 16;
       if (p.b_resident) {
         mbar_wait(&full_b[0], 0, p.err);
         tc_fence_after();
       }
-      const uint32_t b_base0 = smem_u32(smem_b);
+      const uint32_t pix16 = p.pitch >> 4;  // 16-byte units per halo pixel row
+      const uint32_t b_lo0 = (smem_u32(smem_b) >> 4) | lbo_lo;
+      const uint32_t a_lo0 = (smem_u32(smem_a) >> 4) | lbo_lo;
+      const uint32_t a_buf16 = (uint32_t)p.a_buf >> 4, b_sub16 = (uint32_t)p.b_sub >> 4;
+      const uint32_t acc_step = (uint32_t)p.block_n;
+      const uint32_t j_step = 128u * pix16;
+      const uint32_t tap0 = (uint32_t)p.tap_base * pix16;
+      const uint32_t step_r = (uint32_t)(p.tap_step_r * (int)pix16), step_s = (uint32_t)(p.tap_step_s * (int)pix16);
+      const int TR = p.tap_R, TS = p.tap_S, n_chunks = p.n_chunks, sa = p.sa, sb = p.sb;
+      const uint32_t b_tap16 = (uint32_t)n_chunks * b_sub16;
       int ita = 0, itb = 0, lt = 0;
       for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt) {
         const int g = lt & 1;
         mbar_wait(&tmem_empty_bar[g], ((lt >> 1) & 1) ^ 1, p.err);
         tc_fence_after();
-        const uint32_t tacc = tmem_base + (uint32_t)(g * p.nacc * p.block_n);
-        for (int c = 0; c < p.n_chunks; ++c, ++ita) {
-          const int stage = ita % p.sa;
-          mbar_wait(&full_a[stage], (ita / p.sa) & 1, p.err);
+        const uint32_t tacc = tmem_base + (uint32_t)(g * NACC) * acc_step;
+        for (int c = 0; c < n_chunks; ++c, ++ita) {
+          const int stage = ita % sa;
+          mbar_wait(&full_a[stage], (ita / sa) & 1, p.err);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(smem_a + (size_t)stage * p.a_buf);
-          for (int t = 0; t < p.n_taps; ++t) {
-            uint32_t b_base;
-            int bstage = 0;
-            if (p.b_resident) {
-              b_base = b_base0 + (uint32_t)((t * p.n_chunks + c) * p.b_sub);
-            } else {
-              bstage = itb % p.sb;
-              mbar_wait(&full_b[bstage], (itb / p.sb) & 1, p.err);
-              tc_fence_after();
-              b_base = b_base0 + (uint32_t)(bstage * p.b_sub);
+          const uint32_t a_stage = a_lo0 + (uint32_t)stage * a_buf16 + tap0;
+          if (p.b_resident) {
+            if (leader) {
+              uint32_t b_lo = b_lo0 + (uint32_t)c * b_sub16;
+              uint32_t acc = c ? 1u : 0u;
+              uint32_t a_row = a_stage;
+              for (int r = 0; r < TR; ++r, a_row += step_r) {
+                uint32_t a_lo = a_row;
+                for (int s = 0; s < TS; ++s, a_lo += step_s, b_lo += b_tap16) {
+                  halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo, desc_hi, idesc, acc);
+                  acc = 1u;
+                }
+              }
+              umma_commit(&empty_a[stage]);
             }
-            const uint64_t db0 = make_smem_desc(b_base, 16, sbo, p.layout_type);
-            const uint32_t a_tap = a_base + (uint32_t)p.tap_shift[t] * p.pitch;
-            for (int j = 0; j < p.nacc; ++j) {
-              const uint64_t da0 = make_smem_desc(a_tap + (uint32_t)(j * 128) * p.pitch, 16, sbo, p.layout_type);
-              for (int kk = 0; kk < ksteps; ++kk) {
-                // +2 in the 16-byte-unit address field = +32 bytes = 16 bf16 along K
-                umma_bf16(tacc + (uint32_t)(j * p.block_n), da0 + (uint64_t)(2 * kk), db0 + (uint64_t)(2 * kk), p.idesc,
-                          (c | t | kk) ? 1u : 0u);
+          } else {
+            uint32_t acc = c ? 1u : 0u;
+            uint32_t a_row = a_stage;
+            for (int r = 0; r < TR; ++r, a_row += step_r) {
+              uint32_t a_lo = a_row;
+              for (int s = 0; s < TS; ++s, a_lo += step_s, ++itb) {
+                const int bstage = itb % sb;
+                mbar_wait(&full_b[bstage], (itb / sb) & 1, p.err);
+                tc_fence_after();
+                if (leader) {
+                  halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo0 + (uint32_t)bstage * b_sub16, desc_hi, idesc,
+                                       acc);
+                  umma_commit(&empty_b[bstage]);
+                }
+                acc = 1u;
               }
             }
-            if (!p.b_resident) {
-              umma_commit(&empty_b[bstage]);
-              ++itb;
-            }
+            if (leader) umma_commit(&empty_a[stage]);
           }
-          umma_commit(&empty_a[stage]);
         }
-        umma_commit(&tmem_full_bar[g]);
+        if (leader) umma_commit(&tmem_full_bar[g]);
+        __syncwarp();
       }
     }
     __syncwarp();
-  } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..9)
+  } else if (warp - 2 < 4 * p.n_wg) {
+    // ------------------------------------------------------------------ epilogue (n_wg warpgroups, warps 2..)
+    // Accumulators are dealt round-robin to the warpgroups (global accumulator index % n_wg). Per accumulator and per
+    // 64-column pass: TMEM -> registers -> bias/addend/ReLU -> bf16 -> staging (invalid rows as zeros), then each
+    // thread walks a fixed 8-channel column of the staging tile: 16-byte coalesced stores + BatchNorm partial sums
+    // kept in registers for the whole kernel.
     const int wg = (warp - 2) >> 2;
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     const int m = q * 32 + lane;
     const int e = (threadIdx.x - 64) & 127;
-    const int spitch = p.block_n * 2 + 16;
-    uint8_t* stg = smem_stg + (size_t)wg * 128 * spitch;
+    const int sc = p.block_n < 64 ? p.block_n : 64;  // staging columns per pass
+    const int spitch = sc * 2 + 16;
+    const uint32_t stg = smem_u32(smem_stg) + (uint32_t)(wg * 128 * spitch);
+    const uint32_t my_row = stg + (uint32_t)(m * spitch);
     const uint32_t bar_id = 1 + wg;
     const int nch = min(p.block_n, p.Cout - n0);
-    const int pairs = p.block_n >> 1;
-    const int groups = 128 / pairs > 0 ? 128 / pairs : 1;
-    const int pr = e % pairs, sg = e / pairs;
-    const bool stat_thread = p.stats && sg < groups && pairs <= 128 && (nch & 1) == 0 && 2 * pr < nch;
-    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    const bool vec = (p.Cout & 7) == 0;
+    float acc[2][16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[0][i] = acc[1][i] = 0.f;
 
     int lt = 0;
     if (sp0 < sp_step)
@@ -236,121 +296,159 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
         const int g = lt & 1;
         mbar_wait(&tmem_full_bar[g], (lt >> 1) & 1, p.err);
         tc_fence_after();
-        for (int j = wg; j < p.nacc; j += 2) {
+        const long long obase = (long long)img * p.osN + (long long)h0 * p.osH + (long long)w0 * p.osW;
+        const long long abase = (long long)img * p.asN + (long long)h0 * p.asH + (long long)w0 * p.asW;
+        int j = (wg - (lt * p.nacc) % p.n_wg + p.n_wg) % p.n_wg;
+        if (j >= p.nacc) {  // nothing of this tile is ours: the TMEM stage is free as far as we are concerned
+          tc_fence_before();
+          mbar_arrive(&tmem_empty_bar[g]);
+        }
+        for (; j < p.nacc; j += p.n_wg) {
           const int o = j * 128 + m;
-          const int th = o / p.PW, tw = o - th * p.PW;
-          const int w = w0 + tw, h = h0 + th;
-          const bool valid = (tw < p.TW) && (th < p.TH) && (w < p.W) && (h < p.H);
-          const long long ooff = (long long)img * p.osN + (long long)h * p.osH + (long long)w * p.osW;
-          const long long aoff = (long long)img * p.asN + (long long)h * p.asH + (long long)w * p.asW;
+          const int th = (int)(((uint32_t)o * p.inv_pw) >> 20), tw = o - th * p.PW;
+          const bool valid = (tw < p.TW) && (th < p.TH) && (w0 + tw < p.W) && (h0 + th < p.H);
+          const long long ooff = obase + (long long)th * p.osH + (long long)tw * p.osW;
+          const bf16* arow = p.addend + abase + (long long)th * p.asH + (long long)tw * p.asW + n0;
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // previous staging fully consumed
           s_rowoff[wg][m] = valid ? ooff : -1;
           const uint32_t tacc =
               tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
-          for (int c = 0; c < p.block_n; c += 16) {
-            uint32_t v[16];
-            tmem_ld16(tacc + (uint32_t)c, v);
-            tmem_ld_wait();
-            float f[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-            if (p.bias) {
+          for (int pass = 0; pass < 2; ++pass) {
+            const int c0 = pass * 64;
+            if (c0 < p.block_n) {
+              const int cols = min(64, p.block_n - c0);
+              if (pass) asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+              for (int c = 0; c < cols; c += 16) {
+                uint32_t v[16];
+                tmem_ld16(tacc + (uint32_t)(c0 + c), v);
+                tmem_ld_wait();
+                float f[16];
 #pragma unroll
-              for (int i = 0; i < 16; ++i)
-                if (c + i < nch) f[i] += __ldg(p.bias + n0 + c + i);
-            }
-            if (p.addend && valid) {
-              const bf16* ap = p.addend + aoff + n0 + c;
-              if ((p.Cout & 7) == 0) {
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+                if (p.bias) {
 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                  if (c + hh * 8 < nch) {
-                    const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + hh * 8));
-                    const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+                  for (int i = 0; i < 16; ++i)
+                    if (c0 + c + i < nch) f[i] += __ldg(p.bias + n0 + c0 + c + i);
+                }
+                if (p.addend && valid) {
+                  const bf16* ap = arow + c0 + c;
+                  if (vec) {
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                      if (c0 + c + hh * 8 < nch) {
+                        const uint4 u = __ldg(reinterpret_cast<const uint4*>(ap + hh * 8));
+                        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                          f[hh * 8 + 2 * i] += h_bf16lo(uu[i]);
+                          f[hh * 8 + 2 * i + 1] += h_bf16hi(uu[i]);
+                        }
+                      }
+                    }
+                  } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                      if (c0 + c + i < nch) f[i] += __bfloat162float(ap[i]);
+                  }
+                }
+                if (p.relu) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+                }
+                if (!valid) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) f[i] = 0.f;
+                }
+                sts128(my_row + (uint32_t)(c * 2), h_pack(f[0], f[1]), h_pack(f[2], f[3]), h_pack(f[4], f[5]),
+                       h_pack(f[6], f[7]));
+                sts128(my_row + (uint32_t)(c * 2 + 16), h_pack(f[8], f[9]), h_pack(f[10], f[11]),
+                       h_pack(f[12], f[13]), h_pack(f[14], f[15]));
+              }
+              if (c0 + 64 >= p.block_n && j + p.n_wg >= p.nacc) {
+                // last TMEM read of this warpgroup in this tile
+                tc_fence_before();
+                mbar_arrive(&tmem_empty_bar[g]);
+              }
+              asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+              if (vec) {
+                // thread -> fixed 8-channel column `ch`, rows row0, row0 + step, ...
+                const int cpr_log2 = cols == 64 ? 3 : (cols == 32 ? 2 : 1);
+                const int ch = e & ((1 << cpr_log2) - 1);
+                const int step = 128 >> cpr_log2;
+                const bool ch_ok = c0 + ch * 8 < nch;
+                bf16* gcol = p.out + n0 + c0 + ch * 8;
+                uint32_t saddr = stg + (uint32_t)((e >> cpr_log2) * spitch + ch * 16);
+                const uint32_t sstep = (uint32_t)(step * spitch);
+                int row = e >> cpr_log2;
+#pragma unroll 2
+                for (int it = 0; it < (1 << cpr_log2); ++it, row += step, saddr += sstep) {
+                  const long long off = s_rowoff[wg][row];
+                  const uint4 val = lds128(saddr);
+                  if (off >= 0 && ch_ok) *reinterpret_cast<uint4*>(gcol + off) = val;
+                  if (p.stats) {
+                    const uint32_t uu[4] = {val.x, val.y, val.z, val.w};
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                      f[hh * 8 + 2 * i] += h_bf16lo(uu[i]);
-                      f[hh * 8 + 2 * i + 1] += h_bf16hi(uu[i]);
+                      const float x0 = h_bf16lo(uu[i]), x1 = h_bf16hi(uu[i]);
+                      acc[pass][2 * i] += x0;
+                      acc[pass][2 * i + 1] += x1;
+                      acc[pass][8 + 2 * i] = fmaf(x0, x0, acc[pass][8 + 2 * i]);
+                      acc[pass][8 + 2 * i + 1] = fmaf(x1, x1, acc[pass][8 + 2 * i + 1]);
                     }
                   }
                 }
               } else {
-#pragma unroll
-                for (int i = 0; i < 16; ++i)
-                  if (c + i < nch) f[i] += __bfloat162float(ap[i]);
+                // channel count not a multiple of 8 (1-class logit heads): scalar stores, no statistics
+                const int nv = min(cols, nch - c0);
+                for (int id = e; id < 128 * nv; id += 128) {
+                  const int row = id / nv, chn = id - row * nv;
+                  const long long off = s_rowoff[wg][row];
+                  if (off < 0) continue;
+                  p.out[off + n0 + c0 + chn] = __ushort_as_bfloat16(lds16(stg + (uint32_t)(row * spitch + chn * 2)));
+                }
               }
             }
-            if (p.relu) {
-#pragma unroll
-              for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
-            }
-            uint4 o0, o1;
-            o0.x = h_pack(f[0], f[1]);
-            o0.y = h_pack(f[2], f[3]);
-            o0.z = h_pack(f[4], f[5]);
-            o0.w = h_pack(f[6], f[7]);
-            o1.x = h_pack(f[8], f[9]);
-            o1.y = h_pack(f[10], f[11]);
-            o1.z = h_pack(f[12], f[13]);
-            o1.w = h_pack(f[14], f[15]);
-            uint4* sp4 = reinterpret_cast<uint4*>(stg + (size_t)m * spitch + c * 2);
-            sp4[0] = o0;
-            sp4[1] = o1;
           }
-          if (j + 2 >= p.nacc) {
-            // last accumulator of this warpgroup for the tile: its TMEM lanes are drained
-            tc_fence_before();
-            mbar_arrive(&tmem_empty_bar[g]);
-          }
-          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
-
-          if ((p.Cout & 7) == 0) {
-            const int cpr = p.block_n >> 3;
-            const int cvalid = nch >> 3;
-            for (int id = e; id < 128 * cpr; id += 128) {
-              const int row = id / cpr, ch = id - row * cpr;
-              const long long off = s_rowoff[wg][row];
-              if (off < 0 || ch >= cvalid) continue;
-              const uint4 val = *reinterpret_cast<const uint4*>(stg + (size_t)row * spitch + ch * 16);
-              *reinterpret_cast<uint4*>(p.out + off + n0 + ch * 8) = val;
-            }
-          } else {
-            for (int id = e; id < 128 * nch; id += 128) {
-              const int row = id / nch, ch = id - row * nch;
-              const long long off = s_rowoff[wg][row];
-              if (off < 0) continue;
-              p.out[off + n0 + ch] = *reinterpret_cast<const bf16*>(stg + (size_t)row * spitch + ch * 2);
-            }
-          }
-          if (stat_thread) {
-            for (int row = sg; row < 128; row += groups) {
-              if (s_rowoff[wg][row] < 0) continue;
-              const uint32_t u = *reinterpret_cast<const uint32_t*>(stg + (size_t)row * spitch + pr * 4);
-              const float x0 = h_bf16lo(u), x1 = h_bf16hi(u);
-              s0 += x0;
-              q0 += x0 * x0;
-              s1 += x1;
-              q1 += x1 * x1;
-            }
-          }
-        }
-        if (wg >= p.nacc) {  // a warpgroup with no accumulator in this tile still owes its arrivals
-          tc_fence_before();
-          mbar_arrive(&tmem_empty_bar[g]);
         }
       }
-    if (stat_thread) {
-      float* st = p.stats + n0 + 2 * pr;
-      atomicAdd(st, s0);
-      atomicAdd(st + 1, s1);
-      atomicAdd(st + p.Cout, q0);
-      atomicAdd(st + p.Cout + 1, q1);
+    // BatchNorm partial sums: lanes sharing a channel column -> one lane per column -> shared -> (after the final
+    // CTA barrier) one global atomic per channel and CTA
+    if (p.stats && vec) {
+#pragma unroll
+      for (int pass = 0; pass < 2; ++pass) {
+        const int c0 = pass * 64;
+        if (c0 < p.block_n) {
+          const int cols = min(64, p.block_n - c0);
+          const int cpr = cols >> 3;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float v = acc[pass][i];
+            for (int o = 16; o >= cpr; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            acc[pass][i] = v;
+          }
+          if (lane < cpr) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int chn = c0 + lane * 8 + i;
+              if (chn < nch) {
+                atomicAdd(&s_stats[chn], acc[pass][i]);
+                atomicAdd(&s_stats[128 + chn], acc[pass][8 + i]);
+              }
+            }
+          }
+        }
+      }
     }
   }
 #undef HALO_DECODE
 
   tc_fence_before();
   __syncthreads();
+  if (p.stats && (int)threadIdx.x < 2 * p.block_n) {
+    const int which = threadIdx.x >= p.block_n, chn = threadIdx.x - which * p.block_n;
+    if (chn < min(p.block_n, p.Cout - n0)) atomicAdd(p.stats + which * p.Cout + n0 + chn, s_stats[which * 128 + chn]);
+  }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
@@ -359,10 +457,10 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
 
 // ------------------------------------------------------------------------------------------------ host side
 
-static const int kSmemBudget = 224 * 1024;  // dynamic shared memory we allow ourselves (227 KB max per CTA incl. static)
+static const int kSmemBudget = 221 * 1024;  // dynamic shared memory we allow ourselves (227 KB max per CTA incl. static)
 
 struct HaloPlan {
-  int TW, TH, nacc, sa, sb, b_resident;
+  int TW, TH, nacc, sa, sb, b_resident, n_wg;
   double cost;
 };
 
@@ -374,13 +472,23 @@ static bool plan_halo(int H, int W, int N, int n_taps, int n_chunks, int ck, int
   const int max_nacc = 256 / N < 4 ? 256 / N : 4;
   if (max_nacc < 1) return false;
   const long long w_bytes = (long long)n_taps * n_chunks * N * pitch;
-  const int staging = 2 * 128 * (N * 2 + 16);
+  const int stg_wg = 128 * ((N < 64 ? N : 64) * 2 + 16);  // staging bytes per epilogue warpgroup
   best->cost = 1e30;
+  // tuning overrides (debug): PDAC_HALO_TW / PDAC_HALO_NACC / PDAC_HALO_SA / PDAC_HALO_WG
+  static int f_tw = -1, f_nacc = -1, f_sa = -1, f_wg = -1;
+  if (f_tw < 0) {
+    const char* e;
+    f_tw = (e = getenv("PDAC_HALO_TW")) ? atoi(e) : 0;
+    f_nacc = (e = getenv("PDAC_HALO_NACC")) ? atoi(e) : 0;
+    f_sa = (e = getenv("PDAC_HALO_SA")) ? atoi(e) : 0;
+    f_wg = (e = getenv("PDAC_HALO_WG")) ? atoi(e) : 0;
+  }
   const int tws[5] = {16, 32, 64, 128, W};
   for (int ti = 0; ti < 5; ++ti) {
     int TW = tws[ti];
     if (TW > W) TW = W;
     if (TW + ew > 256) continue;
+    if (f_tw && TW != f_tw) continue;
     const int PW = TW + ew;
     for (int nacc = 1; nacc <= max_nacc; ++nacc) {
       int TH = (128 * nacc - TW) / PW + 1;
@@ -389,29 +497,33 @@ static bool plan_halo(int H, int W, int N, int n_taps, int n_chunks, int ck, int
       if (TH + eh > 256) TH = 256 - eh;
       const int nacc_eff = ((TH - 1) * PW + TW + 127) / 128;
       if (nacc_eff != nacc) continue;  // the same tile is reachable with fewer accumulators
+      if (f_nacc && nacc != f_nacc) continue;
       const int R = TH + eh;
       const int a_buf = ((nacc * 128 + eh * PW + ew) * pitch + 1023) & ~1023;
       for (int res = 1; res >= 0; --res) {
-        int sa, sb = 0;
-        long long fixed = staging + 2048;
-        if (res) {
-          if (w_bytes > 112 * 1024) continue;
-          fixed += w_bytes;
-          sa = (int)((kSmemBudget - fixed) / a_buf);
-        } else {
-          sb = 4;
-          fixed += (long long)sb * N * pitch;
-          sa = (int)((kSmemBudget - fixed) / a_buf);
-          if (sa > 3) {  // spend the rest on a deeper weight ring
-            sa = 3;
-            sb = (int)((kSmemBudget - staging - 2048 - 3LL * a_buf) / (N * pitch));
-            if (sb > kHaloMaxSB) sb = kHaloMaxSB;
+        if (res && w_bytes > 112 * 1024) continue;
+        int sa = 0, sb = 0, n_wg = f_wg ? f_wg : 4;
+        for (; n_wg >= 2; n_wg -= 2) {  // four epilogue warpgroups when their staging fits, else two
+          const long long fixed = (long long)n_wg * stg_wg + 2048;
+          if (res) {
+            sa = (int)((kSmemBudget - fixed - w_bytes) / a_buf);
+            sb = 0;
+          } else {
+            sb = 4;
+            sa = (int)((kSmemBudget - fixed - (long long)sb * N * pitch) / a_buf);
+            if (sa > 3) {  // spend the rest on a deeper weight ring
+              sa = 3;
+              sb = (int)((kSmemBudget - fixed - 3LL * a_buf) / (N * pitch));
+              if (sb > kHaloMaxSB) sb = kHaloMaxSB;
+            }
           }
+          if (sa >= 2) break;
         }
         if (sa > kHaloMaxSA) sa = kHaloMaxSA;
+        if (f_sa && sa > f_sa) sa = f_sa;
         if (sa < 2) continue;
         const int tiles = ceil_div(W, TW) * ceil_div(H, TH);
-        const double mma_cyc = (double)tiles * nacc * n_taps * n_chunks * (ck / 16) * (N / 2 > 10 ? N / 2 : 10);
+        const double mma_cyc = (double)tiles * nacc * n_taps * n_chunks * (ck / 16) * (32 + N / 4 > 40 ? 32 + N / 4 : 40);  // measured: ~32 + N/4 cycles per M=128 K=16 MMA
         double bytes = (double)tiles * R * PW * n_chunks * pitch + (double)H * W * N * 2 * (has_addend ? 2 : 1);
         if (!res) bytes += (double)tiles * w_bytes;
         const double mem_cyc = bytes / 40.0;
@@ -425,6 +537,7 @@ static bool plan_halo(int H, int W, int N, int n_taps, int n_chunks, int ck, int
           best->sa = sa;
           best->sb = sb;
           best->b_resident = res;
+          best->n_wg = n_wg;
         }
         if (res) break;  // resident weights always beat streaming them for the same tile
       }
@@ -463,10 +576,17 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   const int cout = out->C;
   const int block_n = cout <= 128 ? ((cout + 15) / 16) * 16 : 128;
   if (tc->wrows < ceil_div(cout, block_n) * block_n) return PDAC_OK;
+  if ((cout & 7) == 0) {
+    // the vectorised epilogue walks 8-channel columns of 16/32/64-wide passes
+    if (block_n != 16 && block_n != 32 && block_n != 64 && block_n != 80 && block_n != 96 && block_n != 128)
+      return PDAC_OK;
+  } else if (stats) {
+    return PDAC_OK;
+  }
   const int chunks0 = views[0].C / ck;
   const int n_chunks = chunks0 + (tc->n_cat > 1 ? views[1].C / ck : 0);
   const int ktot = n_chunks * ck;
-  HaloPlan pl;
+  HaloPlan pl = {0, 0, 0, 0, 0, 0, 0, 0.0};
   if (!plan_halo(out->H, out->W, block_n, tc->n_taps, n_chunks, ck, eh, ew, addend != nullptr, &pl)) return PDAC_OK;
 
   HaloMaps maps;
@@ -481,9 +601,25 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   p.PW = pl.TW + ew;
   p.R = pl.TH + eh;
   p.nacc = pl.nacc;
+  p.n_wg = pl.n_wg;
+  p.inv_pw = (uint32_t)(((1u << 20) + (uint32_t)p.PW - 1) / (uint32_t)p.PW);
   p.dh_min = dh_min;
   p.dw_min = dw_min;
-  for (int t = 0; t < tc->n_taps; ++t) p.tap_shift[t] = (tc->taps[t].dh - dh_min) * p.PW + (tc->taps[t].dw - dw_min);
+  {
+    // the issue loop walks the taps as an affine (r, s) grid; anything else goes to the generic kernel
+    int S = 1;
+    while (S < tc->n_taps && tc->taps[S].dh == tc->taps[0].dh) ++S;
+    if (tc->n_taps % S) return PDAC_OK;
+    const int Rr = tc->n_taps / S;
+    auto shift = [&](int t) { return (tc->taps[t].dh - dh_min) * p.PW + (tc->taps[t].dw - dw_min); };
+    p.tap_R = Rr;
+    p.tap_S = S;
+    p.tap_base = shift(0);
+    p.tap_step_s = S > 1 ? shift(1) - shift(0) : 0;
+    p.tap_step_r = Rr > 1 ? shift(S) - shift(0) : 0;
+    for (int t = 0; t < tc->n_taps; ++t)
+      if (shift(t) != p.tap_base + (t / S) * p.tap_step_r + (t % S) * p.tap_step_s) return PDAC_OK;
+  }
   p.pitch = ck * 2;
   p.layout_type = swizzle_layout_type(p.pitch);
   p.idesc = make_idesc_bf16(128, block_n, 0, 0);
@@ -533,17 +669,25 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     PDAC_TRY(encode_tiled_bf16(&maps.w, w_packed, 2, dims, strides, box, p.pitch));
   }
   const size_t b_bytes = (size_t)(p.b_resident ? p.n_taps * p.n_chunks : p.sb) * p.b_sub;
-  const size_t smem = (size_t)p.sa * p.a_buf + b_bytes + 2 * 128 * (size_t)(block_n * 2 + 16) + 1024;
-  PDAC_REQUIRE(smem <= 224 * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
-  static bool attr_set = false;
-  if (!attr_set) {
-    PDAC_CUDA(cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(224 * 1024)));
-    attr_set = true;
-  }
+  const size_t smem = (size_t)p.sa * p.a_buf + b_bytes + (size_t)p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16) + 1024;
+  PDAC_REQUIRE(smem <= 221 * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
   int per_n = num_sms() / p.tiles_c;
   if (per_n < 1) per_n = 1;
   if (per_n > p.tiles_sp) per_n = p.tiles_sp;
-  conv_halo_kernel<<<per_n * p.tiles_c, kHaloThreads, smem, (cudaStream_t)stream>>>(maps, p);
+  typedef void (*HaloKernel)(const HaloMaps, const HaloParams);
+  static const HaloKernel table[4][3] = {
+      {conv_halo_kernel<1, 1>, conv_halo_kernel<1, 2>, conv_halo_kernel<1, 4>},
+      {conv_halo_kernel<2, 1>, conv_halo_kernel<2, 2>, conv_halo_kernel<2, 4>},
+      {conv_halo_kernel<3, 1>, conv_halo_kernel<3, 2>, conv_halo_kernel<3, 4>},
+      {conv_halo_kernel<4, 1>, conv_halo_kernel<4, 2>, conv_halo_kernel<4, 4>}};
+  static bool attr_set[4][3] = {};
+  const int ki = pl.nacc - 1, kj = ck == 16 ? 0 : (ck == 32 ? 1 : 2);
+  HaloKernel kern = table[ki][kj];
+  if (!attr_set[ki][kj]) {
+    PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(221 * 1024)));
+    attr_set[ki][kj] = true;
+  }
+  kern<<<per_n * p.tiles_c, kHaloThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_halo_kernel");
   *handled = 1;
   return PDAC_OK;
