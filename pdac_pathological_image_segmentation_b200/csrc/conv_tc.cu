@@ -445,29 +445,41 @@ __global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_co
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // warp-converged walk, one elected lane issues (see conv_halo.cu: the issue path must stay below ~40 cycles / MMA)
+    {
+      const uint32_t leader = elect_one();
+      const uint32_t idesc = p.idesc;
+      const uint32_t hi_a = smem_desc_hi(8 * p.pitch_a, p.layout_a), hi_b = smem_desc_hi(8 * p.pitch_b, p.layout_b);
+      const uint32_t ka16 = (16 * p.pitch_a) >> 4, kb16 = (16 * p.pitch_b) >> 4;  // 16 pixels along K, in 16-byte units
+      const uint32_t a_lo0 = smem_desc_lo(smem_u32(smem), (uint32_t)a_box);
+      const uint32_t b_lo0 = smem_desc_lo(smem_u32(smem_b), (uint32_t)b_box);
+      const uint32_t a_slab16 = (uint32_t)a_slab >> 4, b_tile16 = (uint32_t)b_tile >> 4;
+      const uint32_t block_n = (uint32_t)p.block_n;
+      const int stages_a = p.stages_a;
       int ita = 0;
       for (int i = 0; i < n_my_kb; ++i) {
         const int bs = i & 1;
         mbar_wait(&fullB[bs], (i >> 1) & 1, p.err);
         tc_fence_after();
-        const uint32_t b_base = smem_u32(smem_b + (size_t)bs * b_tile);
+        const uint32_t b_lo = b_lo0 + (uint32_t)bs * b_tile16;
         for (int g = 0; g < nslab; ++g, ++ita) {
-          const int stage = ita % p.stages_a;
-          mbar_wait(&fullA[stage], (ita / p.stages_a) & 1, p.err);
+          const int stage = ita % stages_a;
+          mbar_wait(&fullA[stage], (ita / stages_a) & 1, p.err);
           tc_fence_after();
-          const uint32_t a_base = smem_u32(smem + (size_t)stage * a_slab);
+          if (leader) {
+            const uint32_t a_lo = a_lo0 + (uint32_t)stage * a_slab16;
+            const uint32_t td = tmem_base + (uint32_t)g * block_n;
+            umma_bf16_lohi(td, a_lo, hi_a, b_lo, hi_b, idesc, i > 0 ? 1u : 0u);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {  // 8 x 16 pixels
-            const uint64_t da = make_smem_desc(a_base + k * 16 * p.pitch_a, a_box, 8 * p.pitch_a, p.layout_a);
-            const uint64_t db = make_smem_desc(b_base + k * 16 * p.pitch_b, b_box, 8 * p.pitch_b, p.layout_b);
-            umma_bf16(tmem_base + (uint32_t)(g * p.block_n), da, db, p.idesc, (i > 0 || k > 0) ? 1u : 0u);
+            for (int k = 1; k < 8; ++k)  // 8 x 16 pixels
+              umma_bf16_lohi(td, a_lo + k * ka16, hi_a, b_lo + k * kb16, hi_b, idesc, 1u);
+            umma_commit(&emptyA[stage]);
           }
-          umma_commit(&emptyA[stage]);
         }
-        umma_commit(&emptyB[bs]);
+        if (leader) umma_commit(&emptyB[bs]);
+        __syncwarp();
       }
-      umma_commit(&tmem_full_bar);
+      if (leader) umma_commit(&tmem_full_bar);
     }
     __syncwarp();
   } else {
@@ -562,6 +574,9 @@ static int fill_taps(const PdacTapConv* tc, int n_views, const PdacView* views, 
 
 int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed, const float* bias,
                   const PdacView* addend, const PdacView* out, float* stats, void* stream, int* handled);
+
+int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy, float* dw,
+                   int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, void* stream, int* handled);
 
 static int check_dev_ptr(const void* p, const char* what) {
   cudaPointerAttributes at;
@@ -680,6 +695,12 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
   WgradKParams p;
   memset(&p, 0, sizeof(p));
   PDAC_TRY(fill_taps(tc, n_views, views, dy, &p.taps));
+  {
+    // stride-1 multi-tap weight gradients with <= 128 output channels take the halo-tile kernel (wgrad_halo.cu)
+    int handled = 0;
+    PDAC_TRY(wgrad_halo_try(tc, n_views, views, dy, dw, tap_stride, a_stride, b_stride, b_valid, stream, &handled));
+    if (handled) return PDAC_OK;
+  }
   const PdacView* v0 = views + tc->taps[0].src;
   const int ck = pick_ck(tc->n_cat, v0);
   PDAC_REQUIRE(ck >= 16, "input channels must be multiples of 16 (got %d)", v0[0].C);

@@ -144,6 +144,14 @@ __host__ __device__ inline uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
          ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | ((uint64_t)layout_type << 61);
 }
+// The same descriptor as two 32-bit halves: lo = start address | leading byte offset, hi = stride byte offset |
+// version | layout. Only lo changes inside an issue loop (add byte_offset >> 4).
+__host__ __device__ inline uint32_t smem_desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr >> 4) & 0x3FFF) | (((lbo_bytes >> 4) & 0x3FFF) << 16);
+}
+__host__ __device__ inline uint32_t smem_desc_hi(uint32_t sbo_bytes, uint32_t layout_type) {
+  return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (layout_type << 29);
+}
 __host__ __device__ inline uint32_t swizzle_layout_type(int pitch_bytes) {
   return pitch_bytes == 128 ? 2u : (pitch_bytes == 64 ? 4u : 6u);
 }

@@ -150,6 +150,17 @@ WGRAD_CASES = [
     (3, 10, 12, [64], 32, 3, 1, 1, 1),
     (2, 16, 16, [64], 48, 1, 1, 0, 1),
     (4, 64, 64, [64], 64, 3, 1, 1, 1),
+    # halo-tile weight gradient (wgrad_halo.cu): partial tiles, every slab composition (chunk pairs, tap pairs,
+    # kernel-row runs for 16/32-channel tensors), several slab groups per CTA grid, dilation
+    (2, 40, 50, [16], 16, 3, 1, 1, 1),
+    (1, 128, 128, [32], 16, 3, 1, 1, 1),
+    (2, 24, 32, [32, 32], 32, 3, 1, 1, 1),
+    (1, 32, 32, [64, 64], 32, 3, 1, 1, 1),
+    (1, 32, 48, [192], 64, 3, 1, 1, 1),
+    (1, 32, 32, [384], 128, 3, 1, 1, 1),
+    (2, 16, 16, [128], 128, 3, 1, 2, 2),
+    (1, 24, 24, [16], 32, 3, 1, 3, 3),
+    (1, 32, 32, [48], 16, 3, 1, 1, 1),
 ]
 
 
