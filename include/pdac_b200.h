@@ -175,6 +175,30 @@ int pdac_adaptive_avgpool_fwd(const PdacView* x, const PdacView* y, void* stream
 int pdac_adaptive_avgpool_bwd(const PdacView* dy, const PdacView* dx, void* stream);
 int pdac_add(const PdacView* a, const PdacView* b, int relu, const PdacView* y, void* stream);
 
+/* ---- GroupNorm / dropout / depthwise 3x3 (norm_dw.cu) ------------------------------------------------------
+ * The layers smp.FPN / PSPNet / DeepLabV3Plus add to the ResNet18 path (train_worker.py:152-182):
+ * nn.GroupNorm(32, 128) of Conv3x3GNReLU, nn.Dropout2d / nn.Dropout, SeparableConv2d's depthwise 3x3 (dilated). */
+/* stats: fp32 [N][G][2] (sum, sum of squares per image and group; caller zeroes). */
+int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, void* stream);
+/* y = [relu]((x - mean) * rstd * gamma + beta), mean / rstd from stats (biased variance, eps inside the sqrt). */
+int pdac_groupnorm_fwd(const PdacView* x, int G, const float* stats, const float* gamma, const float* beta, float eps,
+                       int relu, const PdacView* y, void* stream);
+/* dz = dy * (y > 0) (y may be NULL); gsums fp32 [N][G][2] += (sum dz*gamma, sum dz*gamma*xhat) (caller zeroes);
+ * dgamma[c] += sum dz*xhat, dbeta[c] += sum dz (may be NULL). */
+int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, int G, const float* stats,
+                              const float* gamma, float eps, float* gsums, float* dgamma, float* dbeta, void* stream);
+/* dx = rstd * (dz*gamma - (gsums0 + xhat*gsums1) / (H*W*C/G)). */
+int pdac_groupnorm_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, int G, const float* stats,
+                             const float* gamma, float eps, const float* gsums, const PdacView* dx, void* stream);
+/* y = x * keep / (1 - p) with keep a counter-based hash of (seed, image, channel) (per_channel = 1: nn.Dropout2d) or
+ * of (seed, element) (nn.Dropout); the backward pass is the same call on the gradient. Not torch's Philox stream. */
+int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long long seed, int per_channel, void* stream);
+/* Depthwise 3x3, stride 1, padding = dilation. w: fp32 [C][9] (the state_dict (C,1,3,3) tensor). flip = 1 applies the
+ * transposed taps (data gradient). */
+int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int flip, const PdacView* y, void* stream);
+/* dw[c][r*3+s] += sum dy[n,h,w,c] * x[n, h+(r-1)*dil, w+(s-1)*dil, c] (fp32 atomics, caller zeroes). */
+int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, void* stream);
+
 /* ---- loss / metric / mask / stitch / optimiser (loss.cu) ---------------------------------------------------- */
 /* tgt_dtype: 0 = fp32, 1 = uint8. sums: 3 doubles (sum p*t, sum p, sum t), kept for backward. loss: 1 float. */
 int pdac_dice_fwd(const float* logits, const void* targets, int tgt_dtype, long long n, double* sums, float smooth,

@@ -70,6 +70,13 @@ SIGNATURES = {
     "pdac_adaptive_avgpool_fwd": [_VP, _VP, _p],
     "pdac_adaptive_avgpool_bwd": [_VP, _VP, _p],
     "pdac_add": [_VP, _VP, _i, _VP, _p],
+    "pdac_groupnorm_stats": [_VP, _i, _p, _p],
+    "pdac_groupnorm_fwd": [_VP, _i, _p, _p, _p, _f, _i, _VP, _p],
+    "pdac_groupnorm_bwd_reduce": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _p, _p, _p],
+    "pdac_groupnorm_bwd_apply": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _VP, _p],
+    "pdac_dropout": [_VP, _VP, _f, C.c_ulonglong, _i, _p],
+    "pdac_dwconv3x3": [_VP, _p, _i, _i, _VP, _p],
+    "pdac_dwconv3x3_wgrad": [_VP, _VP, _i, _p, _p],
     "pdac_dice_fwd": [_p, _p, _i, _ll, _p, _f, _p, _p],
     "pdac_dice_bwd": [_p, _p, _i, _ll, _p, _f, _p, _p, _p],
     "pdac_sigmoid_mask": [_p, _ll, _p, _p, _p],
@@ -105,6 +112,7 @@ def load():
     return lib
 
 
+trace_all = False  # with `trace` set: also time the calls that carry no flops / bytes annotation (profiling scripts)
 trace = None  # bench.py sets this to a list: (name, start_event, end_event, flops, bytes) per traced call
 
 
@@ -113,7 +121,7 @@ def call(name, *args, flops=0, nbytes=0, tag=""):
     flops / nbytes: algorithmic work of the call, recorded with CUDA events on the current stream when tracing."""
     global launches
     lib = load()
-    if trace is not None and (flops or nbytes):
+    if trace is not None and (flops or nbytes or trace_all):
         import torch
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()

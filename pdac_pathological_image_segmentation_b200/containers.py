@@ -127,13 +127,19 @@ class ResNet18(_Container):
     """conv1, bn1, layer1..4 [, fc] in torchvision's order; kaiming-normal(fan_out, relu) conv init, BN 1/0
     (resnet.py:208-213). with_fc=True keeps the classifier the reference's ResUNet never uses."""
 
-    def __init__(self, with_fc, in_channels=3):
+    def __init__(self, with_fc, in_channels=3, output_stride=32):
         super().__init__()
+        if output_stride not in (16, 32):
+            raise ValueError("output_stride must be 32 or 16 (smp make_dilated on layer4)")
         self.conv1 = Conv2d(in_channels, 64, 7, stride=2, padding=3, bias=False)
         self.bn1 = BatchNorm2d(64)
         cin = 64
         for li, c in enumerate((64, 128, 256, 512), start=1):
-            blocks = [BasicBlock(cin, c, 2 if li > 1 else 1), BasicBlock(c, c, 1)]
+            if li == 4 and output_stride == 16:
+                # smp ResNetEncoder.make_dilated: every layer4 conv gets stride 1, dilation 2, padding (k // 2) * 2
+                blocks = [BasicBlock(cin, c, 1, dilation=2), BasicBlock(c, c, 1, dilation=2)]
+            else:
+                blocks = [BasicBlock(cin, c, 2 if li > 1 else 1), BasicBlock(c, c, 1)]
             self.add_module(f"layer{li}", seq(*blocks))
             cin = c
         if with_fc:

@@ -1,0 +1,428 @@
+// GroupNorm (forward / backward), Dropout / Dropout2d and depthwise 3x3 (dilated) convolution on NHWC bf16: the layers
+// smp.FPN (Conv3x3GNReLU, Dropout2d), smp.PSPNet (Dropout2d) and smp.DeepLabV3Plus (SeparableConv2d, Dropout) add to
+// the ResNet18 path (train_worker.py:152-182). All HBM-bound: one thread owns 8 consecutive
+// channels (16 bytes) of a pixel, fixed across its grid-stride loop over the pixels of ONE image (blockIdx.y = image),
+// so per-channel / per-(image, group) constants live in registers.
+#include "common.h"
+#include "vec.cuh"
+#include <string.h>
+
+namespace pdac {
+
+struct ImgView {
+  bf16* ptr;
+  long long sN, ps;  // image stride, pixel stride (elements)
+  int npix, C;       // pixels per image
+};
+
+static int img_view(const PdacView* v, ImgView* f, const char* what) {
+  PDAC_REQUIRE(v && v->ptr, "%s: null view", what);
+  PDAC_REQUIRE(v->C % 8 == 0, "%s: channels (%d) must be a multiple of 8", what, v->C);
+  PDAC_REQUIRE(v->H == 1 || v->sH == (int64_t)v->W * v->sW, "%s: view must be pixel-contiguous inside an image", what);
+  PDAC_REQUIRE(((uintptr_t)v->ptr & 15) == 0 && v->sW % 8 == 0 && v->sN % 8 == 0, "%s: view must be 16-byte aligned", what);
+  f->ptr = (bf16*)v->ptr;
+  f->sN = v->sN;
+  f->ps = v->sW;
+  f->npix = v->H * v->W;
+  f->C = v->C;
+  return PDAC_OK;
+}
+
+struct ImgGrid {
+  dim3 grid;
+  int cg, ppb;
+};
+static ImgGrid img_grid(int npix, int C, int N) {
+  ImgGrid g;
+  g.cg = C / 8;
+  g.ppb = 256 / g.cg;
+  if (g.ppb < 1) g.ppb = 1;
+  int need = (npix + g.ppb - 1) / g.ppb;
+  int cap = (num_sms() * 8 + N - 1) / N;
+  if (cap < 1) cap = 1;
+  g.grid = dim3(need < cap ? need : cap, N, 1);
+  return g;
+}
+#define IMG_SETUP(cg_, ppb_)                                   \
+  const int g = threadIdx.x % (cg_), pl = threadIdx.x / (cg_); \
+  const bool active = pl < (ppb_);                             \
+  const int n = blockIdx.y;                                    \
+  const int pstep = gridDim.x * (ppb_);                        \
+  const int pfirst = blockIdx.x * (ppb_) + pl;
+
+// ------------------------------------------------------------------------------------------------ GroupNorm
+// stats[n][grp][0..1] += sum, sum of squares over the group's channels and the image's pixels
+__global__ void __launch_bounds__(256) gn_stats_kernel(ImgView x, int cpg, float* __restrict__ stats, int G, int cg,
+                                                       int ppb) {
+  IMG_SETUP(cg, ppb)
+  float s[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+  if (active && g < cg) {
+    const bf16* base = x.ptr + (long long)n * x.sN + g * 8;
+    for (int p = pfirst; p < x.npix; p += pstep) {
+      const F8 a = unpack8(ld16(base + (long long)p * x.ps));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s[i] += a.v[i];
+        q[i] = fmaf(a.v[i], a.v[i], q[i]);
+      }
+    }
+    float* st = stats + (long long)n * G * 2;
+    if (cpg >= 8) {
+      float ss = 0.f, qq = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        ss += s[i];
+        qq += q[i];
+      }
+      const int grp = (g * 8) / cpg;
+      atomicAdd(st + grp * 2, ss);
+      atomicAdd(st + grp * 2 + 1, qq);
+    } else {
+      for (int i0 = 0; i0 < 8; i0 += cpg) {
+        float ss = 0.f, qq = 0.f;
+        for (int i = i0; i < i0 + cpg; ++i) {
+          ss += s[i];
+          qq += q[i];
+        }
+        const int grp = (g * 8 + i0) / cpg;
+        atomicAdd(st + grp * 2, ss);
+        atomicAdd(st + grp * 2 + 1, qq);
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void gn_consts(const float* stats, int n, int G, int cpg, int g, float count, float eps,
+                                          float (&mean)[8], float (&rstd)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int grp = (g * 8 + i) / cpg;
+    const float m = stats[((long long)n * G + grp) * 2] / count;
+    float v = stats[((long long)n * G + grp) * 2 + 1] / count - m * m;
+    v = v < 0.f ? 0.f : v;
+    mean[i] = m;
+    rstd[i] = rsqrtf(v + eps);
+  }
+}
+
+__global__ void __launch_bounds__(256) gn_fwd_kernel(ImgView x, int cpg, const float* __restrict__ stats, int G,
+                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                     float eps, int relu, ImgView y, int cg, int ppb) {
+  IMG_SETUP(cg, ppb)
+  if (!active) return;
+  float mean[8], rstd[8], sc[8], sh[8];
+  gn_consts(stats, n, G, cpg, g, (float)x.npix * cpg, eps, mean, rstd);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    sc[i] = rstd[i] * gamma[g * 8 + i];
+    sh[i] = beta[g * 8 + i] - mean[i] * sc[i];
+  }
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  bf16* yb = y.ptr + (long long)n * y.sN + g * 8;
+  for (int p = pfirst; p < x.npix; p += pstep) {
+    F8 a = unpack8(ld16_stream(xb + (long long)p * x.ps));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a.v[i] = fmaf(a.v[i], sc[i], sh[i]);
+      if (relu) a.v[i] = fmaxf(a.v[i], 0.f);
+    }
+    st16(yb + (long long)p * y.ps, pack8(a));
+  }
+}
+
+// gsums[n][grp][0] += sum dz*gamma, [1] += sum dz*gamma*xhat; dgamma[c] += sum dz*xhat, dbeta[c] += sum dz
+__global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(ImgView dy, ImgView y, ImgView x, int cpg,
+                                                            const float* __restrict__ stats, int G,
+                                                            const float* __restrict__ gamma, float eps,
+                                                            float* __restrict__ gsums, float* __restrict__ dgamma,
+                                                            float* __restrict__ dbeta, int cg, int ppb) {
+  IMG_SETUP(cg, ppb)
+  if (!active) return;
+  float mean[8], rstd[8], a0[8], a1[8];
+  gn_consts(stats, n, G, cpg, g, (float)x.npix * cpg, eps, mean, rstd);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) a0[i] = a1[i] = 0.f;
+  const bf16* db = dy.ptr + (long long)n * dy.sN + g * 8;
+  const bf16* yb = y.ptr ? y.ptr + (long long)n * y.sN + g * 8 : nullptr;
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  for (int p = pfirst; p < x.npix; p += pstep) {
+    F8 d = unpack8(ld16(db + (long long)p * dy.ps));
+    const F8 xv = unpack8(ld16(xb + (long long)p * x.ps));
+    if (yb) {
+      const F8 yv = unpack8(ld16(yb + (long long)p * y.ps));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d.v[i] = yv.v[i] > 0.f ? d.v[i] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a0[i] += d.v[i];
+      a1[i] = fmaf(d.v[i], (xv.v[i] - mean[i]) * rstd[i], a1[i]);
+    }
+  }
+  float* gs = gsums + (long long)n * G * 2;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = g * 8 + i;
+    const float ga = gamma[c];
+    atomicAdd(gs + (c / cpg) * 2, a0[i] * ga);
+    atomicAdd(gs + (c / cpg) * 2 + 1, a1[i] * ga);
+    if (dgamma) atomicAdd(dgamma + c, a1[i]);
+    if (dbeta) atomicAdd(dbeta + c, a0[i]);
+  }
+}
+
+__global__ void __launch_bounds__(256) gn_bwd_apply_kernel(ImgView dy, ImgView y, ImgView x, int cpg,
+                                                           const float* __restrict__ stats, int G,
+                                                           const float* __restrict__ gamma, float eps,
+                                                           const float* __restrict__ gsums, ImgView dx, int cg, int ppb) {
+  IMG_SETUP(cg, ppb)
+  if (!active) return;
+  float mean[8], rstd[8], ga[8], k1[8], k2[8];
+  const float count = (float)x.npix * cpg;
+  gn_consts(stats, n, G, cpg, g, count, eps, mean, rstd);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = g * 8 + i;
+    ga[i] = gamma[c];
+    k1[i] = gsums[((long long)n * G + c / cpg) * 2] / count;
+    k2[i] = gsums[((long long)n * G + c / cpg) * 2 + 1] / count;
+  }
+  const bf16* db = dy.ptr + (long long)n * dy.sN + g * 8;
+  const bf16* yb = y.ptr ? y.ptr + (long long)n * y.sN + g * 8 : nullptr;
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  bf16* ob = dx.ptr + (long long)n * dx.sN + g * 8;
+  for (int p = pfirst; p < x.npix; p += pstep) {
+    F8 d = unpack8(ld16_stream(db + (long long)p * dy.ps));
+    const F8 xv = unpack8(ld16_stream(xb + (long long)p * x.ps));
+    if (yb) {
+      const F8 yv = unpack8(ld16_stream(yb + (long long)p * y.ps));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d.v[i] = yv.v[i] > 0.f ? d.v[i] : 0.f;
+    }
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xhat = (xv.v[i] - mean[i]) * rstd[i];
+      o.v[i] = rstd[i] * (d.v[i] * ga[i] - k1[i] - xhat * k2[i]);
+    }
+    st16(ob + (long long)p * dx.ps, pack8(o));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ dropout
+__device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned long long idx) {
+  unsigned long long z = idx * 0x9E3779B97F4A7C15ull + seed;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+// y = x * keep / (1 - p); keep is a function of (seed, n, c) for Dropout2d and of (seed, element) for Dropout, so the
+// backward pass is the same call on the gradient.
+__global__ void __launch_bounds__(256) dropout_kernel(ImgView x, ImgView y, float p, unsigned long long seed,
+                                                      int per_channel, int cg, int ppb) {
+  IMG_SETUP(cg, ppb)
+  if (!active) return;
+  const float inv = 1.f / (1.f - p);
+  float f[8];
+  if (per_channel) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      f[i] = hash_uniform(seed, (unsigned long long)n * x.C + g * 8 + i) >= p ? inv : 0.f;
+  }
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  bf16* yb = y.ptr + (long long)n * y.sN + g * 8;
+  for (int pp = pfirst; pp < x.npix; pp += pstep) {
+    F8 a = unpack8(ld16_stream(xb + (long long)pp * x.ps));
+    if (!per_channel) {
+      const unsigned long long e0 = ((unsigned long long)n * x.npix + pp) * x.C + g * 8;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] = hash_uniform(seed, e0 + i) >= p ? inv : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a.v[i] *= f[i];
+    st16(yb + (long long)pp * y.ps, pack8(a));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ depthwise 3x3
+// y[n,h,w,c] = sum_{r,s} wgt[c][r*3+s] * x[n, h+(r-1)*dil, w+(s-1)*dil, c]   (stride 1, zero padding = dil);
+// flip = 1 uses wgt[c][8 - (r*3+s)]: the data gradient.
+__global__ void __launch_bounds__(256) dw3x3_kernel(ImgView x, int H, int W, const float* __restrict__ wgt, int dil,
+                                                    int flip, ImgView y, int cg, int ppb) {
+  IMG_SETUP(cg, ppb)
+  if (!active) return;
+  float wv[9][8];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) wv[t][i] = wgt[(long long)(g * 8 + i) * 9 + (flip ? 8 - t : t)];
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  bf16* yb = y.ptr + (long long)n * y.sN + g * 8;
+  for (int p = pfirst; p < x.npix; p += pstep) {
+    const int h = p / W, w = p - h * W;
+    F8 acc;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc.v[i] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hh = h + (r - 1) * dil;
+      if (hh < 0 || hh >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int ww = w + (s - 1) * dil;
+        if (ww < 0 || ww >= W) continue;
+        const F8 a = unpack8(ld16(xb + (long long)(hh * W + ww) * x.ps));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc.v[i] = fmaf(a.v[i], wv[r * 3 + s][i], acc.v[i]);
+      }
+    }
+    st16(yb + (long long)p * y.ps, pack8(acc));
+  }
+}
+
+// dw[c][r*3+s] += sum_{n,h,w} dy[n,h,w,c] * x[n, h+(r-1)*dil, w+(s-1)*dil, c]
+__global__ void __launch_bounds__(256) dw3x3_wgrad_kernel(ImgView x, ImgView dy, int H, int W, int dil,
+                                                          float* __restrict__ dw, int cg, int ppb) {
+  IMG_SETUP(cg, ppb)
+  if (!active) return;
+  float acc[9][8];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[t][i] = 0.f;
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  const bf16* db = dy.ptr + (long long)n * dy.sN + g * 8;
+  for (int p = pfirst; p < x.npix; p += pstep) {
+    const int h = p / W, w = p - h * W;
+    const F8 d = unpack8(ld16(db + (long long)p * dy.ps));
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hh = h + (r - 1) * dil;
+      if (hh < 0 || hh >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int ww = w + (s - 1) * dil;
+        if (ww < 0 || ww >= W) continue;
+        const F8 a = unpack8(ld16(xb + (long long)(hh * W + ww) * x.ps));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[r * 3 + s][i] = fmaf(a.v[i], d.v[i], acc[r * 3 + s][i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) atomicAdd(dw + (long long)(g * 8 + i) * 9 + t, acc[t][i]);
+}
+
+}  // namespace pdac
+
+using namespace pdac;
+
+static int gn_check(const PdacView* x, int G, int* cpg) {
+  PDAC_REQUIRE(G > 0 && x->C % G == 0, "GroupNorm: %d channels do not split into %d groups", x->C, G);
+  *cpg = x->C / G;
+  PDAC_REQUIRE(*cpg <= 8 ? 8 % *cpg == 0 : *cpg % 8 == 0, "GroupNorm: %d channels per group unsupported", *cpg);
+  return PDAC_OK;
+}
+
+extern "C" int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, void* stream) {
+  ImgView xv;
+  int cpg;
+  PDAC_TRY(img_view(x, &xv, "groupnorm x"));
+  PDAC_TRY(gn_check(x, G, &cpg));
+  const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  gn_stats_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, cpg, stats, G, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("gn_stats_kernel");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_groupnorm_fwd(const PdacView* x, int G, const float* stats, const float* gamma, const float* beta,
+                                  float eps, int relu, const PdacView* y, void* stream) {
+  ImgView xv, yv;
+  int cpg;
+  PDAC_TRY(img_view(x, &xv, "groupnorm x"));
+  PDAC_TRY(img_view(y, &yv, "groupnorm y"));
+  PDAC_TRY(gn_check(x, G, &cpg));
+  const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  gn_fwd_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, cpg, stats, G, gamma, beta, eps, relu, yv, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("gn_fwd_kernel");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, int G,
+                                         const float* stats, const float* gamma, float eps, float* gsums, float* dgamma,
+                                         float* dbeta, void* stream) {
+  ImgView dv, yv, xv;
+  int cpg;
+  PDAC_TRY(img_view(dy, &dv, "groupnorm dy"));
+  PDAC_TRY(img_view(x, &xv, "groupnorm x"));
+  memset(&yv, 0, sizeof(yv));
+  if (y) PDAC_TRY(img_view(y, &yv, "groupnorm y"));
+  PDAC_TRY(gn_check(x, G, &cpg));
+  const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  gn_bwd_reduce_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(dv, yv, xv, cpg, stats, G, gamma, eps, gsums, dgamma,
+                                                                 dbeta, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("gn_bwd_reduce_kernel");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_groupnorm_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, int G,
+                                        const float* stats, const float* gamma, float eps, const float* gsums,
+                                        const PdacView* dx, void* stream) {
+  ImgView dv, yv, xv, ov;
+  int cpg;
+  PDAC_TRY(img_view(dy, &dv, "groupnorm dy"));
+  PDAC_TRY(img_view(x, &xv, "groupnorm x"));
+  PDAC_TRY(img_view(dx, &ov, "groupnorm dx"));
+  memset(&yv, 0, sizeof(yv));
+  if (y) PDAC_TRY(img_view(y, &yv, "groupnorm y"));
+  PDAC_TRY(gn_check(x, G, &cpg));
+  const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  gn_bwd_apply_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(dv, yv, xv, cpg, stats, G, gamma, eps, gsums, ov, g.cg,
+                                                                g.ppb);
+  PDAC_LAUNCH_CHECK("gn_bwd_apply_kernel");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long long seed, int per_channel,
+                            void* stream) {
+  ImgView xv, yv;
+  PDAC_TRY(img_view(x, &xv, "dropout x"));
+  PDAC_TRY(img_view(y, &yv, "dropout y"));
+  PDAC_REQUIRE(p >= 0.f && p < 1.f, "dropout probability %g out of range [0, 1)", (double)p);
+  const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  dropout_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, yv, p, seed, per_channel, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("dropout_kernel");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int flip, const PdacView* y, void* stream) {
+  ImgView xv, yv;
+  PDAC_TRY(img_view(x, &xv, "dwconv x"));
+  PDAC_TRY(img_view(y, &yv, "dwconv y"));
+  PDAC_REQUIRE(x->H == y->H && x->W == y->W && x->C == y->C && x->N == y->N && dil >= 1, "dwconv: shape mismatch");
+  const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  dw3x3_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, x->H, x->W, w, dil, flip, yv, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("dw3x3_kernel");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, void* stream) {
+  ImgView xv, dv;
+  PDAC_TRY(img_view(x, &xv, "dwconv x"));
+  PDAC_TRY(img_view(dy, &dv, "dwconv dy"));
+  PDAC_REQUIRE(x->H == dy->H && x->W == dy->W && x->C == dy->C && x->N == dy->N && dil >= 1, "dwconv: shape mismatch");
+  ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  // fewer, longer-running blocks: every thread ends with 72 atomics
+  int cap = (num_sms() * 2 + x->N - 1) / x->N;
+  if (cap < 1) cap = 1;
+  if ((int)g.grid.x > cap) g.grid.x = cap;
+  dw3x3_wgrad_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dil, dw, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("dw3x3_wgrad_kernel");
+  return PDAC_OK;
+}

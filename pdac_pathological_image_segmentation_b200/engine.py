@@ -204,7 +204,7 @@ def _bn_prepare(tape, bn: BatchNorm2d, stats, count, device):
     return st
 
 
-def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residual=None):
+def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residual=None, out=None):
     """[relu](BN(conv(cat(srcs))) + residual): conv with per-channel sum / sum-of-squares in its epilogue, a finalize
     kernel, then one fused normalise(+residual)(+ReLU) pass (torchvision resnet.py:92-103; smp Conv2dReLU)."""
     wp_f, wp_t, _ = tape.packs.conv(m)
@@ -214,7 +214,10 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
     x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
     keep_x = tape.enabled
-    y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=None if keep_x else x)
+    if out is not None:        # write the activation straight into a channel slice of a concat buffer
+        y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=out)
+    else:
+        y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=None if keep_x else x)
     training = tape.training
 
     def bwd():
@@ -322,6 +325,98 @@ def add(tape: Tape, a, b):
     return y
 
 
+def conv_gn_relu(tape: Tape, m: Conv2d, gn, srcs):
+    """smp Conv3x3GNReLU body: relu(GroupNorm(conv(x))); per-image group statistics in fp32."""
+    wp_f, wp_t, _ = tape.packs.conv(m)
+    k = m.k
+    x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation)
+    y, stats = ops.groupnorm_fwd(x, gn.num_groups, gn.weight.detach(), gn.bias.detach(), gn.eps, relu=True)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is None:
+            return
+        dx = ops.groupnorm_bwd(dy, y, x, gn.num_groups, stats, gn.weight.detach(), gn.eps,
+                               dgamma=tape.arena.slot(gn.weight), dbeta=tape.arena.slot(gn.bias), out=dy)
+        _conv_backward(tape, m, srcs, dx, wp_t)
+    tape.record(bwd)
+    return y
+
+
+def dropout(tape: Tape, x, p, per_channel):
+    """nn.Dropout2d / nn.Dropout: identity in eval mode or with p == 0; in training a hash-generated mask (the seed is
+    drawn from torch's CPU generator, so torch.manual_seed makes runs reproducible; it is NOT torch's Philox stream)."""
+    if not tape.training or p <= 0.0:
+        return x
+    seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+    y = ops.dropout(x, p, seed, per_channel)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is not None:
+            tape.put(x, ops.dropout(dy, p, seed, per_channel, out=dy))
+    tape.record(bwd)
+    return y
+
+
+def depthwise3x3(tape: Tape, m: Conv2d, x):
+    """SeparableConv2d's depthwise half: Conv2d(C, C, 3, padding=d, dilation=d, groups=C, bias=False)."""
+    w = m.weight.detach()
+    y = ops.dwconv3x3(x, w, m.dilation)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is None:
+            return
+        ops.dwconv3x3_wgrad(x, dy, m.dilation, tape.arena.slot(m.weight))
+        if tape.wants(x):
+            old = tape.pop(x)
+            dx = ops.dwconv3x3(dy, w, m.dilation, flip=True)
+            if old is not None:
+                ops.add(old, dx, out=dx)
+            tape.put(x, dx)
+    tape.record(bwd)
+    return y
+
+
+def adaptive_avgpool(tape: Tape, x, out_hw):
+    y = ops.adaptive_avgpool_fwd(x, out_hw)
+
+    def bwd():
+        dy = tape.pop(y)
+        if dy is not None:
+            tape.put(x, ops.adaptive_avgpool_bwd(dy, (x.shape[1], x.shape[2])))
+    tape.record(bwd)
+    return y
+
+
+def bilinear_into(tape: Tape, x, out, align_corners):
+    """Bilinear resize of x written into `out` (a channel slice of a concat buffer)."""
+    ops.bilinear_fwd(x, (out.shape[1], out.shape[2]), align_corners, out=out)
+
+    def bwd():
+        dy = tape.pop(out)
+        if dy is not None:
+            tape.put(x, ops.bilinear_bwd(dy, (x.shape[1], x.shape[2]), align_corners))
+    tape.record(bwd)
+    return out
+
+
+def concat(tape: Tape, buf, parts):
+    """`buf` (N,H,W,sum C) already holds `parts` (its channel slices, in order, written in place by their producers):
+    torch.cat without a copy. Backward hands every producer its slice of the buffer's gradient."""
+    def bwd():
+        d = tape.pop(buf)
+        if d is None:
+            return
+        c0 = 0
+        for part in parts:
+            tape.put(part, d[..., c0:c0 + part.shape[3]])
+            c0 += part.shape[3]
+    tape.record(bwd)
+    return buf
+
+
 def logits_head(tape: Tape, x, n_classes, out_hw, align_corners):
     """NHWC bf16 (channel-padded) -> fp32 NCHW logits, bilinearly resized to out_hw when it differs
     (models/resunet.py:51-56; smp SegmentationHead upsampling). Returns (logits, feed_grad(g))."""
@@ -364,7 +459,7 @@ def stem_input(tape: Tape, x):
     return z
 
 
-def resnet18_features(tape: Tape, enc, x, depth=5):
+def resnet18_features(tape: Tape, enc, x, depth=5):  # noqa: E302
     """-> [stem (64 @ H/2), layer1 (64 @ H/4), layer2 (128 @ H/8), layer3 (256 @ H/16), layer4 (512 @ H/32)][:depth]
     (models/resunet.py:25-33; smp ResNetEncoder.forward stages 1..depth)."""
     z = stem_input(tape, x)

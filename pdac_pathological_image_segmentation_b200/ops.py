@@ -416,6 +416,54 @@ def adaptive_avgpool_bwd(dy, in_hw):
     return dx
 
 
+# ------------------------------------------------------------------------------------------------ GroupNorm / dropout / depthwise
+def groupnorm_fwd(x, groups, gamma, beta, eps, relu, out=None):
+    """-> (y, stats fp32 [N, G, 2] kept for backward)."""
+    stats = torch.zeros((x.shape[0], groups, 2), dtype=torch.float32, device=x.device)
+    call("pdac_groupnorm_stats", _vp(x), groups, _ptr(stats), _stream())
+    if out is None:
+        out = torch.empty_like(x)
+    call("pdac_groupnorm_fwd", _vp(x), groups, _ptr(stats), _ptr(gamma), _ptr(beta), eps, int(bool(relu)), _vp(out),
+         _stream())
+    return out, stats
+
+
+def groupnorm_bwd(dy, y, x, groups, stats, gamma, eps, dgamma=None, dbeta=None, out=None):
+    """dz = dy * (y > 0) when y is given; returns dx, accumulates dgamma / dbeta."""
+    gsums = torch.zeros((x.shape[0], groups, 2), dtype=torch.float32, device=x.device)
+    call("pdac_groupnorm_bwd_reduce", _vp(dy), _vp(y), _vp(x), groups, _ptr(stats), _ptr(gamma), eps, _ptr(gsums),
+         _ptr(dgamma), _ptr(dbeta), _stream())
+    if out is None:
+        out = torch.empty_like(dy)
+    call("pdac_groupnorm_bwd_apply", _vp(dy), _vp(y), _vp(x), groups, _ptr(stats), _ptr(gamma), eps, _ptr(gsums),
+         _vp(out), _stream())
+    return out
+
+
+def dropout(x, p, seed, per_channel, out=None):
+    """nn.Dropout2d (per_channel) / nn.Dropout with a counter-based hash mask; backward = same call on the gradient."""
+    if out is None:
+        out = torch.empty_like(x)
+    call("pdac_dropout", _vp(x), _vp(out), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(per_channel)), _stream())
+    return out
+
+
+def dwconv3x3(x, w, dil=1, flip=False, out=None):
+    """Depthwise 3x3 (stride 1, padding = dilation); w = the fp32 (C, 1, 3, 3) state_dict tensor. flip: data gradient."""
+    assert w.dtype == torch.float32 and w.is_contiguous() and w.numel() == x.shape[3] * 9
+    if out is None:
+        out = torch.empty_like(x)
+    call("pdac_dwconv3x3", _vp(x), _ptr(w), int(dil), int(bool(flip)), _vp(out), _stream(),
+         flops=18 * x.numel(), nbytes=_act_bytes(x, out), tag=f"dw3x3 d{dil} {tuple(x.shape)}")
+    return out
+
+
+def dwconv3x3_wgrad(x, dy, dil, out):
+    """out: fp32 (C, 1, 3, 3) gradient slot (accumulated into)."""
+    call("pdac_dwconv3x3_wgrad", _vp(x), _vp(dy), int(dil), _ptr(out), _stream())
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ loss / metric
 def _tgt(t):
     _need_cuda(t, "target")

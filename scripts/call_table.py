@@ -1,0 +1,29 @@
+"""Time of one smp-Unet training step by C-ABI entry point (all calls traced with CUDA events; GPU box)."""
+import sys, os, collections
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from pdac_pathological_image_segmentation_b200 import _lib
+from pdac_pathological_image_segmentation_b200.smp import Unet
+from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
+from pdac_pathological_image_segmentation_b200.trainer import TrainStep
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+torch.manual_seed(41)
+m = Unet(encoder_weights=None).cuda().train()
+ts = TrainStep(m)
+img, mask = synthetic_batch(B, 512, seed=41)
+img, mask = img.cuda(), mask.cuda()
+for _ in range(3): ts.step(img, mask)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(); ts.step(img, mask); e1.record(); torch.cuda.synchronize()
+plain = e0.elapsed_time(e1)
+_lib.trace = []; _lib.trace_all = True
+e0.record(); ts.step(img, mask); e1.record(); torch.cuda.synchronize()
+tr, _lib.trace = _lib.trace, None
+agg = collections.OrderedDict()
+for name, a, b, fl, nb, tag in tr:
+    g = agg.setdefault(name, [0.0, 0]); g[0] += a.elapsed_time(b); g[1] += 1
+tot = sum(v[0] for v in agg.values())
+print(f"step {plain:.2f} ms untraced, {e0.elapsed_time(e1):.2f} ms traced; sum of C-ABI calls {tot:.2f} ms")
+for name, (ms, n) in sorted(agg.items(), key=lambda kv: -kv[1][0]):
+    print(f"{name:36s} {n:4d} calls {ms:8.3f} ms  {100*ms/tot:5.1f}%")

@@ -44,6 +44,8 @@ def _pair(name, **kw):
     assert [(k, tuple(v.shape), v.dtype) for k, v in ours.state_dict().items()] == \
            [(k, tuple(v.shape), v.dtype) for k, v in ref.state_dict().items()], "state_dict layout differs from smp's"
     ours.load_state_dict(ref.state_dict(), strict=True)
+    if hasattr(ours, "p_drop"):
+        ours.p_drop = 0.0        # dropout cannot match torch's Philox stream: parity is checked with p = 0
     return ref, ours.to(DEV)
 
 
@@ -53,7 +55,7 @@ def _inputs(size=64, batch=2):
     return R.normalize(img), mask
 
 
-MODELS = ["unet_smp"]
+MODELS = ["unet_smp", "fpn", "pspnet", "deeplabv3+"]
 
 
 @pytest.mark.parametrize("name", MODELS)
@@ -91,21 +93,32 @@ def test_train_step_matches_oracle(name, train):
     ours.train(train)
     emu = copy.deepcopy(ref)
     out = ours(x.to(DEV))
+    out.retain_grad()
     loss = DiceLoss()(torch.squeeze(out), t.to(DEV))
     loss.backward()
     a = ref(x)
+    a.retain_grad()
     la = U.dice_loss(torch.squeeze(a), t)
     la.backward()
     from oracle.resunet_oracle import round_bf16
     with bf16_storage(emu):
         e = emu(round_bf16(x))
+        e.retain_grad()
         le = U.dice_loss(torch.squeeze(e), t)
         le.backward()
+    # the loss gradient at the logits: every parameter gradient inherits its perturbation (coherent shifts of large
+    # logits, e.g. through DeepLab's image-pooling branch, move it by several per cent under bf16 storage alone)
+    gn = a.grad.double().norm() + 1e-30
+    rel_g = ((out.grad.cpu().double() - a.grad.double()).norm() / gn).item()
+    cal_g = ((e.grad.double() - a.grad.double()).norm() / gn).item()
+    assert rel_g <= 1.5 * cal_g + 2e-2, f"{name}: dL/dlogits rel err {rel_g}, bf16 storage alone {cal_g}"
+    g_slack = 2.0 * max(rel_g, cal_g)
     err = (out.detach().cpu() - a.detach()).abs().max().item()
     cal = (e.detach() - a.detach()).abs().max().item()
     assert err <= max(2e-2, 1.5 * cal), f"{name}: logits max-abs err {err}, bf16 storage alone {cal}"
     assert abs(loss.item() - la.item()) <= max(2e-3, 1.5 * abs(le.item() - la.item()))
     pa, pe = dict(ref.named_parameters()), dict(emu.named_parameters())
+    gmax = max(p.grad.double().norm().item() for p in pa.values() if p.grad is not None)
     bad = []
     for k, p in ours.named_parameters():
         if pa[k].grad is None:
@@ -113,9 +126,12 @@ def test_train_step_matches_oracle(name, train):
             continue
         assert p.grad is not None, k
         r = pa[k].grad.double()
-        rel = ((p.grad.cpu().double() - r).norm() / (r.norm() + 1e-30)).item()
-        cal = ((pe[k].grad.double() - r).norm() / (r.norm() + 1e-30)).item()
-        if not rel <= 1.5 * cal + 2e-2:
+        den = r.norm() + 1e-4 * gmax          # gradients that are ~0 in fp32 (cancelled by a following norm layer)
+        rel = ((p.grad.cpu().double() - r).norm() / den).item()
+        cal = ((pe[k].grad.double() - r).norm() / den).item()
+        # 2 x: the emulation is ONE realisation of the rounding noise (BatchNorm over the 8 values of PSPNet's 2x2
+        # pooling branch, or the sum-over-everything head bias gradient, differ by that much between realisations)
+        if not rel <= 2.0 * cal + 2e-2 + g_slack:
             bad.append((k, round(rel, 4), round(cal, 4)))
     assert not bad, f"{name}: gradients farther from fp32 than bf16 storage explains (param, ours, calibrated): {bad}"
     if train:
