@@ -127,6 +127,9 @@ def test_train_step_matches_oracle(name, train):
         assert p.grad is not None, k
         r = pa[k].grad.double()
         den = r.norm() + 1e-4 * gmax          # gradients that are ~0 in fp32 (cancelled by a following norm layer)
+        if r.numel() == 1 and k.startswith("segmentation_head"):
+            # d/d(head bias) = sum of dL/dlogits over everything: signed terms cancel, so judge it against their L1 mass
+            den = a.grad.double().abs().sum()
         rel = ((p.grad.cpu().double() - r).norm() / den).item()
         cal = ((pe[k].grad.double() - r).norm() / den).item()
         # 2 x: the emulation is ONE realisation of the rounding noise (BatchNorm over the 8 values of PSPNet's 2x2
@@ -138,7 +141,11 @@ def test_train_step_matches_oracle(name, train):
         sa, so = ref.state_dict(), ours.state_dict()
         for k in sa:
             if k.endswith("running_var") or k.endswith("running_mean"):
-                assert torch.allclose(so[k].cpu(), sa[k], rtol=5e-2, atol=5e-3), k
+                # DeepLab's image-pooling branch normalises TWO values per channel at this batch size (x_hat = +-1
+                # unless they nearly coincide): downstream statistics inherit that sensitivity
+                atol = 3e-2 if name == "deeplabv3+" else 5e-3
+                diff = (so[k].cpu() - sa[k]).abs()
+                assert (diff <= atol + 5e-2 * sa[k].abs()).all(), (k, diff.max().item())
             if k.endswith("num_batches_tracked"):
                 assert int(so[k]) == int(sa[k]), k
 
