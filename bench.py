@@ -24,7 +24,11 @@ if ROOT not in sys.path:
 
 METRIC = "smp Unet-ResNet18 512x512 bf16 train patches/s"
 UNIT = "patches/s"
-TRAIN_GF_PER_PATCH = 128.321      # SURVEY 8d / BASELINE.md: 2*MACs of all convs, fwd + dgrad + wgrad, classes=1
+# SURVEY 8d / BASELINE.md: 2*MACs of all convs, fwd + dgrad + wgrad, classes=1, per 512x512 patch
+TRAIN_GF = {"unet": 128.321, "fpn": 105.306, "pspnet": 33.182, "deeplabv3+": 108.255, "resunet": 79.782}
+TRAIN_GF_PER_PATCH = TRAIN_GF["unet"]
+MODEL_NAMES = {"unet": "smp Unet-ResNet18", "fpn": "smp FPN-ResNet18", "pspnet": "smp PSPNet-ResNet18",
+               "deeplabv3+": "smp DeepLabV3+-ResNet18 (rates 3,6,9)", "resunet": "ResUNet (models/resunet.py)"}
 FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
 
 
@@ -38,6 +42,13 @@ def parse():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--cpu-batch", type=int, default=2, help="patches per CPU-baseline step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="train", choices=["train", "wsi"],
+                    help="train: the headline train step; wsi: BASELINE configs[4], tiles -> eval forward -> mask -> "
+                         "stitch into the slide mask (tiles/s; a step = one batch of tiles)")
+    ap.add_argument("--tiles", type=int, default=40000, help="wsi: tiles of the synthetic slide (200 x 200 grid)")
+    ap.add_argument("--model", default="unet", choices=sorted(TRAIN_GF),
+                    help="network of the train step (default: BASELINE configs[1], smp Unet-ResNet18; the others are "
+                         "configs[2..3] and the reference's own ResUNet)")
     return ap.parse_args()
 
 
@@ -51,7 +62,7 @@ def peaks():
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm / baseline
-def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None):
+def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None, model_name="unet"):
     """The reference's step (train_worker.py:68-80) on the host cores: oracle restatement of smp.Unet(resnet18) +
     DiceLoss + Adam in stock torch fp32 (smp is absent from the reference tree, see oracle/smp_oracle.py)."""
     import torch
@@ -62,7 +73,24 @@ def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None):
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     torch.set_num_threads(cores)
     torch.manual_seed(41)
-    model = S.Unet(classes=1).train()
+    if model_name == "resunet":
+        import torch.nn as nn
+
+        class _ResUNetOracle(nn.Module):        # functional oracle (resunet_oracle.forward) under an nn.Module face
+            def __init__(self):
+                super().__init__()
+                sd = R.make_state(1, seed=41)
+                self.keys = [k for k, v in sd.items() if v.is_floating_point() and "running" not in k and "fc." not in k]
+                self.sd = {k: v.clone() for k, v in sd.items()}
+                self.ps = nn.ParameterList([nn.Parameter(sd[k].clone()) for k in self.keys])
+
+            def forward(self, x):
+                sd = dict(self.sd)
+                sd.update({k: p for k, p in zip(self.keys, self.ps)})
+                return R.forward(sd, x, x.shape[-1], training=True)
+        model = _ResUNetOracle().train()
+    else:
+        model = S.build({"unet": "unet_smp"}.get(model_name, model_name), classes=1).train()
     opt = torch.optim.Adam(model.parameters(), lr=1e-4)
     img, mask = R.synthetic_batch(batch, size, seed=41)
     x = R.normalize(img)
@@ -84,13 +112,15 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, args.size, args.steps, min(args.warmup, 1))
+    v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, args.size, args.steps, min(args.warmup, 1),
+                                                 model_name=args.model)
     sample = (f"{done} steps x {args.cpu_batch} patches of {args.size}x{args.size} on {cores} host threads "
               f"(oracle port of the reference step, torch fp32 CPU)")
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
+    metric = METRIC if args.model == "unet" else f"{MODEL_NAMES[args.model]} {args.size}x{args.size} bf16 train patches/s"
+    line = {"impl": "reference", "metric": metric, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
             "warmup": min(args.warmup, 1), "ms_per_step": 1000 * dt / max(done, 1), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"smp Unet-ResNet18 train step, {args.size}x{args.size} RGB patches, 1 class, CPU "
+            "config": {"workload": f"{MODEL_NAMES[args.model]} train step, {args.size}x{args.size} RGB patches, 1 class, CPU "
                                    f"sample of {args.cpu_batch} patches/step"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -148,7 +178,7 @@ def run_ours(args):
     import torch.distributed as dist
 
     from pdac_pathological_image_segmentation_b200 import _lib
-    from pdac_pathological_image_segmentation_b200.smp import Unet
+    from pdac_pathological_image_segmentation_b200 import smp as P
     from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
     from pdac_pathological_image_segmentation_b200.trainer import TrainStep
 
@@ -165,7 +195,22 @@ def run_ours(args):
 
     B, S = args.batch, args.size
     torch.manual_seed(41)
-    model = Unet(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None)
+    kw = dict(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None)
+    if args.model == "unet":
+        model = P.Unet(**kw)
+    elif args.model == "fpn":
+        model = P.FPN(**kw)
+    elif args.model == "pspnet":
+        model = P.PSPNet(psp_use_batchnorm=True, **kw)
+    elif args.model == "deeplabv3+":
+        model = P.DeepLabV3Plus(decoder_atrous_rates=(3, 6, 9), **kw)
+    else:
+        import warnings
+
+        from pdac_pathological_image_segmentation_b200.resunet import ResUNet
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            model = ResUNet(num_classes=1, output_size=S)
     model.to(dev).train()
     ts = TrainStep(model, lr=1e-4)
     ts.broadcast_parameters()
@@ -242,9 +287,8 @@ def run_ours(args):
     # ---- roofline of the dominant kernel group (CUDA events recorded on the launching stream, timed region 1) ----
     pk, pk_src = peaks()
     groups = {}
-    for name, a, b, fl, nb, _tag in trace:
-        kind = "wgrad_tc_kernel" if "wgrad" in name else "conv_tc_kernel"
-        g = groups.setdefault(kind, [0.0, 0.0, 0.0, 0])
+    for name, a, b, fl, nb, _tag in trace:       # name = the tensor-core kernel the call dispatched to
+        g = groups.setdefault(name, [0.0, 0.0, 0.0, 0])
         g[0] += a.elapsed_time(b)
         g[1] += fl
         g[2] += nb
@@ -253,25 +297,32 @@ def run_ours(args):
     gms, gfl, gnb, gcalls = groups[dom]
     tc_peak = pk.get("bf16_tflops_sustained") or pk.get("bf16_tflops")
     achieved = gfl / (gms / 1000) / 1e12
+    traffic = None
+    try:        # dram bytes per launch of the dominant kernel from the committed ncu --set full capture, if any
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            traffic = json.load(f).get(dom, {}).get("dram_bytes_per_launch")
+    except Exception:
+        traffic = None
     roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": tc_peak, "unit": "TFLOP/s",
-                "frac": achieved / tc_peak, "traffic": None, "peak_source": f"{pk_src} bf16_tflops_sustained",
+                "frac": achieved / tc_peak, "traffic": traffic, "peak_source": f"{pk_src} bf16_tflops_sustained",
                 "calls_per_step": gcalls / args.steps, "ms_per_step_in_kernel": gms / args.steps,
                 "share_of_step": gms / ms,
                 "groups": {k: {"ms_per_step": v[0] / args.steps, "tflops": v[1] / (v[0] / 1000) / 1e12,
                                "act_gbs": v[2] / (v[0] / 1000) / 1e9} for k, v in groups.items()}}
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+    metric = METRIC if args.model == "unet" else f"{MODEL_NAMES[args.model]} {S}x{S} bf16 train patches/s"
+    line = {"metric": metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"smp Unet-ResNet18 train step (fwd + Dice loss + bwd + allreduce + Adam), "
+            "config": {"workload": f"{MODEL_NAMES[args.model]} train step (fwd + Dice loss + bwd + allreduce + Adam), "
                                    f"{S}x{S} RGB uint8 patches, 1 class, batch {B}/GPU",
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "l2": "inputs and activations (GBs per step) far exceed the 126 MB L2; no explicit flush"},
-            "tc_fraction_of_step": TRAIN_GF_PER_PATCH * 1e9 * value / world / (tc_peak * 1e12) if S == 512 else None,
+            "tc_fraction_of_step": TRAIN_GF[args.model] * 1e9 * value / world / (tc_peak * 1e12) if S == 512 else None,
             "loss": last, "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "roofline": roofline}
     if not args.no_cpu_baseline and world == 1:
-        v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, S, 1000, 1, budget_s=15.0)
+        v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, S, 1000, 1, budget_s=15.0, model_name=args.model)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{done} steps x {args.cpu_batch} patches ({dt:.1f} s) of the same train step, "
                                           f"oracle torch fp32 on {cores} host threads"}
@@ -280,9 +331,94 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------ WSI inference
+def run_wsi(args):
+    """BASELINE configs[4]: synthetic slide of --tiles 512x512 tiles (square grid), Unet-ResNet18 eval forward + sigmoid
+    mask + coordinate stitching, tiles sharded over the ranks by grid-row bands (no collective). One step = one batch
+    of --batch tiles per GPU; value = tiles/s over all ranks."""
+    import math
+
+    import torch
+    import torch.distributed as dist
+
+    from pdac_pathological_image_segmentation_b200 import _lib
+    from pdac_pathological_image_segmentation_b200 import smp as P
+    from pdac_pathological_image_segmentation_b200.wsi import SlideInference
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+    B, S = args.batch, args.size
+    side = int(math.isqrt(args.tiles))
+    torch.manual_seed(41)
+    model = P.Unet(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None).to(dev)
+    inf = SlideInference(model, side, side, tile=S, rank=rank, world=world)
+    g = torch.Generator().manual_seed(41 + rank)
+    host = [torch.randint(0, 256, (B, S, S, 3), dtype=torch.uint8, generator=g).pin_memory() for _ in range(2)]
+    devb = [h.to(dev) for h in host]
+    buf = torch.empty_like(devb[0])
+    n_own = (inf.r1 - inf.r0) * side
+
+    def coords(step):
+        t = (torch.arange(B, dtype=torch.int64) + step * B) % max(n_own, 1)
+        return ((inf.r0 + t // side).to(torch.int32).to(dev), (t % side).to(torch.int32).to(dev))
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+    cs = [coords(i) for i in range(args.steps + args.warmup)]
+    for i in range(args.warmup):
+        inf.run_batch(devb[i % 2], *cs[i])
+    sync_all()
+    l0 = _lib.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        inf.run_batch(devb[i % 2], *cs[args.warmup + i])
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    launches = _lib.launches - l0
+    w0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        buf.copy_(host[i % 2], non_blocking=True)
+        m = inf.run_batch(buf, *cs[args.warmup + i])
+        m[0, 0, :8].cpu()                                  # device -> host read of the step's result
+    e1.record()
+    sync_all()
+    ms2 = max(e0.elapsed_time(e1), (time.perf_counter() - w0) * 1000)
+    t = torch.tensor([ms, ms2], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms2 = t.tolist()
+    if rank == 0:
+        line = {"metric": "smp Unet-ResNet18 512x512 bf16 WSI inference tiles/s (fwd + mask + stitch)",
+                "value": world * B * args.steps / (ms / 1000), "unit": "tiles/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": f"WSI inference, {side}x{side} grid of {S}x{S} uint8 tiles, {B} tiles/step/GPU, "
+                                       f"row-band sharding over {world} rank(s), slide band {tuple(inf.band.shape)} uint8"},
+                "gpu_launches": launches,
+                "e2e": {"value": world * B * args.steps / (ms2 / 1000), "unit": "tiles/s",
+                        "h2d_bytes_per_step": B * S * S * 3, "d2h_bytes_per_step": 8},
+                "time_for_all_tiles_s": args.tiles / (world * B * args.steps / (ms / 1000))}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "wsi":
+        run_wsi(a)
     else:
         run_ours(a)

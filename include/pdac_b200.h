@@ -61,6 +61,9 @@ typedef struct PdacConv {
 
 int pdac_version(void);
 const char* pdac_last_error(void);
+/* Which tensor-core kernel this thread's last convolution call dispatched to: 1 conv_tc_kernel, 2 conv_halo_kernel,
+ * 3 wgrad_tc_kernel, 4 wgrad_halo_kernel (0: none yet). Used by bench.py to attribute event times to kernels. */
+int pdac_last_kernel_id(void);
 /* Reads (and clears) the device-side pipeline error flag; synchronises `stream`. Debug/tests only. */
 int pdac_check_device_flag(void* stream);
 

@@ -104,6 +104,8 @@ def load():
     lib.pdac_version.argtypes = []
     lib.pdac_last_error.restype = C.c_char_p
     lib.pdac_last_error.argtypes = []
+    lib.pdac_last_kernel_id.restype = C.c_int
+    lib.pdac_last_kernel_id.argtypes = []
     for name, args in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype = C.c_int
@@ -112,6 +114,7 @@ def load():
     return lib
 
 
+KERNEL_NAMES = {1: "conv_tc_kernel", 2: "conv_halo_kernel", 3: "wgrad_tc_kernel", 4: "wgrad_halo_kernel"}
 trace_all = False  # with `trace` set: also time the calls that carry no flops / bytes annotation (profiling scripts)
 trace = None  # bench.py sets this to a list: (name, start_event, end_event, flops, bytes) per traced call
 
@@ -127,7 +130,8 @@ def call(name, *args, flops=0, nbytes=0, tag=""):
         e0.record()
         rc = getattr(lib, name)(*args)
         e1.record()
-        trace.append((name, e0, e1, flops, nbytes, tag))
+        kid = lib.pdac_last_kernel_id() if name.startswith(("pdac_conv", "pdac_tapconv")) else 0
+        trace.append((KERNEL_NAMES.get(kid, name), e0, e1, flops, nbytes, tag))
     else:
         rc = getattr(lib, name)(*args)
     launches += 1

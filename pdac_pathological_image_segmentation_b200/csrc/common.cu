@@ -21,6 +21,10 @@ int cuda_fail(cudaError_t e, const char* what) {
               "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
 }
 
+static thread_local int g_last_kernel = 0;
+void note_kernel(int id) { g_last_kernel = id; }
+int last_kernel() { return g_last_kernel; }
+
 __device__ int g_pipeline_err_flag = 0;
 
 int* device_err_flag() {
@@ -103,6 +107,8 @@ extern "C" {
 int pdac_version(void) { return 100; }
 
 const char* pdac_last_error(void) { return pdac::g_err; }
+
+int pdac_last_kernel_id(void) { return pdac::last_kernel(); }
 
 int pdac_check_device_flag(void* stream) {
   using namespace pdac;

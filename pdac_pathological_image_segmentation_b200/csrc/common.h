@@ -42,6 +42,10 @@ int encode_view_map(CUtensorMap* m, const PdacView* v, int ck, int tw, int th, i
 
 int* device_err_flag();  // device pointer to the pipeline error flag
 
+// Which convolution kernel the last pdac_conv* / pdac_tapconv* call of this thread dispatched to (bench attribution).
+enum { KID_NONE = 0, KID_CONV_TC = 1, KID_CONV_HALO = 2, KID_WGRAD_TC = 3, KID_WGRAD_HALO = 4 };
+void note_kernel(int id);
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int pow2_ceil(int x) {
   int p = 1;

@@ -689,6 +689,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   }
   kern<<<per_n * p.tiles_c, kHaloThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_halo_kernel");
+  note_kernel(KID_CONV_HALO);
   *handled = 1;
   return PDAC_OK;
 }

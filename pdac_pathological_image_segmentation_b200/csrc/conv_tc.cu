@@ -682,6 +682,7 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
   if (ctas > p.total_tiles) ctas = p.total_tiles;
   conv_tc_kernel<<<ctas, kThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_tc_kernel");
+  note_kernel(KID_CONV_TC);
   return PDAC_OK;
 }
 
@@ -765,6 +766,7 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
   dim3 grid(splits, y, z);
   wgrad_tc_kernel<<<grid, kWgradThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_tc_kernel");
+  note_kernel(KID_WGRAD_TC);
   return PDAC_OK;
 }
 

@@ -332,7 +332,7 @@ static int gn_check(const PdacView* x, int G, int* cpg) {
 
 extern "C" int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, void* stream) {
   ImgView xv;
-  int cpg;
+  int cpg = 0;
   PDAC_TRY(img_view(x, &xv, "groupnorm x"));
   PDAC_TRY(gn_check(x, G, &cpg));
   const ImgGrid g = img_grid(xv.npix, x->C, x->N);
@@ -344,7 +344,7 @@ extern "C" int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, void
 extern "C" int pdac_groupnorm_fwd(const PdacView* x, int G, const float* stats, const float* gamma, const float* beta,
                                   float eps, int relu, const PdacView* y, void* stream) {
   ImgView xv, yv;
-  int cpg;
+  int cpg = 0;
   PDAC_TRY(img_view(x, &xv, "groupnorm x"));
   PDAC_TRY(img_view(y, &yv, "groupnorm y"));
   PDAC_TRY(gn_check(x, G, &cpg));
@@ -358,7 +358,7 @@ extern "C" int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, 
                                          const float* stats, const float* gamma, float eps, float* gsums, float* dgamma,
                                          float* dbeta, void* stream) {
   ImgView dv, yv, xv;
-  int cpg;
+  int cpg = 0;
   PDAC_TRY(img_view(dy, &dv, "groupnorm dy"));
   PDAC_TRY(img_view(x, &xv, "groupnorm x"));
   memset(&yv, 0, sizeof(yv));
@@ -375,7 +375,7 @@ extern "C" int pdac_groupnorm_bwd_apply(const PdacView* dy, const PdacView* y, c
                                         const float* stats, const float* gamma, float eps, const float* gsums,
                                         const PdacView* dx, void* stream) {
   ImgView dv, yv, xv, ov;
-  int cpg;
+  int cpg = 0;
   PDAC_TRY(img_view(dy, &dv, "groupnorm dy"));
   PDAC_TRY(img_view(x, &xv, "groupnorm x"));
   PDAC_TRY(img_view(dx, &ov, "groupnorm dx"));

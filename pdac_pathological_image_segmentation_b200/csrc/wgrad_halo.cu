@@ -376,6 +376,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   dim3 grid(splits, ygroups, 1);
   wgrad_halo_kernel<<<grid, kWhThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_halo_kernel");
+  note_kernel(KID_WGRAD_HALO);
   *handled = 1;
   return PDAC_OK;
 }
