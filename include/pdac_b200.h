@@ -150,14 +150,16 @@ int pdac_bn_prepare(const float* stats, double count, const float* gamma, const 
 /* y = [relu](x*scale[c] + shift[c] + residual); scale_shift / residual may be NULL. */
 int pdac_scale_shift_act(const PdacView* x, const float* scale_shift, const PdacView* residual, int relu,
                          const PdacView* y, void* stream);
-/* BN backward pass 1: dz = dy * (y > 0) (y may be NULL = no ReLU); sums[c] += sum dz, sums[C+c] += sum dz*xhat. */
-int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd, float* sums,
-                       void* stream);
+/* BN backward pass 1: dz = dy * (y > 0); sums[c] += sum dz, sums[C+c] += sum dz*xhat. ReLU mask: from y; or, with
+ * y NULL and scale_shift (the forward's [2][C]) given, recomputed as x*scale + shift > 0 (y is then never read); with
+ * both NULL there is no ReLU. */
+int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
+                       const float* scale_shift, float* sums, void* stream);
 /* BN backward pass 2: dx = gamma*invstd*(dz - sums0/count - xhat*sums1/count) (train) or gamma*invstd*dz (eval);
  * optionally stores dz (the residual branch's gradient) and dgamma = sums1, dbeta = sums0. */
 int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
-                      const float* gamma, const float* sums, double count, int train, const PdacView* dx,
-                      const PdacView* dz_out, float* dgamma, float* dbeta, void* stream);
+                      const float* gamma, const float* scale_shift, const float* sums, double count, int train,
+                      const PdacView* dx, const PdacView* dz_out, float* dgamma, float* dbeta, void* stream);
 /* dz = dy * (y > 0) (y, dz may be NULL); dbias[c] += sum dz (may be NULL; caller zeroes). */
 int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias, void* stream);
 

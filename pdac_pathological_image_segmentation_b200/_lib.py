@@ -56,8 +56,8 @@ SIGNATURES = {
     "pdac_unpack_stem_wgrad": [_p, _i, _p, _p],
     "pdac_bn_prepare": [_p, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _p, _i, _p],
     "pdac_scale_shift_act": [_VP, _p, _VP, _i, _VP, _p],
-    "pdac_bn_bwd_reduce": [_VP, _VP, _VP, _p, _p, _p],
-    "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],
+    "pdac_bn_bwd_reduce": [_VP, _VP, _VP, _p, _p, _p, _p],
+    "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],
     "pdac_relu_bwd_bias": [_VP, _VP, _VP, _p, _p],
     "pdac_maxpool3x3s2_fwd": [_VP, _VP, _p, _p],
     "pdac_maxpool3x3s2_bwd": [_VP, _p, _VP, _p],

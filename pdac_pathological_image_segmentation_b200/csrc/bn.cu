@@ -105,33 +105,61 @@ __global__ void __launch_bounds__(256) scale_shift_act_kernel(Flat x, const floa
 }
 
 // ------------------------------------------------------------------------------------------------ BN backward
-// pass 1: sums[c] = sum dz, sums[C+c] = sum dz * xhat, dz = dy * (y > 0)
+// pass 1: sums[c] = sum dz, sums[C+c] = sum dz * xhat, dz = dy * (y > 0). The ReLU mask comes from y or, when y is
+// NULL and `ss` (the forward's scale / shift) is given, is recomputed as x*scale + shift > 0 — the same fma the forward
+// rounded to bf16, so the decision is identical and y is not read at all. Two pixels per iteration keep more loads
+// in flight.
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
-                                                            float* __restrict__ sums, int cg, int ppb) {
+                                                            const float* __restrict__ ss, float* __restrict__ sums,
+                                                            int cg, int ppb) {
   __shared__ float red[256][17];
   EW_SETUP(cg, ppb)
-  float s0[8], s1[8], mean[8];
+  float s0[8], s1[8], mean[8], sc[8], sh[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     s0[i] = 0.f;
     s1[i] = 0.f;
     mean[i] = (active && mi) ? mi[g * 8 + i] : 0.f;
+    sc[i] = (active && ss) ? ss[g * 8 + i] : 0.f;
+    sh[i] = (active && ss) ? ss[dy.C + g * 8 + i] : 0.f;
   }
+  const bool xmask = ss != nullptr && y.ptr == nullptr && x.ptr != nullptr;
   if (active) {
-    for (long long p = pfirst; p < dy.npix; p += pstep) {
-      F8 d = unpack8(ld16_stream(dy.ptr + p * dy.ps + g * 8));
+    for (long long p = pfirst; p < dy.npix; p += 2 * pstep) {
+      const long long p2 = p + pstep;
+      const bool two = p2 < dy.npix;
+      uint4 rd[2], ry[2], rx[2];
+      rd[0] = ld16_stream(dy.ptr + p * dy.ps + g * 8);
+      if (two) rd[1] = ld16_stream(dy.ptr + p2 * dy.ps + g * 8);
       if (y.ptr) {
-        const F8 yy = unpack8(ld16_stream(y.ptr + p * y.ps + g * 8));
-#pragma unroll
-        for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+        ry[0] = ld16_stream(y.ptr + p * y.ps + g * 8);
+        if (two) ry[1] = ld16_stream(y.ptr + p2 * y.ps + g * 8);
       }
       if (x.ptr) {
-        const F8 xx = unpack8(ld16_stream(x.ptr + p * x.ps + g * 8));
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s1[i] = fmaf(d.v[i], xx.v[i] - mean[i], s1[i]);
+        rx[0] = ld16_stream(x.ptr + p * x.ps + g * 8);
+        if (two) rx[1] = ld16_stream(x.ptr + p2 * x.ps + g * 8);
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) s0[i] += d.v[i];
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !two) break;
+        F8 d = unpack8(rd[u]);
+        F8 xx;
+        if (x.ptr) xx = unpack8(rx[u]);
+        if (y.ptr) {
+          const F8 yy = unpack8(ry[u]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+        } else if (xmask) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d.v[i] = fmaf(xx.v[i], sc[i], sh[i]) > 0.f ? d.v[i] : 0.f;
+        }
+        if (x.ptr) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s1[i] = fmaf(d.v[i], xx.v[i] - mean[i], s1[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s0[i] += d.v[i];
+      }
     }
   }
 #pragma unroll
@@ -155,13 +183,13 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Fla
 
 // pass 2: dx = gamma*invstd*(dz - sum_dz/M - xhat * sum_dz_xhat/M)   (train)   |   gamma*invstd*dz   (eval)
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
-                                                           const float* __restrict__ gamma,
+                                                           const float* __restrict__ gamma, const float* __restrict__ ss,
                                                            const float* __restrict__ sums, float inv_count, int train,
                                                            Flat dx, Flat dz, float* __restrict__ dgamma,
                                                            float* __restrict__ dbeta, int cg, int ppb) {
   EW_SETUP(cg, ppb)
   if (!active) return;
-  float a[8], m1[8], m2[8], mean[8], invstd[8];
+  float a[8], m1[8], m2[8], mean[8], invstd[8], sc[8], sh[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = g * 8 + i;
@@ -170,29 +198,55 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat
     a[i] = (gamma ? gamma[c] : 1.f) * invstd[i];
     m1[i] = train ? sums[c] * inv_count : 0.f;
     m2[i] = train ? sums[dy.C + c] * inv_count : 0.f;
+    sc[i] = ss ? ss[c] : 0.f;
+    sh[i] = ss ? ss[dy.C + c] : 0.f;
     if (blockIdx.x == 0 && pl == 0) {
       if (dgamma) dgamma[c] = sums[dy.C + c];
       if (dbeta) dbeta[c] = sums[c];
     }
   }
-  for (long long p = pfirst; p < dy.npix; p += pstep) {
-    F8 d = unpack8(ld16_stream(dy.ptr + p * dy.ps + g * 8));
+  const bool xmask = ss != nullptr && y.ptr == nullptr && x.ptr != nullptr;
+  const bool need_x = train || xmask;
+  for (long long p = pfirst; p < dy.npix; p += 2 * pstep) {
+    const long long p2 = p + pstep;
+    const bool two = p2 < dy.npix;
+    uint4 rd[2], ry[2], rx[2];
+    rd[0] = ld16_stream(dy.ptr + p * dy.ps + g * 8);
+    if (two) rd[1] = ld16_stream(dy.ptr + p2 * dy.ps + g * 8);
     if (y.ptr) {
-      const F8 yy = unpack8(ld16_stream(y.ptr + p * y.ps + g * 8));
-#pragma unroll
-      for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+      ry[0] = ld16_stream(y.ptr + p * y.ps + g * 8);
+      if (two) ry[1] = ld16_stream(y.ptr + p2 * y.ps + g * 8);
     }
-    if (dz.ptr) st16(dz.ptr + p * dz.ps + g * 8, pack8(d));
-    F8 o;
-    if (train) {
-      const F8 xx = unpack8(ld16_stream(x.ptr + p * x.ps + g * 8));
-#pragma unroll
-      for (int i = 0; i < 8; ++i) o.v[i] = a[i] * (d.v[i] - m1[i] - (xx.v[i] - mean[i]) * invstd[i] * m2[i]);
-    } else {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) o.v[i] = a[i] * d.v[i];
+    if (need_x) {
+      rx[0] = ld16_stream(x.ptr + p * x.ps + g * 8);
+      if (two) rx[1] = ld16_stream(x.ptr + p2 * x.ps + g * 8);
     }
-    st16(dx.ptr + p * dx.ps + g * 8, pack8(o));
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+      const long long pp = u ? p2 : p;
+      F8 d = unpack8(rd[u]);
+      F8 xx;
+      if (need_x) xx = unpack8(rx[u]);
+      if (y.ptr) {
+        const F8 yy = unpack8(ry[u]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
+      } else if (xmask) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d.v[i] = fmaf(xx.v[i], sc[i], sh[i]) > 0.f ? d.v[i] : 0.f;
+      }
+      if (dz.ptr) st16(dz.ptr + pp * dz.ps + g * 8, pack8(d));
+      F8 o;
+      if (train) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o.v[i] = a[i] * (d.v[i] - m1[i] - (xx.v[i] - mean[i]) * invstd[i] * m2[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o.v[i] = a[i] * d.v[i];
+      }
+      st16(dx.ptr + pp * dx.ps + g * 8, pack8(o));
+    }
   }
 }
 
@@ -265,7 +319,7 @@ extern "C" int pdac_scale_shift_act(const PdacView* x, const float* scale_shift,
 }
 
 extern "C" int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
-                                  float* sums, void* stream) {
+                                  const float* scale_shift, float* sums, void* stream) {
   Flat fd, fy = {nullptr, 0, 0, 0}, fx = {nullptr, 0, 0, 0};
   PDAC_TRY(flatten(dy, &fd, "dy"));
   if (y) PDAC_TRY(flatten(y, &fy, "y"));
@@ -273,14 +327,16 @@ extern "C" int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const P
   PDAC_REQUIRE(sums, "bn_bwd_reduce: null sums");
   PDAC_REQUIRE(fd.C <= 2048, "bn_bwd_reduce: too many channels");
   const EwGrid g = ew_grid(fd.npix, fd.C);
-  bn_bwd_reduce_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, sums, g.cg, g.ppb);
+  bn_bwd_reduce_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums, g.cg,
+                                                                  g.ppb);
   PDAC_LAUNCH_CHECK("bn_bwd_reduce");
   return PDAC_OK;
 }
 
 extern "C" int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
-                                 const float* gamma, const float* sums, double count, int train, const PdacView* dx,
-                                 const PdacView* dz_out, float* dgamma, float* dbeta, void* stream) {
+                                 const float* gamma, const float* scale_shift, const float* sums, double count,
+                                 int train, const PdacView* dx, const PdacView* dz_out, float* dgamma, float* dbeta,
+                                 void* stream) {
   Flat fd, fy = {nullptr, 0, 0, 0}, fx = {nullptr, 0, 0, 0}, fdx, fdz = {nullptr, 0, 0, 0};
   PDAC_TRY(flatten(dy, &fd, "dy"));
   if (y) PDAC_TRY(flatten(y, &fy, "y"));
@@ -289,8 +345,9 @@ extern "C" int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const Pd
   if (dz_out) PDAC_TRY(flatten(dz_out, &fdz, "dz"));
   PDAC_REQUIRE(mean_invstd && sums, "bn_bwd_apply: null stats");
   PDAC_REQUIRE(!train || x, "bn_bwd_apply: training mode needs the conv output x");
+  PDAC_REQUIRE(!(scale_shift && !y) || x, "bn_bwd_apply: recomputing the ReLU mask needs the conv output x");
   const EwGrid g = ew_grid(fd.npix, fd.C);
-  bn_bwd_apply_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, sums,
+  bn_bwd_apply_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, scale_shift, sums,
                                                                   (float)(1.0 / count), train, fdx, fdz, dgamma, dbeta,
                                                                   g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("bn_bwd_apply");

@@ -225,12 +225,15 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         if dy is None:
             return
         sums = torch.zeros((2, m.cout), dtype=F32, device=dev)
-        ops.bn_bwd_reduce(dy, y if relu else None, x, st.mi, sums)
+        # without a residual the ReLU mask is recomputed from x and the forward's scale / shift: y is not re-read
+        ymask = y if (relu and residual is not None) else None
+        ssm = st.ss if (relu and residual is None) else None
+        ops.bn_bwd_reduce(dy, ymask, x, st.mi, sums, scale_shift=ssm)
         want_res = residual is not None and tape.wants(residual)
         dxr = torch.empty_like(dy) if want_res else dy
-        ops.bn_bwd_apply(dy, y if relu else None, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dxr,
+        ops.bn_bwd_apply(dy, ymask, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dxr,
                          dz_out=dy if (want_res and relu) else None, dgamma=tape.arena.slot(bn.weight),
-                         dbeta=tape.arena.slot(bn.bias))
+                         dbeta=tape.arena.slot(bn.bias), scale_shift=ssm)
         if want_res:
             tape.put(residual, dy)
         _conv_backward(tape, m, srcs, dxr, wp_t)
@@ -253,9 +256,9 @@ def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
         if dy is None:
             return
         sums = torch.zeros((2, m.cout), dtype=F32, device=dev)
-        ops.bn_bwd_reduce(dy, y, x, st.mi, sums)
-        ops.bn_bwd_apply(dy, y, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dy,
-                         dgamma=tape.arena.slot(bn.weight), dbeta=tape.arena.slot(bn.bias))
+        ops.bn_bwd_reduce(dy, None, x, st.mi, sums, scale_shift=st.ss)
+        ops.bn_bwd_apply(dy, None, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dy,
+                         dgamma=tape.arena.slot(bn.weight), dbeta=tape.arena.slot(bn.bias), scale_shift=st.ss)
         dwp = ops.stem_conv_wgrad(z, dy)
         ops.unpack_stem_wgrad(dwp, m.cout, out=tape.arena.slot(m.weight))
     tape.record(bwd)

@@ -317,15 +317,18 @@ def scale_shift_act(x, scale_shift=None, residual=None, relu=False, out=None):
     return out
 
 
-def bn_bwd_reduce(dy, y, x, mean_invstd, sums):
-    call("pdac_bn_bwd_reduce", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(sums), _stream())
+def bn_bwd_reduce(dy, y, x, mean_invstd, sums, scale_shift=None):
+    """y: ReLU output for the mask, or None with scale_shift given to recompute the mask from x (y is not read)."""
+    call("pdac_bn_bwd_reduce", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(scale_shift), _ptr(sums), _stream())
     return sums
 
 
-def bn_bwd_apply(dy, y, x, mean_invstd, gamma, sums, count, train, dx=None, dz_out=None, dgamma=None, dbeta=None):
+def bn_bwd_apply(dy, y, x, mean_invstd, gamma, sums, count, train, dx=None, dz_out=None, dgamma=None, dbeta=None,
+                 scale_shift=None):
     if dx is None:
         dx = torch.empty_like(dy)
-    call("pdac_bn_bwd_apply", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(gamma), _ptr(sums), float(count),
+    call("pdac_bn_bwd_apply", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(gamma), _ptr(scale_shift), _ptr(sums),
+         float(count),
          int(bool(train)), _vp(dx), _vp(dz_out), _ptr(dgamma), _ptr(dbeta), _stream())
     return dx
 
