@@ -89,6 +89,11 @@ typedef struct PdacTapConv {
  * atomically accumulated (BatchNorm batch statistics); caller zeroes it. */
 int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
                      const float* bias, const PdacView* addend, const PdacView* out, float* stats, void* stream);
+/* Same with a per-channel affine epilogue: out = act( acc * scale[c] + shift[c] + addend ) — eval-mode BatchNorm
+ * (+ residual + ReLU) folded into the convolution (test.py:139-142 inference, torchvision resnet.py:92-103). */
+int pdac_tapconv_fwd_affine(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
+                            const float* scale, const float* shift, const PdacView* addend, const PdacView* out,
+                            void* stream);
 /* dw[t*tap_stride + a*a_stride + b*b_stride] += sum_pixels cat(views)[p + off_t, a] * dy[p, b]  (fp32 atomics;
  * caller zeroes dw). a runs over the concatenated source channels, b over the first b_valid channels of dy
  * (0 = all; dy may be channel-padded). */
@@ -99,6 +104,8 @@ int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const PdacView* views
  * row (r*S+s)*wrows + cout. */
 int pdac_conv2d_fwd(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed, const float* bias,
                     const PdacView* addend, const PdacView* out, float* stats, void* stream);
+int pdac_conv2d_fwd_affine(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed, const float* scale,
+                           const float* shift, const PdacView* addend, const PdacView* out, void* stream);
 /* dx = conv_transpose(dy, w) (+ addend): the data gradient of the conv described by cv. w_packed_t:
  * [R*S*wrows][Cout] with row (r*S+s)*wrows + cin (taps un-flipped: the library derives the offsets). For
  * stride 2 the four output parity classes are separate launches; classes no tap reaches get addend or zero. */

@@ -42,6 +42,8 @@ SIGNATURES = {
     "pdac_tapconv_fwd": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
     "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _i, _p],
     "pdac_conv2d_fwd": [C.POINTER(PdacConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
+    "pdac_conv2d_fwd_affine": [C.POINTER(PdacConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
+    "pdac_tapconv_fwd_affine": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
     "pdac_conv2d_dgrad": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, _p],
     "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _i, _p],
     "pdac_convt2x2_fwd": [_VP, _p, _i, _p, _i, _VP, _p],

@@ -87,20 +87,33 @@ __global__ void __launch_bounds__(256) scale_shift_act_kernel(Flat x, const floa
     sc[i] = ss ? ss[g * 8 + i] : 1.f;
     sh[i] = ss ? ss[x.C + g * 8 + i] : 0.f;
   }
-  for (long long p = pfirst; p < x.npix; p += pstep) {
-    F8 a = unpack8(ld16_stream(x.ptr + p * x.ps + g * 8));
-#pragma unroll
-    for (int i = 0; i < 8; ++i) a.v[i] = fmaf(a.v[i], sc[i], sh[i]);
+  for (long long p = pfirst; p < x.npix; p += 2 * pstep) {
+    const long long p2 = p + pstep;
+    const bool two = p2 < x.npix;
+    uint4 rx[2], rr[2];
+    rx[0] = ld16_stream(x.ptr + p * x.ps + g * 8);
+    if (two) rx[1] = ld16_stream(x.ptr + p2 * x.ps + g * 8);
     if (res.ptr) {
-      const F8 r = unpack8(ld16_stream(res.ptr + p * res.ps + g * 8));
-#pragma unroll
-      for (int i = 0; i < 8; ++i) a.v[i] += r.v[i];
+      rr[0] = ld16_stream(res.ptr + p * res.ps + g * 8);
+      if (two) rr[1] = ld16_stream(res.ptr + p2 * res.ps + g * 8);
     }
-    if (relu) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) a.v[i] = fmaxf(a.v[i], 0.f);
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+      F8 a = unpack8(rx[u]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a.v[i] = fmaf(a.v[i], sc[i], sh[i]);
+      if (res.ptr) {
+        const F8 r = unpack8(rr[u]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a.v[i] += r.v[i];
+      }
+      if (relu) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a.v[i] = fmaxf(a.v[i], 0.f);
+      }
+      st16(y.ptr + (u ? p2 : p) * y.ps + g * 8, pack8(a));
     }
-    st16(y.ptr + p * y.ps + g * 8, pack8(a));
   }
 }
 

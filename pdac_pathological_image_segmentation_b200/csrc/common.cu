@@ -21,6 +21,10 @@ int cuda_fail(cudaError_t e, const char* what) {
               "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
 }
 
+static thread_local const float* g_epi_scale = nullptr;
+void set_epi_scale(const float* scale) { g_epi_scale = scale; }
+const float* epi_scale() { return g_epi_scale; }
+
 static thread_local int g_last_kernel = 0;
 void note_kernel(int id) { g_last_kernel = id; }
 int last_kernel() { return g_last_kernel; }

@@ -46,6 +46,11 @@ int* device_err_flag();  // device pointer to the pipeline error flag
 enum { KID_NONE = 0, KID_CONV_TC = 1, KID_CONV_HALO = 2, KID_WGRAD_TC = 3, KID_WGRAD_HALO = 4 };
 void note_kernel(int id);
 
+// Per-channel epilogue scale of the next tap convolution launched by this thread (set by the *_affine entry points:
+// eval-mode BatchNorm folded into the GEMM epilogue as y = act(acc * scale + shift + addend)).
+void set_epi_scale(const float* scale);
+const float* epi_scale();
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int pow2_ceil(int x) {
   int p = 1;

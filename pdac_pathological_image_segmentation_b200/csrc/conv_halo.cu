@@ -16,6 +16,7 @@
 // (accumulators of a tile alternate between them), warp 10 = weight TMA producer.
 #include "common.h"
 #include "ptx.cuh"
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -46,6 +47,7 @@ struct HaloParams {
   const bf16* addend;
   long long asN, asH, asW;
   const float* bias;
+  const float* scale;
   float* stats;
   int relu;
   int* err;
@@ -107,7 +109,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
 
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + (size_t)p.sa * p.a_buf;
-  const int b_bytes = (p.b_resident ? p.n_taps * p.n_chunks : p.sb) * p.b_sub;
+  const int b_bytes = (p.b_resident ? p.n_taps * p.n_chunks : p.sb * p.tap_S) * p.b_sub;
   uint8_t* smem_stg = smem_b + b_bytes;
 
   // this CTA's share: a fixed N tile and every ctas_sp-th spatial tile
@@ -183,11 +185,13 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
         int itb = 0;
         for (int sp = sp0; sp < p.tiles_sp; sp += sp_step) {
           for (int c = 0; c < p.n_chunks; ++c) {
-            for (int t = 0; t < p.n_taps; ++t, ++itb) {
+            for (int r = 0; r < p.tap_R; ++r, ++itb) {  // one stage = the tap_S taps of a kernel row
               const int stage = itb % p.sb;
               mbar_wait(&empty_b[stage], ((itb / p.sb) & 1) ^ 1, p.err);
-              mbar_expect_tx(&full_b[stage], (uint32_t)p.b_sub);
-              tma_load_2d(smem_b + (size_t)stage * p.b_sub, &maps.w, &full_b[stage], c * p.ck, t * p.wrows + n0);
+              mbar_expect_tx(&full_b[stage], (uint32_t)(p.tap_S * p.b_sub));
+              for (int s = 0; s < p.tap_S; ++s)
+                tma_load_2d(smem_b + (size_t)(stage * p.tap_S + s) * p.b_sub, &maps.w, &full_b[stage], c * p.ck,
+                            (r * p.tap_S + s) * p.wrows + n0);
             }
           }
         }
@@ -244,21 +248,24 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
               umma_commit(&empty_a[stage]);
             }
           } else {
+            // streamed weights: one ring stage holds the TS taps of a kernel row, so the warp-wide barrier wait and
+            // the re-divergence around the issue (~150 cycles) are paid once per TS * NACC * KS MMAs
             uint32_t acc = c ? 1u : 0u;
             uint32_t a_row = a_stage;
-            for (int r = 0; r < TR; ++r, a_row += step_r) {
-              uint32_t a_lo = a_row;
-              for (int s = 0; s < TS; ++s, a_lo += step_s, ++itb) {
-                const int bstage = itb % sb;
-                mbar_wait(&full_b[bstage], (itb / sb) & 1, p.err);
-                tc_fence_after();
-                if (leader) {
-                  halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo0 + (uint32_t)bstage * b_sub16, desc_hi, idesc,
-                                       acc);
-                  umma_commit(&empty_b[bstage]);
+            for (int r = 0; r < TR; ++r, a_row += step_r, ++itb) {
+              const int bstage = itb % sb;
+              mbar_wait(&full_b[bstage], (itb / sb) & 1, p.err);
+              tc_fence_after();
+              if (leader) {
+                uint32_t a_lo = a_row;
+                uint32_t b_lo = b_lo0 + (uint32_t)(bstage * TS) * b_sub16;
+                for (int s = 0; s < TS; ++s, a_lo += step_s, b_lo += b_sub16) {
+                  halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo, desc_hi, idesc, acc);
+                  acc = 1u;
                 }
-                acc = 1u;
+                umma_commit(&empty_b[bstage]);
               }
+              acc = 1u;
             }
             if (leader) umma_commit(&empty_a[stage]);
           }
@@ -326,6 +333,11 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
                 float f[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+                if (p.scale) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    if (c0 + c + i < nch) f[i] *= __ldg(p.scale + n0 + c0 + c + i);
+                }
                 if (p.bias) {
 #pragma unroll
                   for (int i = 0; i < 16; ++i)
@@ -466,7 +478,7 @@ struct HaloPlan {
 
 // Picks the tile. Cost model (cycles per image, per SM share): MMA issue = tiles * nacc * taps * K16-steps * max(N/2, 10)
 // against bytes moved (halo in + tile out) at ~40 B/cycle/SM; the larger of the two plus a per-tile overhead.
-static bool plan_halo(int H, int W, int N, int n_taps, int n_chunks, int ck, int eh, int ew, int has_addend,
+static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int ck, int eh, int ew, int has_addend,
                       HaloPlan* best) {
   const int pitch = ck * 2;
   const int max_nacc = 256 / N < 4 ? 256 / N : 4;
@@ -509,11 +521,12 @@ static bool plan_halo(int H, int W, int N, int n_taps, int n_chunks, int ck, int
             sa = (int)((kSmemBudget - fixed - w_bytes) / a_buf);
             sb = 0;
           } else {
-            sb = 4;
-            sa = (int)((kSmemBudget - fixed - (long long)sb * N * pitch) / a_buf);
+            const long long row_bytes = (long long)ts * N * pitch;  // one ring stage = a kernel row of taps
+            sb = 2;
+            sa = (int)((kSmemBudget - fixed - sb * row_bytes) / a_buf);
             if (sa > 3) {  // spend the rest on a deeper weight ring
               sa = 3;
-              sb = (int)((kSmemBudget - fixed - 3LL * a_buf) / (N * pitch));
+              sb = (int)((kSmemBudget - fixed - 3LL * a_buf) / row_bytes);
               if (sb > kHaloMaxSB) sb = kHaloMaxSB;
             }
           }
@@ -527,8 +540,9 @@ static bool plan_halo(int H, int W, int N, int n_taps, int n_chunks, int ck, int
         double bytes = (double)tiles * R * PW * n_chunks * pitch + (double)H * W * N * 2 * (has_addend ? 2 : 1);
         if (!res) bytes += (double)tiles * w_bytes;
         const double mem_cyc = bytes / 40.0;
-        const double cost = (mma_cyc > mem_cyc ? mma_cyc : mem_cyc) + 0.15 * (mma_cyc < mem_cyc ? mma_cyc : mem_cyc) +
-                            300.0 * tiles;
+        double cost = (mma_cyc > mem_cyc ? mma_cyc : mem_cyc) + 0.5 * (mma_cyc < mem_cyc ? mma_cyc : mem_cyc) +
+                      300.0 * tiles;
+        if (!res) cost += 150.0 * tiles * (n_taps / ts) * n_chunks;  // per weight stage: barrier wait + commit in the issue path
         if (cost < best->cost) {
           best->cost = cost;
           best->TW = TW;
@@ -586,9 +600,24 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   const int chunks0 = views[0].C / ck;
   const int n_chunks = chunks0 + (tc->n_cat > 1 ? views[1].C / ck : 0);
   const int ktot = n_chunks * ck;
+  int tap_s = 1;  // taps per kernel row (the tap list is an (r, s) grid, verified below)
+  while (tap_s < tc->n_taps && tc->taps[tap_s].dh == tc->taps[0].dh) ++tap_s;
+  if (tc->n_taps % tap_s) return PDAC_OK;
   HaloPlan pl = {0, 0, 0, 0, 0, 0, 0, 0.0};
-  if (!plan_halo(out->H, out->W, block_n, tc->n_taps, n_chunks, ck, eh, ew, addend != nullptr, &pl)) return PDAC_OK;
+  if (!plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, &pl))
+    return PDAC_OK;
 
+  {
+    static int dbg = -1;
+    if (dbg < 0) {
+      const char* e = getenv("PDAC_HALO_DEBUG");
+      dbg = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (dbg)
+      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d cost=%.0f\n",
+              out->N, out->H, out->W, n_chunks, ck, block_n, tc->n_taps, pl.TW, pl.TH, pl.nacc, pl.sa, pl.sb,
+              pl.b_resident, pl.n_wg, pl.cost);
+  }
   HaloMaps maps;
   HaloParams p;
   memset(&p, 0, sizeof(p));
@@ -657,6 +686,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
                                   addend->sN % 8 == 0)),
                  "out/addend view must be 16-byte aligned");
   p.bias = bias;
+  p.scale = epi_scale();
   p.stats = stats;
   p.relu = tc->relu;
   p.err = device_err_flag();
@@ -668,7 +698,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     uint32_t box[2] = {(uint32_t)ck, (uint32_t)block_n};
     PDAC_TRY(encode_tiled_bf16(&maps.w, w_packed, 2, dims, strides, box, p.pitch));
   }
-  const size_t b_bytes = (size_t)(p.b_resident ? p.n_taps * p.n_chunks : p.sb) * p.b_sub;
+  const size_t b_bytes = (size_t)(p.b_resident ? p.n_taps * p.n_chunks : p.sb * p.tap_S) * p.b_sub;
   const size_t smem = (size_t)p.sa * p.a_buf + b_bytes + (size_t)p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16) + 1024;
   PDAC_REQUIRE(smem <= 221 * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
   int per_n = num_sms() / p.tiles_c;

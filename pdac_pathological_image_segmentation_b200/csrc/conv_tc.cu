@@ -50,6 +50,7 @@ struct ConvKParams {
   const bf16* addend;
   long long asN, asH, asW;
   const float* bias;
+  const float* scale;
   float* stats;
   int relu;
   int* err;
@@ -238,6 +239,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         float f[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+        if (p.scale) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (c + i < nch) f[i] *= __ldg(p.scale + n0 + c + i);
+        }
         if (p.bias) {
 #pragma unroll
           for (int i = 0; i < 16; ++i)
@@ -660,6 +666,7 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
                                   addend->sN % 8 == 0)),
                  "out/addend view must be 16-byte aligned");
   p.bias = bias;
+  p.scale = epi_scale();
   p.stats = stats;
   p.relu = tc->relu;
   p.err = device_err_flag();
@@ -853,6 +860,26 @@ extern "C" int pdac_conv2d_fwd(const PdacConv* cv, int n_src, const PdacView* sr
   int nv = 0;
   PDAC_TRY(build_fwd_taps(cv, n_src, src, &tc, views, &nv));
   return pdac_tapconv_fwd(&tc, nv, views, w_packed, bias, addend, out, stats, stream);
+}
+
+extern "C" int pdac_conv2d_fwd_affine(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed,
+                                      const float* scale, const float* shift, const PdacView* addend,
+                                      const PdacView* out, void* stream) {
+  PDAC_REQUIRE(scale && shift, "conv2d_fwd_affine: null scale / shift");
+  set_epi_scale(scale);
+  const int rc = pdac_conv2d_fwd(cv, n_src, src, w_packed, shift, addend, out, nullptr, stream);
+  set_epi_scale(nullptr);
+  return rc;
+}
+
+extern "C" int pdac_tapconv_fwd_affine(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
+                                       const float* scale, const float* shift, const PdacView* addend,
+                                       const PdacView* out, void* stream) {
+  PDAC_REQUIRE(scale && shift, "tapconv_fwd_affine: null scale / shift");
+  set_epi_scale(scale);
+  const int rc = pdac_tapconv_fwd(tc, n_views, views, w_packed, shift, addend, out, nullptr, stream);
+  set_epi_scale(nullptr);
+  return rc;
 }
 
 extern "C" int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,

@@ -89,34 +89,55 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(V4 x, V4 y, uint8_t* _
   }
 }
 
+// One thread produces the 2x2 block (2i+a, 2j+b) of dx for 8 channels: those four pixels are covered by the windows
+// (i,j), (i,j+1), (i+1,j), (i+1,j+1) only, so each window's arg-max bytes and gradient are loaded once for four outputs.
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(V4 dy, const uint8_t* __restrict__ idx, V4 dx) {
   const int cg = dx.C / 8;
-  const long long total = (long long)dx.N * dx.H * dx.W * cg;
+  const int bh = (dx.H + 1) >> 1, bw = (dx.W + 1) >> 1;
+  const long long total = (long long)dx.N * bh * bw * cg;
   PIX_LOOP(total) {
-    DECODE(e, cg, dx.W, dx.H)
-    float acc[8];
+    DECODE(e, cg, bw, bh)
+    float acc[4][8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-    const int oh_lo = h >> 1, oh_hi = (h + 1) >> 1;  // windows with 2*oh-1 <= h <= 2*oh+1
-    const int ow_lo = w >> 1, ow_hi = (w + 1) >> 1;
-    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
-      if (oh >= dy.H) continue;
-      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-        if (ow >= dy.W) continue;
-        const int tap = (h - (2 * oh - 1)) * 3 + (w - (2 * ow - 1));
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[q][i] = 0.f;
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int oh = h + a, ow = w + b;  // window (oh, ow) covers rows 2*oh-1 .. 2*oh+1
+        if (oh >= dy.H || ow >= dy.W) continue;
         const uint2 p = __ldg(reinterpret_cast<const uint2*>(idx + (((long long)n * dy.H + oh) * dy.W + ow) * dx.C + g * 8));
         const F8 d = unpack8(ld16(dy.at(n, oh, ow) + g * 8));
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int b = (int)(((i < 4 ? p.x : p.y) >> ((i & 3) * 8)) & 0xff);
-          if (b == tap) acc[i] += d.v[i];
+        for (int pa = 0; pa < 2; ++pa) {
+#pragma unroll
+          for (int pb = 0; pb < 2; ++pb) {
+            // pixel (2h+pa, 2w+pb) sits at tap (2h+pa - (2oh-1), 2w+pb - (2ow-1)) of this window, if inside 0..2
+            const int tr = pa + 1 - 2 * a, tc = pb + 1 - 2 * b;
+            if (tr < 0 || tr > 2 || tc < 0 || tc > 2) continue;
+            const int tap = tr * 3 + tc;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int bt = (int)(((i < 4 ? p.x : p.y) >> ((i & 3) * 8)) & 0xff);
+              if (bt == tap) acc[pa * 2 + pb][i] += d.v[i];
+            }
+          }
         }
       }
     }
-    F8 o;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
-    st16(dx.at(n, h, w) + g * 8, pack8(o));
+    for (int pa = 0; pa < 2; ++pa)
+#pragma unroll
+      for (int pb = 0; pb < 2; ++pb) {
+        const int hh = 2 * h + pa, ww = 2 * w + pb;
+        if (hh >= dx.H || ww >= dx.W) continue;
+        F8 o;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o.v[i] = acc[pa * 2 + pb][i];
+        st16(dx.at(n, hh, ww) + g * 8, pack8(o));
+      }
   }
 }
 
@@ -400,7 +421,7 @@ extern "C" int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, con
   PDAC_REQUIRE(idx, "maxpool bwd: null idx");
   PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C && vdy.H == (vdx.H - 1) / 2 + 1 && vdy.W == (vdx.W - 1) / 2 + 1,
                "maxpool bwd: shape mismatch");
-  const long long total = (long long)vdx.N * vdx.H * vdx.W * (vdx.C / 8);
+  const long long total = (long long)vdx.N * ((vdx.H + 1) / 2) * ((vdx.W + 1) / 2) * (vdx.C / 8);
   if (!total) return PDAC_OK;
   maxpool_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vdy, idx, vdx);
   PDAC_LAUNCH_CHECK("maxpool_bwd");

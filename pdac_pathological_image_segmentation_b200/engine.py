@@ -210,6 +210,11 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
     wp_f, wp_t, _ = tape.packs.conv(m)
     k = m.k
     dev = srcs[0].device
+    if not tape.training and not tape.enabled:
+        # inference: BatchNorm is a per-channel affine map -> folded (with the residual and the ReLU) into the conv epilogue
+        st = _bn_prepare(tape, bn, None, 1, dev)
+        return ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, relu=relu, bias=st.ss[1],
+                              addend=residual, scale=st.ss[0], out=out)
     stats = torch.zeros((2, m.cout), dtype=F32, device=dev) if tape.training else None
     x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
@@ -245,6 +250,9 @@ def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
     """7x7 s2 p3 conv + BN + ReLU on the space-to-depth input z (N, H/2, W/2, 16) as a 4x4 s1 tap convolution."""
     wp = tape.packs.stem(m)
     dev = z.device
+    if not tape.training and not tape.enabled:
+        st = _bn_prepare(tape, bn, None, 1, dev)
+        return ops.stem_conv_fwd(z, wp, m.cout, scale=st.ss[0], shift=st.ss[1], relu=True)
     stats = torch.zeros((2, m.cout), dtype=F32, device=dev) if tape.training else None
     x = ops.stem_conv_fwd(z, wp, m.cout, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)

@@ -77,7 +77,7 @@ def _act_bytes(*ts):
 
 
 def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=None, addend=None, stats=None,
-               out=None, c_real=None):
+               out=None, c_real=None, scale=None):
     """out = [relu](conv(cat(srcs), w) + bias + addend); optional BN statistics (fp32 [2, cout], pre-zeroed)."""
     x0 = srcs[0]
     ho, wo = conv_out_hw(x0.shape[1], x0.shape[2], R, S, stride, pad, dil)
@@ -88,6 +88,13 @@ def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=No
     assert wp.dtype == BF16 and wp.is_contiguous() and wp.shape[1] == ktot, (wp.shape, ktot)
     cv = _conv_struct(R, S, stride, pad, dil, relu, wrows)
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
+    if scale is not None:        # out = act(acc * scale + bias + addend): eval-mode BatchNorm folded into the epilogue
+        assert stats is None and bias is not None
+        call("pdac_conv2d_fwd_affine", C.byref(cv), len(srcs), views, _ptr(wp), _ptr(scale), _ptr(bias), _vp(addend),
+             _vp(out), _stream(), flops=2 * x0.shape[0] * ho * wo * (c_real or cout) * ktot * R * S,
+             nbytes=_act_bytes(out, addend, *srcs),
+             tag=f"fwd+bn {R}x{S}s{stride}d{dil} {x0.shape[0]}x{ho}x{wo} {ktot}->{cout}")
+        return out
     call("pdac_conv2d_fwd", C.byref(cv), len(srcs), views, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
          _stream(), flops=2 * x0.shape[0] * ho * wo * (c_real or cout) * ktot * R * S,
          nbytes=_act_bytes(out, addend, *srcs),
@@ -161,10 +168,16 @@ def _tapconv(taps, n_cat, wrows, relu):
     return tc
 
 
-def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=None, stats=None, flops=0):
-    """Generalised tap convolution (pdac_tapconv_fwd): taps = [(first view index, dh, dw), ...]."""
+def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=None, stats=None, flops=0, scale=None):
+    """Generalised tap convolution (pdac_tapconv_fwd): taps = [(first view index, dh, dw), ...]. With `scale` the
+    epilogue is act(acc * scale + bias + addend) (pdac_tapconv_fwd_affine; no statistics)."""
     tc = _tapconv(taps, n_cat, wp.shape[0] // len(taps), relu)
     vs = (PdacView * len(views))(*[view(v) for v in views])
+    if scale is not None:
+        assert stats is None and bias is not None
+        call("pdac_tapconv_fwd_affine", C.byref(tc), len(views), vs, _ptr(wp), _ptr(scale), _ptr(bias), _vp(addend),
+             _vp(out), _stream(), flops=flops, nbytes=_act_bytes(out, addend, *views[:n_cat]))
+        return out
     call("pdac_tapconv_fwd", C.byref(tc), len(views), vs, _ptr(wp), _ptr(bias), _vp(addend), _vp(out), _ptr(stats),
          _stream(), flops=flops, nbytes=_act_bytes(out, addend, *views[:n_cat]))
     return out
@@ -183,10 +196,10 @@ def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1, 
 STEM_TAPS = [(0, a - 2, b - 2) for a in range(4) for b in range(4)]
 
 
-def stem_conv_fwd(z, wp, cout, stats=None, out=None):
+def stem_conv_fwd(z, wp, cout, stats=None, out=None, scale=None, shift=None, relu=False):
     if out is None:
         out = empty_act(z.shape[0], z.shape[1], z.shape[2], cout, z.device)
-    return tapconv_fwd([z], STEM_TAPS, wp, out, stats=stats,
+    return tapconv_fwd([z], STEM_TAPS, wp, out, stats=stats, scale=scale, bias=shift, relu=relu,
                        flops=2 * out.shape[0] * out.shape[1] * out.shape[2] * cout * 147)
 
 

@@ -129,7 +129,10 @@ def test_resunet_eval_matches_reference_golden(nc):
     # eval-mode forward WITH grad (reference quirk: epochs >= 2 train in eval mode)
     out2 = m(R.normalize(img).to(DEV))
     out2.sum().backward()
-    assert (out2 - out).abs().max().item() == 0.0
+    # the no-grad forward folds BatchNorm into the conv epilogue (x is never rounded to bf16), the grad-enabled one
+    # keeps x for backward: same arithmetic up to that one rounding per layer
+    assert (out2 - out).abs().max().item() <= 1e-2
+    assert (out2 - ref).abs().max().item() <= 2e-2
     assert m.conv4.weight.grad is not None and torch.isfinite(m.encoder.conv1.weight.grad).all()
 
 
