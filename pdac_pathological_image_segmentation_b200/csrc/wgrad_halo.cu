@@ -41,6 +41,7 @@ struct WhMaps {
 
 struct WhParams {
   WhSlab slabs[kWhMaxSlabs];
+  uint8_t cg_first[kWhMaxSlabs + 1];  // slabs of chunk group cg: [cg_first[cg], cg_first[cg + 1])
   int n_slabs, spc;        // total slabs, slabs per CTA (grid.y = ceil(n_slabs / spc))
   int n_cg, cps;           // chunk groups per K block, chunks per group
   int chunks0, n_chunks, ck;
@@ -152,22 +153,22 @@ __global__ void __launch_bounds__(kWhThreads, 1) wgrad_halo_kernel(const __grid_
       mbar_wait(&fullB[bs], (i >> 1) & 1, p.err);
       tc_fence_after();
       const uint32_t b_lo = b_lo0 + (uint32_t)bs * b_tile16;
-      int s = slab0;
       for (int cg = cg_lo; cg <= cg_hi; ++cg, ++ita) {
         const int stage = ita % stages_a;
         mbar_wait(&fullA[stage], (ita / stages_a) & 1, p.err);
         tc_fence_after();
-        const uint32_t st_lo = a_lo0 + (uint32_t)stage * a_stage16;
-        for (; s < slab1 && p.slabs[s].cg == cg; ++s) {
-          if (leader) {
+        if (leader) {  // one divergent region per halo stage: all of its slabs back to back
+          const uint32_t st_lo = a_lo0 + (uint32_t)stage * a_stage16;
+          const int s_lo = max((int)p.cg_first[cg], slab0), s_hi = min((int)p.cg_first[cg + 1], slab1);
+          for (int s = s_lo; s < s_hi; ++s) {
             const uint32_t a_lo = (st_lo + p.slabs[s].a_off16) | (p.slabs[s].lbo16 << 16);
             const uint32_t td = tmem_base + (uint32_t)(s - slab0) * block_n;
             umma_bf16_lohi(td, a_lo, hi_a, b_lo, hi_b, idesc, i > 0 ? 1u : 0u);
 #pragma unroll
             for (int k = 1; k < 8; ++k) umma_bf16_lohi(td, a_lo + k * ka16, hi_a, b_lo + k * kb16, hi_b, idesc, 1u);
           }
+          umma_commit(&emptyA[stage]);
         }
-        if (leader) umma_commit(&emptyA[stage]);
       }
       if (leader) umma_commit(&emptyB[bs]);
       __syncwarp();
@@ -337,6 +338,13 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
     }
   }
   p.n_slabs = ns;
+  {
+    int s = 0;
+    for (int cg = 0; cg <= p.n_cg; ++cg) {
+      while (s < ns && p.slabs[s].cg < cg) ++s;
+      p.cg_first[cg] = (uint8_t)s;
+    }
+  }
   int spc_max = 512 / block_n;
   if (spc_max > ns) spc_max = ns;
   const int ygroups = ceil_div(ns, spc_max);
