@@ -144,10 +144,15 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(V4 dy, const uint8_t* 
 // ------------------------------------------------------------------------------------------------ nearest x2
 __global__ void __launch_bounds__(256) up2_fwd_kernel(V4 x, V4 y) {
   const int cg = x.C / 8;
-  const long long total = (long long)y.N * y.H * y.W * cg;
+  const long long total = (long long)x.N * x.H * x.W * cg;  // one thread per INPUT vector: 1 load, 4 stores
   PIX_LOOP(total) {
-    DECODE(e, cg, y.W, y.H)
-    st16(y.at(n, h, w) + g * 8, ld16(x.at(n, h >> 1, w >> 1) + g * 8));
+    DECODE(e, cg, x.W, x.H)
+    const uint4 v = ld16_stream(x.at(n, h, w) + g * 8);
+    bf16* o = y.at(n, 2 * h, 2 * w) + g * 8;
+    st16(o, v);
+    st16(o + y.sW, v);
+    st16(o + y.sH, v);
+    st16(o + y.sH + y.sW, v);
   }
 }
 // dx = sum of the 2x2 block of dy (+ addend)
@@ -433,7 +438,7 @@ extern "C" int pdac_upsample_nearest2x_fwd(const PdacView* x, const PdacView* y,
   PDAC_TRY(to_v4(x, &vx, "x"));
   PDAC_TRY(to_v4(y, &vy, "y"));
   PDAC_REQUIRE(vy.N == vx.N && vy.C == vx.C && vy.H == 2 * vx.H && vy.W == 2 * vx.W, "nearest2x: shape mismatch");
-  const long long total = (long long)vy.N * vy.H * vy.W * (vx.C / 8);
+  const long long total = (long long)vx.N * vx.H * vx.W * (vx.C / 8);
   if (!total) return PDAC_OK;
   up2_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vx, vy);
   PDAC_LAUNCH_CHECK("up2_fwd");

@@ -246,8 +246,9 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   }
   if (ck < 16 || dy->C % 16) return PDAC_OK;
   const int cout = dy->C;
-  if (cout > 128) return PDAC_OK;  // wide outputs: few slabs fit TMEM, the generic kernel does as well
-  const int block_n = cout;
+  if (cout > 128 && cout % 128) return PDAC_OK;
+  const int block_n = cout > 128 ? 128 : cout;  // wider outputs: 128-column pieces over grid.z (dY is split, X re-read)
+  const int zgroups = cout / block_n;
   int ckb = 64;
   while (cout % ckb) ckb >>= 1;
 
@@ -372,7 +373,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   for (int s = 0; s < tc->n_cat; ++s) PDAC_TRY(encode_view_map(&maps.a[s], &views[s], ck, p.PW, p.R, 1));
   if (tc->n_cat == 1) maps.a[1] = maps.a[0];
   PDAC_TRY(encode_view_map(&maps.dy, dy, ckb, 16, 8, 1));
-  int splits = num_sms() / ygroups;
+  int splits = num_sms() / (ygroups * zgroups);
   if (splits < 1) splits = 1;
   if (splits > p.n_kblocks) splits = p.n_kblocks;
   const size_t smem = (size_t)stages_a * a_stage + 2 * (size_t)b_tile + 1024;
@@ -381,7 +382,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
     PDAC_CUDA(cudaFuncSetAttribute(wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(222 * 1024)));
     attr_set = true;
   }
-  dim3 grid(splits, ygroups, 1);
+  dim3 grid(splits, ygroups, zgroups);
   wgrad_halo_kernel<<<grid, kWhThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_halo_kernel");
   note_kernel(KID_WGRAD_HALO);
