@@ -147,21 +147,47 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
-#define HALO_DECODE(sp)                         \
-  int r_ = (sp);                                \
-  const int tile_w = r_ % p.tiles_w;            \
-  r_ /= p.tiles_w;                              \
-  const int tile_h = r_ % p.tiles_h;            \
-  const int img = r_ / p.tiles_h;               \
-  const int w0 = tile_w * p.TW, h0 = tile_h * p.TH;
+  // Spatial tile walker: tile index sp = (img * tiles_h + tile_h) * tiles_w + tile_w advances by sp_step per iteration;
+  // the decomposition is carried incrementally (a handful of integer divisions per tile and thread used to cost more
+  // than the epilogue proper on the 16-channel layers).
+  struct Walk {
+    int tw, th, img, dw, dh, dimg;
+  };
+  auto walk_init = [&](Walk& k) {
+    int r = sp0;
+    k.tw = r % p.tiles_w;
+    r /= p.tiles_w;
+    k.th = r % p.tiles_h;
+    k.img = r / p.tiles_h;
+    int d = sp_step;
+    k.dw = d % p.tiles_w;
+    d /= p.tiles_w;
+    k.dh = d % p.tiles_h;
+    k.dimg = d / p.tiles_h;
+  };
+  auto walk_next = [&](Walk& k) {
+    k.tw += k.dw;
+    if (k.tw >= p.tiles_w) {
+      k.tw -= p.tiles_w;
+      ++k.th;
+    }
+    k.th += k.dh;
+    if (k.th >= p.tiles_h) {
+      k.th -= p.tiles_h;
+      ++k.img;
+    }
+    k.img += k.dimg;
+  };
 
   if (warp == 0) {
     // ------------------------------------------------------------------ halo producer
     if (lane == 0 && sp0 < sp_step) {
       const uint32_t halo_bytes = (uint32_t)(p.R * p.PW) * p.pitch;
       int ita = 0;
-      for (int sp = sp0; sp < p.tiles_sp; sp += sp_step) {
-        HALO_DECODE(sp)
+      Walk wk;
+      walk_init(wk);
+      for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, walk_next(wk)) {
+        const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
         for (int c = 0; c < p.n_chunks; ++c, ++ita) {
           const int stage = ita % p.sa;
           mbar_wait(&empty_a[stage], ((ita / p.sa) & 1) ^ 1, p.err);
@@ -297,15 +323,22 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
     for (int i = 0; i < 16; ++i) acc[0][i] = acc[1][i] = 0.f;
 
     int lt = 0;
+    Walk wk;
+    walk_init(wk);
+    const int nacc_mod = p.nacc % p.n_wg;
+    int wg_off = 0;  // (lt * nacc) % n_wg, carried incrementally
     if (sp0 < sp_step)
-      for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt) {
-        HALO_DECODE(sp)
+      for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt, walk_next(wk)) {
+        const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
         const int g = lt & 1;
         mbar_wait(&tmem_full_bar[g], (lt >> 1) & 1, p.err);
         tc_fence_after();
         const long long obase = (long long)img * p.osN + (long long)h0 * p.osH + (long long)w0 * p.osW;
         const long long abase = (long long)img * p.asN + (long long)h0 * p.asH + (long long)w0 * p.asW;
-        int j = (wg - (lt * p.nacc) % p.n_wg + p.n_wg) % p.n_wg;
+        int j = wg - wg_off;
+        if (j < 0) j += p.n_wg;
+        wg_off += nacc_mod;
+        if (wg_off >= p.n_wg) wg_off -= p.n_wg;
         if (j >= p.nacc) {  // nothing of this tile is ours: the TMEM stage is free as far as we are concerned
           tc_fence_before();
           mbar_arrive(&tmem_empty_bar[g]);
@@ -453,7 +486,6 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
       }
     }
   }
-#undef HALO_DECODE
 
   tc_fence_before();
   __syncthreads();
