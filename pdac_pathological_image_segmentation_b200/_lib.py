@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpdac_b200.so")
+LIB_PATH = os.environ.get("PDAC_B200_LIB") or os.path.join(_HERE, "libpdac_b200.so")  # override: diagnostic builds
 
 PDAC_MAX_TAPS = 16
 
@@ -133,6 +133,12 @@ def call(name, *args, flops=0, nbytes=0, tag=""):
         rc = getattr(lib, name)(*args)
         e1.record()
         kid = lib.pdac_last_kernel_id() if name.startswith(("pdac_conv", "pdac_tapconv")) else 0
+        if not tag:  # shape of the first view argument, for per-layer tables of the elementwise passes
+            for a in args:
+                v = getattr(a, "_obj", None)
+                if isinstance(v, PdacView):
+                    tag = f"{v.N}x{v.H}x{v.W}x{v.C}"
+                    break
         trace.append((KERNEL_NAMES.get(kid, name), e0, e1, flops, nbytes, tag))
     else:
         rc = getattr(lib, name)(*args)

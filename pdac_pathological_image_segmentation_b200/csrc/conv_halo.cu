@@ -38,6 +38,7 @@ struct HaloParams {
   int nacc, TW, TH, PW, R;
   uint32_t inv_pw;  // ceil(2^20 / PW): o / PW == (o * inv_pw) >> 20 for o < 1024
   int n_wg;         // epilogue warpgroups in use (2 or 4)
+  int w_warp;       // index of the weight-producer warp (= 2 + 4 * n_wg in the two-CTAs-per-SM variant, else 18)
   int tiles_w, tiles_h, tiles_sp;  // spatial tiles per image row / column, total over the batch
   int a_buf, sa;                   // bytes per halo stage, stages
   int b_resident, sb, b_sub;       // weights resident? else ring stages; bytes per (tap, chunk) weight tile
@@ -53,7 +54,34 @@ struct HaloParams {
   int* err;
 };
 
+// -DPDAC_HALO_PROF (make prof): per-CTA cycle counters of where each role waits, read back with pdac_halo_prof_read
+#ifdef PDAC_HALO_PROF
+__device__ long long g_halo_prof[160 * 16];
+__device__ int g_halo_dbg;  // bit 0: no global stores, 1: epilogue only releases TMEM, 2: no MMAs, 3: no statistics
+#define DBG(bit) (dbg_mask & (1 << (bit)))
+#define PROF_DECL(x) long long x = 0
+#define PROF_WAIT(accum, stmt) \
+  {                            \
+    long long _t = clock64();  \
+    stmt;                      \
+    accum += clock64() - _t;   \
+  }
+#define PROF_PUT(slot, v) g_halo_prof[(blockIdx.x % 160) * 16 + (slot)] = (v)
+#else
+#define PROF_DECL(x)
+#define PROF_WAIT(accum, stmt) \
+  { stmt; }
+#define PROF_PUT(slot, v)
+#define DBG(bit) 0
+#endif
+
 static constexpr int kHaloThreads = 64 + 4 * 128 + 32;  // TMA warp, MMA warp, up to 4 epilogue warpgroups, weight warp
+// Two-CTAs-per-SM variant (low channel counts: small tiles, small weights): TMA warp, MMA warp, 2 epilogue warpgroups,
+// weight warp. tcgen05.mma issue is in-order and nearly synchronous with execution (scripts/probe/mma_issue.cu: the
+// issuing thread is held at the execution rate, the queue is only a few instructions deep), so every cycle the single
+// issuing thread spends on barrier waits, commits and loop overhead idles the tensor pipe; a second resident CTA has
+// its own issuing warp and fills those gaps.
+static constexpr int kHaloThreadsDual = 64 + 2 * 128 + 32;
 static constexpr int kHaloMaxSA = 12;
 static constexpr int kHaloMaxSB = 8;
 
@@ -90,9 +118,9 @@ __device__ __forceinline__ void halo_issue(uint32_t tacc, uint32_t acc_step, uin
   }
 }
 
-template <int NACC, int KS>
-__global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid_constant__ HaloMaps maps,
-                                                                    const __grid_constant__ HaloParams p) {
+template <int NACC, int KS, int DUAL>
+__global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ? 2 : 1)
+    conv_halo_kernel(const __grid_constant__ HaloMaps maps, const __grid_constant__ HaloParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_a[kHaloMaxSA];
   __shared__ __align__(8) uint64_t empty_a[kHaloMaxSA];
@@ -106,6 +134,14 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef PDAC_HALO_PROF
+  const int dbg_mask = g_halo_dbg;
+  long long t_k0 = 0, g_k0 = 0;
+  if (threadIdx.x == 0) {
+    t_k0 = clock64();
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_k0));
+  }
+#endif
 
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + (size_t)p.sa * p.a_buf;
@@ -186,19 +222,21 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
       int ita = 0;
       Walk wk;
       walk_init(wk);
+      PROF_DECL(w_ea);
       for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, walk_next(wk)) {
         const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
         for (int c = 0; c < p.n_chunks; ++c, ++ita) {
           const int stage = ita % p.sa;
-          mbar_wait(&empty_a[stage], ((ita / p.sa) & 1) ^ 1, p.err);
+          PROF_WAIT(w_ea, mbar_wait(&empty_a[stage], ((ita / p.sa) & 1) ^ 1, p.err));
           mbar_expect_tx(&full_a[stage], halo_bytes);
           const int s = c >= p.chunks0;
           tma_load_4d(smem_a + (size_t)stage * p.a_buf, &maps.a[s], &full_a[stage], (s ? c - p.chunks0 : c) * p.ck,
                       w0 + p.dw_min, h0 + p.dh_min, img);
         }
       }
+      PROF_PUT(7, w_ea);
     }
-  } else if (warp == 18) {
+  } else if (warp == p.w_warp) {
     // ------------------------------------------------------------------ weight producer
     if (lane == 0 && sp0 < sp_step) {
       if (p.b_resident) {
@@ -209,11 +247,12 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
                         t * p.wrows + n0);
       } else {
         int itb = 0;
+        PROF_DECL(w_eb);
         for (int sp = sp0; sp < p.tiles_sp; sp += sp_step) {
           for (int c = 0; c < p.n_chunks; ++c) {
             for (int r = 0; r < p.tap_R; ++r, ++itb) {  // one stage = the tap_S taps of a kernel row
               const int stage = itb % p.sb;
-              mbar_wait(&empty_b[stage], ((itb / p.sb) & 1) ^ 1, p.err);
+              PROF_WAIT(w_eb, mbar_wait(&empty_b[stage], ((itb / p.sb) & 1) ^ 1, p.err));
               mbar_expect_tx(&full_b[stage], (uint32_t)(p.tap_S * p.b_sub));
               for (int s = 0; s < p.tap_S; ++s)
                 tma_load_2d(smem_b + (size_t)(stage * p.tap_S + s) * p.b_sub, &maps.w, &full_b[stage], c * p.ck,
@@ -221,6 +260,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
             }
           }
         }
+        PROF_PUT(8, w_eb);
       }
     }
   } else if (warp == 1) {
@@ -231,7 +271,12 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
     // block is compile-time unrolled and the taps are walked as an affine (r, s) grid with no table look-ups.
     if (sp0 < sp_step) {
       const uint32_t leader = elect_one();
+#ifdef PDAC_HALO_PROF
+      // bit 4: every MMA computes N = 16 columns only (garbage results; issue-bound vs execution-bound test)
+      const uint32_t idesc = DBG(4) ? ((p.idesc & ~(0x3Fu << 17)) | (2u << 17)) : p.idesc;
+#else
       const uint32_t idesc = p.idesc;
+#endif
       const uint32_t desc_hi = (uint32_t)(make_smem_desc(0, 16, 8 * p.pitch, p.layout_type) >> 32);
       const uint32_t lbo_lo = (16u >> 4) << 16;
       if (p.b_resident) {
@@ -249,17 +294,31 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
       const int TR = p.tap_R, TS = p.tap_S, n_chunks = p.n_chunks, sa = p.sa, sb = p.sb;
       const uint32_t b_tap16 = (uint32_t)n_chunks * b_sub16;
       int ita = 0, itb = 0, lt = 0;
+      PROF_DECL(w_te);
+      PROF_DECL(w_fa);
+      PROF_DECL(w_fb);
+      PROF_DECL(w_cm);
+      PROF_DECL(w_sw);
+      PROF_DECL(w_fn);
+      PROF_DECL(w_ld);
+      PROF_DECL(t_mma0);
+#ifdef PDAC_HALO_PROF
+      t_mma0 = clock64();
+#endif
       for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt) {
         const int g = lt & 1;
-        mbar_wait(&tmem_empty_bar[g], ((lt >> 1) & 1) ^ 1, p.err);
-        tc_fence_after();
+        PROF_WAIT(w_te, mbar_wait(&tmem_empty_bar[g], ((lt >> 1) & 1) ^ 1, p.err));
+        PROF_WAIT(w_fn, tc_fence_after());
         const uint32_t tacc = tmem_base + (uint32_t)(g * NACC) * acc_step;
         for (int c = 0; c < n_chunks; ++c, ++ita) {
           const int stage = ita % sa;
-          mbar_wait(&full_a[stage], (ita / sa) & 1, p.err);
-          tc_fence_after();
+          PROF_WAIT(w_fa, mbar_wait(&full_a[stage], (ita / sa) & 1, p.err));
+          PROF_WAIT(w_fn, tc_fence_after());
           const uint32_t a_stage = a_lo0 + (uint32_t)stage * a_buf16 + tap0;
           if (p.b_resident) {
+#ifdef PDAC_HALO_PROF
+            const long long t_ld0 = clock64();
+#endif
             if (leader) {
               uint32_t b_lo = b_lo0 + (uint32_t)c * b_sub16;
               uint32_t acc = c ? 1u : 0u;
@@ -267,12 +326,15 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
               for (int r = 0; r < TR; ++r, a_row += step_r) {
                 uint32_t a_lo = a_row;
                 for (int s = 0; s < TS; ++s, a_lo += step_s, b_lo += b_tap16) {
-                  halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo, desc_hi, idesc, acc);
+                  if (!DBG(2)) halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo, desc_hi, idesc, acc);
                   acc = 1u;
                 }
               }
-              umma_commit(&empty_a[stage]);
+              PROF_WAIT(w_cm, umma_commit(&empty_a[stage]));
             }
+#ifdef PDAC_HALO_PROF
+            w_ld += clock64() - t_ld0;
+#endif
           } else {
             // streamed weights: one ring stage holds the TS taps of a kernel row, so the warp-wide barrier wait and
             // the re-divergence around the issue (~150 cycles) are paid once per TS * NACC * KS MMAs
@@ -280,25 +342,38 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
             uint32_t a_row = a_stage;
             for (int r = 0; r < TR; ++r, a_row += step_r, ++itb) {
               const int bstage = itb % sb;
-              mbar_wait(&full_b[bstage], (itb / sb) & 1, p.err);
-              tc_fence_after();
+              PROF_WAIT(w_fb, mbar_wait(&full_b[bstage], (itb / sb) & 1, p.err));
+              PROF_WAIT(w_fn, tc_fence_after());
               if (leader) {
                 uint32_t a_lo = a_row;
                 uint32_t b_lo = b_lo0 + (uint32_t)(bstage * TS) * b_sub16;
                 for (int s = 0; s < TS; ++s, a_lo += step_s, b_lo += b_sub16) {
-                  halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo, desc_hi, idesc, acc);
+                  if (!DBG(2)) halo_issue<NACC, KS>(tacc, acc_step, a_lo, j_step, b_lo, desc_hi, idesc, acc);
                   acc = 1u;
                 }
-                umma_commit(&empty_b[bstage]);
+                PROF_WAIT(w_cm, umma_commit(&empty_b[bstage]));
               }
               acc = 1u;
             }
-            if (leader) umma_commit(&empty_a[stage]);
+            PROF_WAIT(w_cm, if (leader) umma_commit(&empty_a[stage]));
           }
         }
-        if (leader) umma_commit(&tmem_full_bar[g]);
-        __syncwarp();
+        PROF_WAIT(w_cm, if (leader) umma_commit(&tmem_full_bar[g]));
+        PROF_WAIT(w_sw, __syncwarp());
       }
+#ifdef PDAC_HALO_PROF
+      if (lane == 0) {
+        PROF_PUT(0, clock64() - t_mma0);
+        PROF_PUT(1, w_te);
+        PROF_PUT(2, w_fa);
+        PROF_PUT(3, w_fb);
+        PROF_PUT(4, (long long)lt);
+        PROF_PUT(10, w_sw);
+        PROF_PUT(11, w_fn);
+        PROF_PUT(12, w_ld);
+      }
+      if (leader) PROF_PUT(9, w_cm);
+#endif
     }
     __syncwarp();
   } else if (warp - 2 < 4 * p.n_wg) {
@@ -318,20 +393,28 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
     const uint32_t bar_id = 1 + wg;
     const int nch = min(p.block_n, p.Cout - n0);
     const bool vec = (p.Cout & 7) == 0;
-    float acc[2][16];
+    constexpr int NPASS = DUAL ? 1 : 2;  // 64-column passes per accumulator (the dual variant has N <= 32)
+    float acc[NPASS][16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) acc[0][i] = acc[1][i] = 0.f;
+    for (int ps = 0; ps < NPASS; ++ps)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) acc[ps][i] = 0.f;
 
     int lt = 0;
     Walk wk;
     walk_init(wk);
+    PROF_DECL(w_tf);
+    PROF_DECL(t_epi0);
+#ifdef PDAC_HALO_PROF
+    t_epi0 = clock64();
+#endif
     const int nacc_mod = p.nacc % p.n_wg;
     int wg_off = 0;  // (lt * nacc) % n_wg, carried incrementally
     if (sp0 < sp_step)
       for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt, walk_next(wk)) {
         const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
         const int g = lt & 1;
-        mbar_wait(&tmem_full_bar[g], (lt >> 1) & 1, p.err);
+        PROF_WAIT(w_tf, mbar_wait(&tmem_full_bar[g], (lt >> 1) & 1, p.err));
         tc_fence_after();
         const long long obase = (long long)img * p.osN + (long long)h0 * p.osH + (long long)w0 * p.osW;
         const long long abase = (long long)img * p.asN + (long long)h0 * p.asH + (long long)w0 * p.asW;
@@ -339,9 +422,10 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
         if (j < 0) j += p.n_wg;
         wg_off += nacc_mod;
         if (wg_off >= p.n_wg) wg_off -= p.n_wg;
-        if (j >= p.nacc) {  // nothing of this tile is ours: the TMEM stage is free as far as we are concerned
+        if (j >= p.nacc || DBG(1)) {  // nothing of this tile is ours: the TMEM stage is free as far as we are concerned
           tc_fence_before();
           mbar_arrive(&tmem_empty_bar[g]);
+          if (DBG(1)) continue;
         }
         for (; j < p.nacc; j += p.n_wg) {
           const int o = j * 128 + m;
@@ -354,7 +438,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
           const uint32_t tacc =
               tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
 #pragma unroll
-          for (int pass = 0; pass < 2; ++pass) {
+          for (int pass = 0; pass < NPASS; ++pass) {
             const int c0 = pass * 64;
             if (c0 < p.block_n) {
               const int cols = min(64, p.block_n - c0);
@@ -430,8 +514,8 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
                 for (int it = 0; it < (1 << cpr_log2); ++it, row += step, saddr += sstep) {
                   const long long off = s_rowoff[wg][row];
                   const uint4 val = lds128(saddr);
-                  if (off >= 0 && ch_ok) *reinterpret_cast<uint4*>(gcol + off) = val;
-                  if (p.stats) {
+                  if (off >= 0 && ch_ok && !DBG(0)) *reinterpret_cast<uint4*>(gcol + off) = val;
+                  if (p.stats && !DBG(3)) {
                     const uint32_t uu[4] = {val.x, val.y, val.z, val.w};
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
@@ -457,11 +541,17 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
           }
         }
       }
+#ifdef PDAC_HALO_PROF
+    if (threadIdx.x == 64) {
+      PROF_PUT(5, clock64() - t_epi0);
+      PROF_PUT(6, w_tf);
+    }
+#endif
     // BatchNorm partial sums: lanes sharing a channel column -> one lane per column -> shared -> (after the final
     // CTA barrier) one global atomic per channel and CTA
     if (p.stats && vec) {
 #pragma unroll
-      for (int pass = 0; pass < 2; ++pass) {
+      for (int pass = 0; pass < NPASS; ++pass) {
         const int c0 = pass * 64;
         if (c0 < p.block_n) {
           const int cols = min(64, p.block_n - c0);
@@ -497,6 +587,15 @@ __global__ void __launch_bounds__(kHaloThreads, 1) conv_halo_kernel(const __grid
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
+#ifdef PDAC_HALO_PROF
+  if (threadIdx.x == 0) {
+    long long g_k1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_k1));
+    PROF_PUT(13, g_k0);
+    PROF_PUT(14, g_k1);
+    PROF_PUT(15, clock64() - t_k0);
+  }
+#endif
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -511,9 +610,13 @@ struct HaloPlan {
 // Picks the tile. Cost model (cycles per image, per SM share): MMA issue = tiles * nacc * taps * K16-steps * max(N/2, 10)
 // against bytes moved (halo in + tile out) at ~40 B/cycle/SM; the larger of the two plus a per-tile overhead.
 static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int ck, int eh, int ew, int has_addend,
-                      HaloPlan* best) {
+                      int dual, HaloPlan* best) {
   const int pitch = ck * 2;
-  const int max_nacc = 256 / N < 4 ? 256 / N : 4;
+  // dual: two CTAs per SM, each with half of the shared memory (228 KB per SM, 1 KB reserved + ~6.5 KB static per CTA)
+  // and half of the tensor memory
+  const long long kSmemBudget = dual ? 104 * 1024 : pdac::kSmemBudget;
+  const int tmem_half = dual ? 128 : 256;
+  const int max_nacc = tmem_half / N < 4 ? tmem_half / N : 4;
   if (max_nacc < 1) return false;
   const long long w_bytes = (long long)n_taps * n_chunks * N * pitch;
   const int stg_wg = 128 * ((N < 64 ? N : 64) * 2 + 16);  // staging bytes per epilogue warpgroup
@@ -546,7 +649,7 @@ static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int
       const int a_buf = ((nacc * 128 + eh * PW + ew) * pitch + 1023) & ~1023;
       for (int res = 1; res >= 0; --res) {
         if (res && w_bytes > 112 * 1024) continue;
-        int sa = 0, sb = 0, n_wg = f_wg ? f_wg : 4;
+        int sa = 0, sb = 0, n_wg = dual ? 2 : (f_wg ? f_wg : 4);
         for (; n_wg >= 2; n_wg -= 2) {  // four epilogue warpgroups when their staging fits, else two
           const long long fixed = (long long)n_wg * stg_wg + 2048;
           if (res) {
@@ -636,7 +739,16 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   while (tap_s < tc->n_taps && tc->taps[tap_s].dh == tc->taps[0].dh) ++tap_s;
   if (tc->n_taps % tap_s) return PDAC_OK;
   HaloPlan pl = {0, 0, 0, 0, 0, 0, 0, 0.0};
-  if (!plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, &pl))
+  // Low channel counts (K chunk and N <= 32): two CTAs per SM, see kHaloThreadsDual. PDAC_HALO_DUAL=0 disables.
+  static int dual_ok = -1;
+  if (dual_ok < 0) {
+    const char* e = getenv("PDAC_HALO_DUAL");
+    dual_ok = (e && e[0] == '0') ? 0 : 1;
+  }
+  int dual = dual_ok && ck <= 32 && block_n <= 32;
+  if (dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1, &pl))
+    dual = 0;
+  if (!dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 0, &pl))
     return PDAC_OK;
 
   {
@@ -646,9 +758,9 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
       dbg = (e && e[0] == '1') ? 1 : 0;
     }
     if (dbg)
-      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d cost=%.0f\n",
+      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d dual=%d cost=%.0f\n",
               out->N, out->H, out->W, n_chunks, ck, block_n, tc->n_taps, pl.TW, pl.TH, pl.nacc, pl.sa, pl.sb,
-              pl.b_resident, pl.n_wg, pl.cost);
+              pl.b_resident, pl.n_wg, dual, pl.cost);
   }
   HaloMaps maps;
   HaloParams p;
@@ -663,6 +775,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   p.R = pl.TH + eh;
   p.nacc = pl.nacc;
   p.n_wg = pl.n_wg;
+  p.w_warp = dual ? 2 + 4 * pl.n_wg : 18;
   p.inv_pw = (uint32_t)(((1u << 20) + (uint32_t)p.PW - 1) / (uint32_t)p.PW);
   p.dh_min = dh_min;
   p.dw_min = dw_min;
@@ -732,24 +845,30 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   }
   const size_t b_bytes = (size_t)(p.b_resident ? p.n_taps * p.n_chunks : p.sb * p.tap_S) * p.b_sub;
   const size_t smem = (size_t)p.sa * p.a_buf + b_bytes + (size_t)p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16) + 1024;
-  PDAC_REQUIRE(smem <= 221 * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
-  int per_n = num_sms() / p.tiles_c;
+  PDAC_REQUIRE(smem <= (size_t)(dual ? 105 : 221) * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
+  int per_n = (dual ? 2 : 1) * num_sms() / p.tiles_c;
   if (per_n < 1) per_n = 1;
   if (per_n > p.tiles_sp) per_n = p.tiles_sp;
   typedef void (*HaloKernel)(const HaloMaps, const HaloParams);
-  static const HaloKernel table[4][3] = {
-      {conv_halo_kernel<1, 1>, conv_halo_kernel<1, 2>, conv_halo_kernel<1, 4>},
-      {conv_halo_kernel<2, 1>, conv_halo_kernel<2, 2>, conv_halo_kernel<2, 4>},
-      {conv_halo_kernel<3, 1>, conv_halo_kernel<3, 2>, conv_halo_kernel<3, 4>},
-      {conv_halo_kernel<4, 1>, conv_halo_kernel<4, 2>, conv_halo_kernel<4, 4>}};
-  static bool attr_set[4][3] = {};
-  const int ki = pl.nacc - 1, kj = ck == 16 ? 0 : (ck == 32 ? 1 : 2);
+  static const HaloKernel table[4][5] = {
+      {conv_halo_kernel<1, 1, 0>, conv_halo_kernel<1, 2, 0>, conv_halo_kernel<1, 4, 0>, conv_halo_kernel<1, 1, 1>,
+       conv_halo_kernel<1, 2, 1>},
+      {conv_halo_kernel<2, 1, 0>, conv_halo_kernel<2, 2, 0>, conv_halo_kernel<2, 4, 0>, conv_halo_kernel<2, 1, 1>,
+       conv_halo_kernel<2, 2, 1>},
+      {conv_halo_kernel<3, 1, 0>, conv_halo_kernel<3, 2, 0>, conv_halo_kernel<3, 4, 0>, conv_halo_kernel<3, 1, 1>,
+       conv_halo_kernel<3, 2, 1>},
+      {conv_halo_kernel<4, 1, 0>, conv_halo_kernel<4, 2, 0>, conv_halo_kernel<4, 4, 0>, conv_halo_kernel<4, 1, 1>,
+       conv_halo_kernel<4, 2, 1>}};
+  static bool attr_set[4][5] = {};
+  const int ki = pl.nacc - 1, kj = (ck == 16 ? 0 : (ck == 32 ? 1 : 2)) + (dual ? 3 : 0);
   HaloKernel kern = table[ki][kj];
   if (!attr_set[ki][kj]) {
-    PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(221 * 1024)));
+    PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((dual ? 105 : 221) * 1024)));
+    if (dual)
+      PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     attr_set[ki][kj] = true;
   }
-  kern<<<per_n * p.tiles_c, kHaloThreads, smem, (cudaStream_t)stream>>>(maps, p);
+  kern<<<per_n * p.tiles_c, dual ? kHaloThreadsDual : kHaloThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_halo_kernel");
   note_kernel(KID_CONV_HALO);
   *handled = 1;
@@ -757,3 +876,13 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
 }
 
 }  // namespace pdac
+
+#ifdef PDAC_HALO_PROF
+// Diagnostic build only (make prof): copies the 160 x 16 per-CTA cycle counters of the last conv_halo launch to the host.
+extern "C" int pdac_halo_dbg_set(int v) {
+  return cudaMemcpyToSymbol(pdac::g_halo_dbg, &v, sizeof(int)) == cudaSuccess ? 0 : -1;
+}
+extern "C" int pdac_halo_prof_read(long long* host) {
+  return cudaMemcpyFromSymbol(host, pdac::g_halo_prof, sizeof(long long) * 160 * 16) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -27,3 +27,17 @@ tot = sum(v[0] for v in agg.values())
 print(f"step {plain:.2f} ms untraced, {e0.elapsed_time(e1):.2f} ms traced; sum of C-ABI calls {tot:.2f} ms")
 for name, (ms, n) in sorted(agg.items(), key=lambda kv: -kv[1][0]):
     print(f"{name:36s} {n:4d} calls {ms:8.3f} ms  {100*ms/tot:5.1f}%")
+
+if len(sys.argv) > 2:  # per-shape rows of the named entry points: python scripts/call_table.py 64 pdac_bn_bwd_apply ...
+    for want in sys.argv[2:]:
+        rows = collections.OrderedDict()
+        for name, a, b, fl, nb, tag in tr:
+            if name == want:
+                g = rows.setdefault(tag, [0.0, 0]); g[0] += a.elapsed_time(b); g[1] += 1
+        print(f"-- {want}")
+        for tag, (ms, n) in sorted(rows.items(), key=lambda kv: -kv[1][0]):
+            try:
+                d = [int(x) for x in tag.split("x")]; el = d[0] * d[1] * d[2] * d[3]
+            except Exception:
+                el = 0
+            print(f"   {tag:22s} {n:3d} calls {ms:7.3f} ms  {ms/n*1e3:7.1f} us/call  {el*2/1e6/(ms/n) if ms else 0:7.1f} GB/s per 2-byte pass")
