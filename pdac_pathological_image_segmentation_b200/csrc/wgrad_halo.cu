@@ -56,8 +56,12 @@ struct WhParams {
   int* err;
 };
 
-__global__ void __launch_bounds__(kWhThreads, 1) wgrad_halo_kernel(const __grid_constant__ WhMaps maps,
-                                                                   const __grid_constant__ WhParams p) {
+// DUAL: two CTAs per SM (each <= 104 KB of shared memory and <= 256 TMEM columns). The single issuing thread spends a
+// few hundred cycles per halo stage on barrier waits, slab-table reads and commits, during which the tensor pipe idles
+// (the MMA queue is only a few instructions deep, scripts/probe/mma_issue.cu); a second resident CTA fills those gaps.
+template <int DUAL>
+__global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(const __grid_constant__ WhMaps maps,
+                                                                              const __grid_constant__ WhParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t fullA[kWhMaxStages];
   __shared__ __align__(8) uint64_t emptyA[kWhMaxStages];
@@ -346,7 +350,20 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
       p.cg_first[cg] = (uint8_t)s;
     }
   }
-  int spc_max = 512 / block_n;
+  static int dual_ok = -1;
+  if (dual_ok < 0) {
+    const char* e = getenv("PDAC_WGRAD_DUAL");
+    dual_ok = e ? atoi(e) : 1;
+  }
+  // two CTAs per SM when all slabs fit in half of the tensor memory (the 16- and 32-channel layers) or, for N <= 64,
+  // in two slab groups over grid.y (64 -> 64: 0.136 -> 0.119 ms; N = 128 loses, 32 -> 128: 0.343 -> 0.377 ms).
+  // PDAC_WGRAD_DUAL=2 (experiment): whenever the shared memory allows
+  int dual = dual_ok && (ns * block_n <= 256 || (block_n <= 64 && ns * block_n <= 512) || dual_ok == 2);
+  {
+    const int a_stage_ = p.a_buf * p.cps;
+    if (dual && (104 * 1024 - 2 * 128 * block_n * 2 - 1024) / a_stage_ < 3) dual = 0;
+  }
+  int spc_max = (dual ? 256 : 512) / block_n;
   if (spc_max > ns) spc_max = ns;
   const int ygroups = ceil_div(ns, spc_max);
   p.spc = ceil_div(ns, ygroups);
@@ -366,24 +383,30 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   p.err = device_err_flag();
   const int b_tile = 128 * block_n * 2;
   const int a_stage = p.a_buf * p.cps;
-  int stages_a = (220 * 1024 - 2 * b_tile - 1024) / a_stage;
+  int stages_a = ((dual ? 104 : 220) * 1024 - 2 * b_tile - 1024) / a_stage;
   if (stages_a > kWhMaxStages) stages_a = kWhMaxStages;
   if (stages_a < 2) return PDAC_OK;
   p.stages_a = stages_a;
   for (int s = 0; s < tc->n_cat; ++s) PDAC_TRY(encode_view_map(&maps.a[s], &views[s], ck, p.PW, p.R, 1));
   if (tc->n_cat == 1) maps.a[1] = maps.a[0];
   PDAC_TRY(encode_view_map(&maps.dy, dy, ckb, 16, 8, 1));
-  int splits = num_sms() / (ygroups * zgroups);
+  int splits = (dual ? 2 : 1) * num_sms() / (ygroups * zgroups);
   if (splits < 1) splits = 1;
   if (splits > p.n_kblocks) splits = p.n_kblocks;
   const size_t smem = (size_t)stages_a * a_stage + 2 * (size_t)b_tile + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    PDAC_CUDA(cudaFuncSetAttribute(wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(222 * 1024)));
+    PDAC_CUDA(cudaFuncSetAttribute(wgrad_halo_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(222 * 1024)));
+    PDAC_CUDA(cudaFuncSetAttribute(wgrad_halo_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(105 * 1024)));
+    PDAC_CUDA(cudaFuncSetAttribute(wgrad_halo_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                   cudaSharedmemCarveoutMaxShared));
     attr_set = true;
   }
   dim3 grid(splits, ygroups, zgroups);
-  wgrad_halo_kernel<<<grid, kWhThreads, smem, (cudaStream_t)stream>>>(maps, p);
+  if (dual)
+    wgrad_halo_kernel<1><<<grid, kWhThreads, smem, (cudaStream_t)stream>>>(maps, p);
+  else
+    wgrad_halo_kernel<0><<<grid, kWhThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_halo_kernel");
   note_kernel(KID_WGRAD_HALO);
   *handled = 1;
