@@ -24,13 +24,23 @@ static int flatten(const PdacView* v, Flat* f, const char* what) {
 struct EwGrid {
   int blocks, cg, ppb;
 };
-static EwGrid ew_grid(long long npix, int C) {
+// The grid is persistent: exactly the number of 256-thread blocks that are resident at once (occupancy query per
+// kernel), so every thread loads its per-channel constants once and there is a single wave (with 8 blocks per SM
+// requested and 2 resident, bn_bwd_apply ran four waves, each paying the constant loads and the DRAM latency chain:
+// 25 us for a 17 MB tensor).
+template <typename K>
+static int resident_blocks(K kernel) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  return per_sm * num_sms();
+}
+static EwGrid ew_grid(long long npix, int C, int resident) {
   EwGrid g;
   g.cg = C / 8;
   g.ppb = 256 / g.cg;
   if (g.ppb < 1) g.ppb = 1;
   long long need = (npix + g.ppb - 1) / g.ppb;
-  long long cap = (long long)num_sms() * 8;
+  long long cap = resident;
   g.blocks = (int)(need < cap ? need : cap);
   if (g.blocks < 1) g.blocks = 1;
   return g;
@@ -202,15 +212,19 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat
                                                            float* __restrict__ dbeta, int cg, int ppb) {
   EW_SETUP(cg, ppb)
   if (!active) return;
-  float a[8], m1[8], m2[8], mean[8], invstd[8], sc[8], sh[8];
+  // dx = a * (dz - m1 - (x - mean) * invstd * m2) = a * dz + k1 * (x - mean) + k0 (x - mean is formed first: folding the
+  // mean into k0 cancels catastrophically on the few-sample BatchNorms of the PSP pooling branches)
+  float a[8], k1[8], k0[8], mean[8], sc[8], sh[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = g * 8 + i;
+    const float invstd = mi[dy.C + c];
     mean[i] = mi[c];
-    invstd[i] = mi[dy.C + c];
-    a[i] = (gamma ? gamma[c] : 1.f) * invstd[i];
-    m1[i] = train ? sums[c] * inv_count : 0.f;
-    m2[i] = train ? sums[dy.C + c] * inv_count : 0.f;
+    a[i] = (gamma ? gamma[c] : 1.f) * invstd;
+    const float m1 = train ? sums[c] * inv_count : 0.f;
+    const float m2 = train ? sums[dy.C + c] * inv_count : 0.f;
+    k1[i] = -a[i] * invstd * m2;
+    k0[i] = -a[i] * m1;
     sc[i] = ss ? ss[c] : 0.f;
     sh[i] = ss ? ss[dy.C + c] : 0.f;
     if (blockIdx.x == 0 && pl == 0) {
@@ -253,7 +267,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat
       F8 o;
       if (train) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) o.v[i] = a[i] * (d.v[i] - m1[i] - (xx.v[i] - mean[i]) * invstd[i] * m2[i]);
+        for (int i = 0; i < 8; ++i) o.v[i] = fmaf(a[i], d.v[i], fmaf(k1[i], xx.v[i] - mean[i], k0[i]));
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) o.v[i] = a[i] * d.v[i];
@@ -325,7 +339,8 @@ extern "C" int pdac_scale_shift_act(const PdacView* x, const float* scale_shift,
                "scale_shift_act: shape mismatch");
   PDAC_REQUIRE(fx.C <= 2048, "scale_shift_act: too many channels");
   if (fx.npix == 0) return PDAC_OK;
-  const EwGrid g = ew_grid(fx.npix, fx.C);
+  static const int resident = resident_blocks(scale_shift_act_kernel);
+  const EwGrid g = ew_grid(fx.npix, fx.C, resident);
   scale_shift_act_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fx, scale_shift, fr, relu, fy, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("scale_shift_act");
   return PDAC_OK;
@@ -339,7 +354,8 @@ extern "C" int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const P
   if (x) PDAC_TRY(flatten(x, &fx, "x"));
   PDAC_REQUIRE(sums, "bn_bwd_reduce: null sums");
   PDAC_REQUIRE(fd.C <= 2048, "bn_bwd_reduce: too many channels");
-  const EwGrid g = ew_grid(fd.npix, fd.C);
+  static const int resident = resident_blocks(bn_bwd_reduce_kernel);
+  const EwGrid g = ew_grid(fd.npix, fd.C, resident);
   bn_bwd_reduce_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums, g.cg,
                                                                   g.ppb);
   PDAC_LAUNCH_CHECK("bn_bwd_reduce");
@@ -359,7 +375,8 @@ extern "C" int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const Pd
   PDAC_REQUIRE(mean_invstd && sums, "bn_bwd_apply: null stats");
   PDAC_REQUIRE(!train || x, "bn_bwd_apply: training mode needs the conv output x");
   PDAC_REQUIRE(!(scale_shift && !y) || x, "bn_bwd_apply: recomputing the ReLU mask needs the conv output x");
-  const EwGrid g = ew_grid(fd.npix, fd.C);
+  static const int resident = resident_blocks(bn_bwd_apply_kernel);
+  const EwGrid g = ew_grid(fd.npix, fd.C, resident);
   bn_bwd_apply_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, scale_shift, sums,
                                                                   (float)(1.0 / count), train, fdx, fdz, dgamma, dbeta,
                                                                   g.cg, g.ppb);
@@ -373,7 +390,8 @@ extern "C" int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const P
   PDAC_TRY(flatten(dy, &fd, "dy"));
   if (y) PDAC_TRY(flatten(y, &fy, "y"));
   if (dz) PDAC_TRY(flatten(dz, &fdz, "dz"));
-  const EwGrid g = ew_grid(fd.npix, fd.C);
+  static const int resident = resident_blocks(relu_bwd_bias_kernel);
+  const EwGrid g = ew_grid(fd.npix, fd.C, resident);
   relu_bwd_bias_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fdz, dbias, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("relu_bwd_bias");
   return PDAC_OK;
