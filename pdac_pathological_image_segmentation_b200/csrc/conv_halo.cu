@@ -219,19 +219,23 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
     // ------------------------------------------------------------------ halo producer
     if (lane == 0 && sp0 < sp_step) {
       const uint32_t halo_bytes = (uint32_t)(p.R * p.PW) * p.pitch;
-      int ita = 0;
+      int stage = 0;
+      uint32_t phase = 0;  // ring position and its wrap parity, carried incrementally (no divisions in the loops)
       Walk wk;
       walk_init(wk);
       PROF_DECL(w_ea);
       for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, walk_next(wk)) {
         const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
-        for (int c = 0; c < p.n_chunks; ++c, ++ita) {
-          const int stage = ita % p.sa;
-          PROF_WAIT(w_ea, mbar_wait(&empty_a[stage], ((ita / p.sa) & 1) ^ 1, p.err));
+        for (int c = 0; c < p.n_chunks; ++c) {
+          PROF_WAIT(w_ea, mbar_wait(&empty_a[stage], phase ^ 1, p.err));
           mbar_expect_tx(&full_a[stage], halo_bytes);
           const int s = c >= p.chunks0;
           tma_load_4d(smem_a + (size_t)stage * p.a_buf, &maps.a[s], &full_a[stage], (s ? c - p.chunks0 : c) * p.ck,
                       w0 + p.dw_min, h0 + p.dh_min, img);
+          if (++stage == p.sa) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
       }
       PROF_PUT(7, w_ea);
@@ -246,17 +250,21 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
             tma_load_2d(smem_b + (size_t)(t * p.n_chunks + c) * p.b_sub, &maps.w, &full_b[0], c * p.ck,
                         t * p.wrows + n0);
       } else {
-        int itb = 0;
+        int stage = 0;
+        uint32_t phase = 0;
         PROF_DECL(w_eb);
         for (int sp = sp0; sp < p.tiles_sp; sp += sp_step) {
           for (int c = 0; c < p.n_chunks; ++c) {
-            for (int r = 0; r < p.tap_R; ++r, ++itb) {  // one stage = the tap_S taps of a kernel row
-              const int stage = itb % p.sb;
-              PROF_WAIT(w_eb, mbar_wait(&empty_b[stage], ((itb / p.sb) & 1) ^ 1, p.err));
+            for (int r = 0; r < p.tap_R; ++r) {  // one stage = the tap_S taps of a kernel row
+              PROF_WAIT(w_eb, mbar_wait(&empty_b[stage], phase ^ 1, p.err));
               mbar_expect_tx(&full_b[stage], (uint32_t)(p.tap_S * p.b_sub));
               for (int s = 0; s < p.tap_S; ++s)
                 tma_load_2d(smem_b + (size_t)(stage * p.tap_S + s) * p.b_sub, &maps.w, &full_b[stage], c * p.ck,
                             (r * p.tap_S + s) * p.wrows + n0);
+              if (++stage == p.sb) {
+                stage = 0;
+                phase ^= 1;
+              }
             }
           }
         }
@@ -293,7 +301,8 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
       const uint32_t step_r = (uint32_t)(p.tap_step_r * (int)pix16), step_s = (uint32_t)(p.tap_step_s * (int)pix16);
       const int TR = p.tap_R, TS = p.tap_S, n_chunks = p.n_chunks, sa = p.sa, sb = p.sb;
       const uint32_t b_tap16 = (uint32_t)n_chunks * b_sub16;
-      int ita = 0, itb = 0, lt = 0;
+      int stage = 0, bstage = 0, lt = 0;
+      uint32_t phase = 0, bphase = 0;
       PROF_DECL(w_te);
       PROF_DECL(w_fa);
       PROF_DECL(w_fb);
@@ -310,9 +319,8 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
         PROF_WAIT(w_te, mbar_wait(&tmem_empty_bar[g], ((lt >> 1) & 1) ^ 1, p.err));
         PROF_WAIT(w_fn, tc_fence_after());
         const uint32_t tacc = tmem_base + (uint32_t)(g * NACC) * acc_step;
-        for (int c = 0; c < n_chunks; ++c, ++ita) {
-          const int stage = ita % sa;
-          PROF_WAIT(w_fa, mbar_wait(&full_a[stage], (ita / sa) & 1, p.err));
+        for (int c = 0; c < n_chunks; ++c) {
+          PROF_WAIT(w_fa, mbar_wait(&full_a[stage], phase, p.err));
           PROF_WAIT(w_fn, tc_fence_after());
           const uint32_t a_stage = a_lo0 + (uint32_t)stage * a_buf16 + tap0;
           if (p.b_resident) {
@@ -340,9 +348,8 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
             // the re-divergence around the issue (~150 cycles) are paid once per TS * NACC * KS MMAs
             uint32_t acc = c ? 1u : 0u;
             uint32_t a_row = a_stage;
-            for (int r = 0; r < TR; ++r, a_row += step_r, ++itb) {
-              const int bstage = itb % sb;
-              PROF_WAIT(w_fb, mbar_wait(&full_b[bstage], (itb / sb) & 1, p.err));
+            for (int r = 0; r < TR; ++r, a_row += step_r) {
+              PROF_WAIT(w_fb, mbar_wait(&full_b[bstage], bphase, p.err));
               PROF_WAIT(w_fn, tc_fence_after());
               if (leader) {
                 uint32_t a_lo = a_row;
@@ -354,8 +361,16 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                 PROF_WAIT(w_cm, umma_commit(&empty_b[bstage]));
               }
               acc = 1u;
+              if (++bstage == sb) {
+                bstage = 0;
+                bphase ^= 1;
+              }
             }
             PROF_WAIT(w_cm, if (leader) umma_commit(&empty_a[stage]));
+          }
+          if (++stage == sa) {
+            stage = 0;
+            phase ^= 1;
           }
         }
         PROF_WAIT(w_cm, if (leader) umma_commit(&tmem_full_bar[g]));

@@ -830,17 +830,26 @@ static int build_fwd_taps(const PdacConv* cv, int n_src, const PdacView* src, Pd
   return PDAC_OK;
 }
 
+// out view = add view (or zeros), V channels per thread (V = 8: one 16-byte access; V = 1: any alignment)
+template <int V>
 __global__ void fill_view_kernel(bf16* out, long long sN, long long sH, long long sW, int N, int H, int W, int C,
                                  const bf16* add, long long aN, long long aH, long long aW) {
-  const long long total = (long long)N * H * W * C;
+  const int cv = C / V;
+  const long long total = (long long)N * H * W * cv;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    long long r = i / C;
+    const int c = (int)(i % cv) * V;
+    long long r = i / cv;
     const int w = (int)(r % W);
     r /= W;
     const int h = (int)(r % H);
     const int n = (int)(r / H);
-    out[n * sN + h * sH + w * sW + c] = add ? add[n * aN + h * aH + w * aW + c] : __float2bfloat16(0.f);
+    bf16* o = out + n * sN + h * sH + w * sW + c;
+    if (V == 8) {
+      *reinterpret_cast<uint4*>(o) =
+          add ? __ldg(reinterpret_cast<const uint4*>(add + n * aN + h * aH + w * aW + c)) : make_uint4(0, 0, 0, 0);
+    } else {
+      *o = add ? add[n * aN + h * aH + w * aW + c] : __float2bfloat16(0.f);
+    }
   }
 }
 
@@ -941,12 +950,23 @@ extern "C" int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const v
       if (addend) adp = parity_view(*addend, ph, pw);
       if (dxp.H <= 0 || dxp.W <= 0) continue;
       if (tc.n_taps == 0) {
-        const long long total = (long long)dxp.N * dxp.H * dxp.W * dxp.C;
+        // no tap lands on this parity class (1x1 stride 2): dx = addend there, i.e. nothing to do when the gradient
+        // is accumulated in place, else a copy / zero fill
+        if (addend && adp.ptr == dxp.ptr && adp.sN == dxp.sN && adp.sH == dxp.sH && adp.sW == dxp.sW) continue;
+        const bool v8 = dxp.C % 8 == 0 && ((uintptr_t)dxp.ptr & 15) == 0 && dxp.sW % 8 == 0 && dxp.sH % 8 == 0 &&
+                        dxp.sN % 8 == 0 &&
+                        (!addend || (((uintptr_t)adp.ptr & 15) == 0 && adp.sW % 8 == 0 && adp.sH % 8 == 0 && adp.sN % 8 == 0));
+        const long long total = (long long)dxp.N * dxp.H * dxp.W * (v8 ? dxp.C / 8 : dxp.C);
         int blocks = (int)((total + 255) / 256);
         if (blocks > 148 * 8) blocks = 148 * 8;
-        fill_view_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-            (bf16*)dxp.ptr, dxp.sN, dxp.sH, dxp.sW, dxp.N, dxp.H, dxp.W, dxp.C, addend ? (const bf16*)adp.ptr : nullptr,
-            addend ? adp.sN : 0, addend ? adp.sH : 0, addend ? adp.sW : 0);
+        if (v8)
+          fill_view_kernel<8><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+              (bf16*)dxp.ptr, dxp.sN, dxp.sH, dxp.sW, dxp.N, dxp.H, dxp.W, dxp.C,
+              addend ? (const bf16*)adp.ptr : nullptr, addend ? adp.sN : 0, addend ? adp.sH : 0, addend ? adp.sW : 0);
+        else
+          fill_view_kernel<1><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+              (bf16*)dxp.ptr, dxp.sN, dxp.sH, dxp.sW, dxp.N, dxp.H, dxp.W, dxp.C,
+              addend ? (const bf16*)adp.ptr : nullptr, addend ? adp.sN : 0, addend ? adp.sH : 0, addend ? adp.sW : 0);
         PDAC_LAUNCH_CHECK("fill_view_kernel");
         continue;
       }

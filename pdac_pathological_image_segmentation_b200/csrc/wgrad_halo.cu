@@ -112,7 +112,8 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
   if (warp == 0) {
     if (lane == 0) {
       const uint32_t halo_bytes = (uint32_t)(p.R * p.PW) * p.pitch_a;
-      int ita = 0;
+      int stage = 0;
+      uint32_t phase = 0;  // A ring position and wrap parity, carried incrementally
       for (int i = 0; i < n_my_kb; ++i) {
         int kb = blockIdx.x + i * gridDim.x;
         const int tile_w = kb % p.tiles_w;
@@ -125,9 +126,8 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
         mbar_expect_tx(&fullB[bs], (uint32_t)b_tile);
         for (int j = 0; j < p.nboxb; ++j)
           tma_load_4d(smem_b + (size_t)bs * b_tile + (size_t)j * b_box, &maps.dy, &fullB[bs], n0 + j * p.ckb, w0, h0, img);
-        for (int cg = cg_lo; cg <= cg_hi; ++cg, ++ita) {
-          const int stage = ita % p.stages_a;
-          mbar_wait(&emptyA[stage], ((ita / p.stages_a) & 1) ^ 1, p.err);
+        for (int cg = cg_lo; cg <= cg_hi; ++cg) {
+          mbar_wait(&emptyA[stage], phase ^ 1, p.err);
           const int c_first = cg * p.cps;
           const int nc = min(p.cps, p.n_chunks - c_first);
           mbar_expect_tx(&fullA[stage], halo_bytes * (uint32_t)nc);
@@ -136,6 +136,10 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
             const int s = c >= p.chunks0;
             tma_load_4d(smem + (size_t)stage * a_stage + (size_t)j * p.a_buf, &maps.a[s], &fullA[stage],
                         (s ? c - p.chunks0 : c) * p.ck, w0 + p.dw_min, h0 + p.dh_min, img);
+          }
+          if (++stage == p.stages_a) {
+            stage = 0;
+            phase ^= 1;
           }
         }
       }
@@ -151,15 +155,15 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
     const uint32_t a_stage16 = (uint32_t)a_stage >> 4, b_tile16 = (uint32_t)b_tile >> 4;
     const uint32_t block_n = (uint32_t)p.block_n;
     const int stages_a = p.stages_a;
-    int ita = 0;
+    int stage = 0;
+    uint32_t phase = 0;
     for (int i = 0; i < n_my_kb; ++i) {
       const int bs = i & 1;
       mbar_wait(&fullB[bs], (i >> 1) & 1, p.err);
       tc_fence_after();
       const uint32_t b_lo = b_lo0 + (uint32_t)bs * b_tile16;
-      for (int cg = cg_lo; cg <= cg_hi; ++cg, ++ita) {
-        const int stage = ita % stages_a;
-        mbar_wait(&fullA[stage], (ita / stages_a) & 1, p.err);
+      for (int cg = cg_lo; cg <= cg_hi; ++cg) {
+        mbar_wait(&fullA[stage], phase, p.err);
         tc_fence_after();
         if (leader) {  // one divergent region per halo stage: all of its slabs back to back
           const uint32_t st_lo = a_lo0 + (uint32_t)stage * a_stage16;
@@ -172,6 +176,10 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
             for (int k = 1; k < 8; ++k) umma_bf16_lohi(td, a_lo + k * ka16, hi_a, b_lo + k * kb16, hi_b, idesc, 1u);
           }
           umma_commit(&emptyA[stage]);
+        }
+        if (++stage == stages_a) {
+          stage = 0;
+          phase ^= 1;
         }
       }
       if (leader) umma_commit(&emptyB[bs]);
