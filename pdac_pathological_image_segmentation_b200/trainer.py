@@ -14,8 +14,12 @@ from .engine import GradArena, Tape
 
 
 class TrainStep:
-    def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, process_group=None, bucket_mb=25.0):
+    def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, process_group=None, bucket_mb=25.0, graph=False):
+        """graph=True: after two eager steps per input shape, forward + loss + backward (about 260 kernel launches) are
+        captured once into a CUDA graph and replayed; the gradient allreduce and Adam stay outside the graph."""
         self.model = model
+        self.use_graph = bool(graph)
+        self._g_key = None
         self.params = model._trainable()
         dev = self.params[0].device
         if dev.type != "cuda":
@@ -69,7 +73,39 @@ class TrainStep:
         self.model._packs.invalidate()
 
     def step(self, img_u8, mask_u8, aug=None):
-        loss, score = self.forward_backward(img_u8, mask_u8, aug)
+        if self.use_graph:
+            loss, score = self._graph_forward_backward(img_u8, mask_u8, aug)
+        else:
+            loss, score = self.forward_backward(img_u8, mask_u8, aug)
         self._allreduce()
         self.optimizer_step()
         return loss, score
+
+    def _graph_forward_backward(self, img_u8, mask_u8, aug):
+        """forward_backward through a captured CUDA graph: inputs are copied into static buffers, every kernel argument
+        (tensor maps, arena slots, the allocator's activation addresses) is baked at capture time. BatchNorm's
+        num_batches_tracked and running statistics advance on the device, so replays keep the module state exact."""
+        from . import _lib
+        key = (tuple(img_u8.shape), tuple(mask_u8.shape), None if aug is None else tuple(aug.shape), self.model.training)
+        if key != self._g_key:
+            self._g_key, self._g, self._g_warm = key, None, 0
+            self._g_img, self._g_mask = torch.empty_like(img_u8), torch.empty_like(mask_u8)
+            self._g_aug = None if aug is None else torch.empty_like(aug)
+        self._g_img.copy_(img_u8, non_blocking=True)
+        self._g_mask.copy_(mask_u8, non_blocking=True)
+        if aug is not None:
+            self._g_aug.copy_(aug, non_blocking=True)
+        if self._g is None:
+            if self._g_warm < 2:   # eager: lazy one-time host initialisation inside the library, allocator warm-up
+                self._g_warm += 1
+                return self.forward_backward(self._g_img, self._g_mask, self._g_aug)
+            l0 = _lib.launches
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._g_out = self.forward_backward(self._g_img, self._g_mask, self._g_aug)
+            self._g_launches = _lib.launches - l0
+            _lib.launches = l0
+            self._g = g
+        self._g.replay()
+        _lib.launches += self._g_launches
+        return self._g_out[0].clone(), self._g_out[1].clone()
