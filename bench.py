@@ -270,6 +270,7 @@ def run_ours(args):
         sync_all()
         ms = e0.elapsed_time(e1)
         launches = _lib.launches - l0
+        use_graph = ts._g is not None      # steps with active Dropout draw host seeds and stay eager
     clocks = sampler.stop() if rank == 0 else None
     t = torch.tensor([ms], device=dev)
     if world > 1:

@@ -112,6 +112,7 @@ class Tape:
         self.steps = []
         self.grads = {}
         self.nograd = set()
+        self.host_rng = False
 
     def record(self, fn):
         if self.enabled:
@@ -360,6 +361,7 @@ def dropout(tape: Tape, x, p, per_channel):
     if not tape.training or p <= 0.0:
         return x
     seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+    tape.host_rng = True   # a per-step host value is baked into the launch: such a step must not be replayed from a graph
     y = ops.dropout(x, p, seed, per_channel)
 
     def bwd():

@@ -20,6 +20,7 @@ class TrainStep:
         self.model = model
         self.use_graph = bool(graph)
         self._g_key = None
+        self._host_rng = False
         self.params = model._trainable()
         dev = self.params[0].device
         if dev.type != "cuda":
@@ -56,6 +57,7 @@ class TrainStep:
         z, mask = ops.stem_prep_u8(img_u8, mask_u8, aug)
         tape = Tape(model._packs, model.training, self.arena)
         logits, feed = model._run(tape, z)
+        self._host_rng = bool(getattr(tape, "host_rng", False))
         if logits.shape[1] != 1:
             raise RuntimeError("TrainStep implements the reference's 1-class sigmoid/Dice step (train_worker.py:150-182)")
         score, _ = ops.dice_score(logits, mask, pred_is_logits=True)
@@ -96,7 +98,9 @@ class TrainStep:
         if aug is not None:
             self._g_aug.copy_(aug, non_blocking=True)
         if self._g is None:
-            if self._g_warm < 2:   # eager: lazy one-time host initialisation inside the library, allocator warm-up
+            if self._g_warm < 2 or self._host_rng:
+                # eager: lazy one-time host initialisation inside the library, allocator warm-up; and for good when the
+                # step draws host random numbers (active Dropout: the seed is a launch argument)
                 self._g_warm += 1
                 return self.forward_backward(self._g_img, self._g_mask, self._g_aug)
             l0 = _lib.launches

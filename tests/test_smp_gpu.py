@@ -243,26 +243,28 @@ def test_trainstep_gradients_equal_autograd_path_eval_mode():
 
 
 def test_trainstep_cuda_graph_replays_the_eager_step():
-    """TrainStep(graph=True) replays forward + loss + backward from a CUDA graph; in eval mode (no atomics in the
-    forward) its losses, gradients and parameters follow the eager harness step for step."""
-    import copy
-
+    """TrainStep(graph=True) replays forward + loss + backward from a CUDA graph. In eval mode (no atomics in the
+    forward) the replay and an eager forward_backward of the SAME harness on the same batch give the same loss, score
+    and gradient arena, step after step, with Adam updates (and weight re-packs) in between."""
     from pdac_pathological_image_segmentation_b200.smp import Unet
     from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
     from pdac_pathological_image_segmentation_b200.trainer import TrainStep
     torch.manual_seed(11)
-    m1 = Unet(encoder_weights=None).to(DEV).eval()
-    m2 = copy.deepcopy(m1)
-    t1, t2 = TrainStep(m1, lr=1e-3), TrainStep(m2, lr=1e-3, graph=True)
-    batches = [synthetic_batch(2, 128, seed=20 + i) for i in range(3)]
-    for it in range(6):                         # steps 0-1 eager warm-up, step 2 captures, 3-5 replay
-        img, mask = (x.to(DEV) for x in batches[it % 3])
-        l1, s1 = t1.step(img, mask)
-        l2, s2 = t2.step(img, mask)
-        assert abs(l1.item() - l2.item()) <= 1e-5, (it, l1.item(), l2.item())
-        assert abs(s1.item() - s2.item()) <= 1e-5
-        g1, g2 = t1.arena.flat.double(), t2.arena.flat.double()
-        assert ((g1 - g2).norm() / (g1.norm() + 1e-30)).item() <= 1e-3, it
-    assert t2._g is not None
-    frac = ((t1.flat_params - t2.flat_params).abs() > 2e-4).float().mean().item()
-    assert frac <= 0.02, frac
+    m = Unet(encoder_weights=None).to(DEV).eval()
+    ts = TrainStep(m, lr=1e-5, graph=True)
+    batches = [tuple(x.to(DEV) for x in synthetic_batch(2, 128, seed=20 + i)) for i in range(3)]
+    for it in range(6):                         # steps 0-1 eager warm-up, step 2 captures + replays, 3-5 replay
+        img, mask = batches[it % 3]
+        l2, s2 = ts._graph_forward_backward(img, mask, None)
+        g2 = ts.arena.flat.double().clone()
+        l1, s1 = ts.forward_backward(img, mask)
+        g1 = ts.arena.flat.double()
+        assert g1.norm().item() > 1e-3          # the comparison below is about real gradients
+        assert abs(l1.item() - l2.item()) <= 1e-6 and abs(s1.item() - s2.item()) <= 1e-6, (it, l1.item(), l2.item())
+        assert ((g1 - g2).norm() / g1.norm()).item() <= 1e-3, it
+        ts.optimizer_step()
+    assert ts._g is not None
+    # and through the public call
+    before = ts.flat_params.clone()
+    loss, _ = ts.step(*batches[0])
+    assert torch.isfinite(loss) and (ts.flat_params - before).abs().max().item() > 0
