@@ -284,11 +284,27 @@ __global__ void __launch_bounds__(256) dw3x3_kernel(ImgView x, int H, int W, con
   }
 }
 
+// Block-level reduction of the per-thread 9 x 8 partial weight gradients in (dynamic) shared memory, then one global
+// atomic per (channel, tap) and block: the pixel lanes of a block share their channels, and 72 global atomics per
+// THREAD (5 M per call on 2.7 k addresses) were what the 304-channel layer's 3.3 ms consisted of.
+__device__ __forceinline__ void dw_flush(float (&acc)[9][8], bool active, int g, int cg, float* __restrict__ dw) {
+  extern __shared__ float s_dw[];  // [cg * 8 channels][9 taps]
+  for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) s_dw[i] = 0.f;
+  __syncthreads();
+  if (active) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(&s_dw[(g * 8 + i) * 9 + t], acc[t][i]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) atomicAdd(dw + i, s_dw[i]);
+}
+
 // dw[c][r*3+s] += sum_{n,h,w} dy[n,h,w,c] * x[n, h+(r-1)*dil, w+(s-1)*dil, c]
 __global__ void __launch_bounds__(256) dw3x3_wgrad_kernel(ImgView x, ImgView dy, int H, int W, int dil,
                                                           float* __restrict__ dw, int cg, int ppb) {
   IMG_SETUP(cg, ppb)
-  if (!active) return;
   float acc[9][8];
 #pragma unroll
   for (int t = 0; t < 9; ++t)
@@ -296,7 +312,7 @@ __global__ void __launch_bounds__(256) dw3x3_wgrad_kernel(ImgView x, ImgView dy,
     for (int i = 0; i < 8; ++i) acc[t][i] = 0.f;
   const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
   const bf16* db = dy.ptr + (long long)n * dy.sN + g * 8;
-  for (int p = pfirst; p < x.npix; p += pstep) {
+  for (int p = pfirst; active && p < x.npix; p += pstep) {
     const int h = p / W, w = p - h * W;
     const F8 d = unpack8(ld16(db + (long long)p * dy.ps));
 #pragma unroll
@@ -313,10 +329,125 @@ __global__ void __launch_bounds__(256) dw3x3_wgrad_kernel(ImgView x, ImgView dy,
       }
     }
   }
+  dw_flush(acc, active, g, cg, dw);
+}
+
+// dilation 1 (DeepLabV3+ decoder: 304 channels at 128x128, the expensive one): a thread owns one image row and slides a
+// 3x3 window of packed columns along it, so a pixel costs 3 new 16-byte loads instead of 9; the pixel lanes of a block
+// are consecutive rows, whose halo rows hit L1.
+__global__ void __launch_bounds__(256, 2) dw3x3_d1_kernel(ImgView x, int H, int W, const float* __restrict__ wgt, int flip,
+                                                          ImgView y, int cg, int ppb) {
+  const int g = threadIdx.x % cg, pl = threadIdx.x / cg;
+  const int n = blockIdx.y, h = blockIdx.x * ppb + pl;
+  if (pl >= ppb || h >= H) return;
+  // weights as packed bf16 pairs (36 registers instead of 72: room for two pixels per iteration at 2 blocks / SM);
+  // the tensor-core convolutions round their weights to bf16 as well
+  uint32_t wp[9][4];
 #pragma unroll
   for (int t = 0; t < 9; ++t)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) atomicAdd(dw + (long long)(g * 8 + i) * 9 + t, acc[t][i]);
+    for (int i = 0; i < 4; ++i) {
+      const float* wr = wgt + (long long)(g * 8 + 2 * i) * 9 + (flip ? 8 - t : t);
+      const __nv_bfloat162 hh = __floats2bfloat162_rn(wr[0], wr[9]);
+      wp[t][i] = *reinterpret_cast<const uint32_t*>(&hh);
+    }
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  bf16* yb = y.ptr + (long long)n * y.sN + g * 8;
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  bool rok[3];
+  const bf16* rp[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const int hh = h + r - 1;
+    rok[r] = hh >= 0 && hh < H;
+    rp[r] = xb + (long long)((rok[r] ? hh : h) * W) * x.ps;
+  }
+  uint4 c0[3], c1[3], c2[3], c3[3];  // columns w-1, w, w+1, w+2 of rows h-1, h, h+1
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    c0[r] = zero;
+    c1[r] = rok[r] ? ld16(rp[r]) : zero;
+  }
+  auto tap = [&](F8& acc, const uint4& v, int t) {
+    const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc.v[2 * i] = fmaf(__uint_as_float(u[i] << 16), __uint_as_float(wp[t][i] << 16), acc.v[2 * i]);
+      acc.v[2 * i + 1] =
+          fmaf(__uint_as_float(u[i] & 0xffff0000u), __uint_as_float(wp[t][i] & 0xffff0000u), acc.v[2 * i + 1]);
+    }
+  };
+  for (int w = 0; w < W; w += 2) {  // W is even (checked by the launcher)
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      c2[r] = rok[r] ? ld16(rp[r] + (long long)(w + 1) * x.ps) : zero;
+      c3[r] = (rok[r] && w + 2 < W) ? ld16(rp[r] + (long long)(w + 2) * x.ps) : zero;
+    }
+    F8 a0, a1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a0.v[i] = a1.v[i] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      tap(a0, c0[r], r * 3);
+      tap(a0, c1[r], r * 3 + 1);
+      tap(a0, c2[r], r * 3 + 2);
+      tap(a1, c1[r], r * 3);
+      tap(a1, c2[r], r * 3 + 1);
+      tap(a1, c3[r], r * 3 + 2);
+    }
+    st16(yb + (long long)(h * W + w) * y.ps, pack8(a0));
+    st16(yb + (long long)(h * W + w + 1) * y.ps, pack8(a1));
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      c0[r] = c2[r];
+      c1[r] = c3[r];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) dw3x3_d1_wgrad_kernel(ImgView x, ImgView dy, int H, int W,
+                                                             float* __restrict__ dw, int cg, int ppb) {
+  const int g = threadIdx.x % cg, pl = threadIdx.x / cg;
+  const int n = blockIdx.y;
+  const bool lane_ok = pl < ppb;
+  float acc[9][8];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[t][i] = 0.f;
+  const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
+  const bf16* db = dy.ptr + (long long)n * dy.sN + g * 8;
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+  for (int h = blockIdx.x * ppb + pl; lane_ok && h < H; h += gridDim.x * ppb) {
+    uint4 c0[3], c1[3], c2[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hh = h + r - 1;
+      c0[r] = zero;
+      c1[r] = (hh >= 0 && hh < H) ? ld16(xb + (long long)(hh * W) * x.ps) : zero;
+    }
+    for (int w = 0; w < W; ++w) {
+      const F8 d = unpack8(ld16_stream(db + (long long)(h * W + w) * dy.ps));
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int hh = h + r - 1;
+        c2[r] = (hh >= 0 && hh < H && w + 1 < W) ? ld16(xb + (long long)(hh * W + w + 1) * x.ps) : zero;
+      }
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const F8 a0 = unpack8(c0[r]), a1 = unpack8(c1[r]), a2 = unpack8(c2[r]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          acc[r * 3][i] = fmaf(a0.v[i], d.v[i], acc[r * 3][i]);
+          acc[r * 3 + 1][i] = fmaf(a1.v[i], d.v[i], acc[r * 3 + 1][i]);
+          acc[r * 3 + 2][i] = fmaf(a2.v[i], d.v[i], acc[r * 3 + 2][i]);
+        }
+        c0[r] = c1[r];
+        c1[r] = c2[r];
+      }
+    }
+  }
+  dw_flush(acc, lane_ok, g, cg, dw);
 }
 
 }  // namespace pdac
@@ -407,6 +538,12 @@ extern "C" int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int fl
   PDAC_TRY(img_view(y, &yv, "dwconv y"));
   PDAC_REQUIRE(x->H == y->H && x->W == y->W && x->C == y->C && x->N == y->N && dil >= 1, "dwconv: shape mismatch");
   const ImgGrid g = img_grid(xv.npix, x->C, x->N);
+  if (dil == 1 && x->W >= 16 && x->W % 2 == 0) {
+    dw3x3_d1_kernel<<<dim3(ceil_div(x->H, g.ppb), x->N), 256, 0, (cudaStream_t)stream>>>(xv, x->H, x->W, w, flip, yv,
+                                                                                         g.cg, g.ppb);
+    PDAC_LAUNCH_CHECK("dw3x3_d1_kernel");
+    return PDAC_OK;
+  }
   dw3x3_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, x->H, x->W, w, dil, flip, yv, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("dw3x3_kernel");
   return PDAC_OK;
@@ -422,7 +559,17 @@ extern "C" int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int d
   int cap = (num_sms() * 2 + x->N - 1) / x->N;
   if (cap < 1) cap = 1;
   if ((int)g.grid.x > cap) g.grid.x = cap;
-  dw3x3_wgrad_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dil, dw, g.cg, g.ppb);
+  const size_t smem = (size_t)g.cg * 72 * sizeof(float);
+  PDAC_REQUIRE(smem <= 48 * 1024, "dwconv wgrad: too many channels (%d)", x->C);
+  if (dil == 1 && x->W >= 16) {
+    int bands = ceil_div(x->H, g.ppb);
+    int per_img = (num_sms() * 4 + x->N - 1) / x->N;  // ~4 blocks per SM in total, each walking whole rows
+    if (per_img > bands) per_img = bands;
+    dw3x3_d1_wgrad_kernel<<<dim3(per_img, x->N), 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dw, g.cg, g.ppb);
+    PDAC_LAUNCH_CHECK("dw3x3_d1_wgrad_kernel");
+    return PDAC_OK;
+  }
+  dw3x3_wgrad_kernel<<<g.grid, 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dil, dw, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("dw3x3_wgrad_kernel");
   return PDAC_OK;
 }

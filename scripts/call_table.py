@@ -8,7 +8,13 @@ from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
 from pdac_pathological_image_segmentation_b200.trainer import TrainStep
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 torch.manual_seed(41)
-m = Unet(encoder_weights=None).cuda().train()
+_mk = os.environ.get("MODEL", "unet")       # MODEL=fpn|pspnet|deeplabv3+ for the other smp networks
+if _mk == "unet":
+    m = Unet(encoder_weights=None).cuda().train()
+else:
+    from pdac_pathological_image_segmentation_b200 import smp as _P
+    _cls = {"fpn": _P.FPN, "pspnet": _P.PSPNet, "deeplabv3+": _P.DeepLabV3Plus}[_mk]
+    m = _cls(encoder_weights=None).cuda().train()
 ts = TrainStep(m)
 img, mask = synthetic_batch(B, 512, seed=41)
 img, mask = img.cuda(), mask.cuda()
