@@ -276,6 +276,58 @@ __global__ void __launch_bounds__(256) bilinear_bwd_kernel(V4 dy, V4 dx, Lin lh,
   }
 }
 
+// Sum of the pixel lanes' partial 8-channel vectors of a block (thread = (pixel lane, channel group g), cg groups):
+// returns true on the lane-0 threads, whose acc[] then holds the block total.
+__device__ __forceinline__ bool lanes_reduce(float (&acc)[8], int cg) {
+  __shared__ float red[256][9];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[threadIdx.x][i] = acc[i];
+  __syncthreads();
+  const int lanes = blockDim.x / cg;
+  if ((int)threadIdx.x >= cg) return false;
+  for (int q = 1; q < lanes; ++q)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += red[q * cg + threadIdx.x][i];
+  return true;
+}
+
+// Small dx (PSPNet's 1x1 .. 6x6 pooling bins upsampled to 64x64): one thread per dx element would gather thousands of
+// dy pixels serially from a few thousand threads (1.7 ms per call); here one block owns a dx pixel and its pixel lanes
+// split the contributing dy window.
+__global__ void __launch_bounds__(256) bilinear_bwd_coop_kernel(V4 dy, V4 dx, Lin lh, Lin lw) {
+  const int cg = dx.C / 8;
+  const int g = threadIdx.x % cg, pl = threadIdx.x / cg, lanes = blockDim.x / cg;
+  int r = blockIdx.x;
+  const int w = r % dx.W;
+  r /= dx.W;
+  const int h = r % dx.H, n = r / dx.H;
+  int ohl, ohh, owl, owh;
+  out_range(lh, h, dy.H, ohl, ohh);
+  out_range(lw, w, dy.W, owl, owh);
+  const int ww_n = owh - owl + 1, cnt = (ohh - ohl + 1) * ww_n;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int k = pl; k < cnt && pl < lanes; k += lanes) {
+    const int oh = ohl + k / ww_n, ow = owl + k % ww_n;
+    int h0, h1, w0, w1;
+    float a, b;
+    lh.src(oh, h0, h1, a);
+    lw.src(ow, w0, w1, b);
+    const float kk = ((h0 == h ? 1.f - a : 0.f) + (h1 == h ? a : 0.f)) * ((w0 == w ? 1.f - b : 0.f) + (w1 == w ? b : 0.f));
+    if (kk == 0.f) continue;
+    const F8 d = unpack8(ld16(dy.at(n, oh, ow) + g * 8));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = fmaf(kk, d.v[i], acc[i]);
+  }
+  if (lanes_reduce(acc, cg)) {
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+    st16(dx.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+
 // head variants: NHWC bf16 (first Cu channels of a padded buffer) -> NCHW fp32 logits, and the gradient back
 __global__ void __launch_bounds__(256) bilinear_head_fwd_kernel(V4 x, int Cu, float* __restrict__ out, int Ho, int Wo,
                                                                 Lin lh, Lin lw) {
@@ -352,6 +404,32 @@ __global__ void __launch_bounds__(256) adaptive_avgpool_fwd_kernel(V4 x, V4 y) {
         for (int i = 0; i < 8; ++i) acc[i] += v.v[i];
       }
     const float inv = 1.f / (float)((h1 - h0) * (w1 - w0));
+    F8 o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i] * inv;
+    st16(y.at(n, h, w) + g * 8, pack8(o));
+  }
+}
+// large bins (PSPNet: 64x64 -> 1x1 .. 6x6): one block per output pixel, its pixel lanes split the bin
+__global__ void __launch_bounds__(256) adaptive_avgpool_fwd_coop_kernel(V4 x, V4 y) {
+  const int cg = x.C / 8;
+  const int g = threadIdx.x % cg, pl = threadIdx.x / cg, lanes = blockDim.x / cg;
+  int r = blockIdx.x;
+  const int w = r % y.W;
+  r /= y.W;
+  const int h = r % y.H, n = r / y.H;
+  const int h0 = bin_lo(h, x.H, y.H), h1 = bin_hi(h, x.H, y.H), w0 = bin_lo(w, x.W, y.W), w1 = bin_hi(w, x.W, y.W);
+  const int ww_n = w1 - w0, cnt = (h1 - h0) * ww_n;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int k = pl; k < cnt && pl < lanes; k += lanes) {
+    const F8 v = unpack8(ld16(x.at(n, h0 + k / ww_n, w0 + k % ww_n) + g * 8));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += v.v[i];
+  }
+  if (lanes_reduce(acc, cg)) {
+    const float inv = 1.f / (float)cnt;
     F8 o;
 #pragma unroll
     for (int i = 0; i < 8; ++i) o.v[i] = acc[i] * inv;
@@ -478,6 +556,12 @@ extern "C" int pdac_bilinear_bwd(const PdacView* dy, int align_corners, const Pd
   PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C, "bilinear bwd: shape mismatch");
   const long long total = (long long)vdx.N * vdx.H * vdx.W * (vdx.C / 8);
   if (!total) return PDAC_OK;
+  if ((long long)vdy.H * vdy.W >= 64LL * vdx.H * vdx.W && vdx.C / 8 <= 128) {
+    bilinear_bwd_coop_kernel<<<vdx.N * vdx.H * vdx.W, 256, 0, (cudaStream_t)stream>>>(
+        vdy, vdx, make_lin(vdx.H, vdy.H, align_corners), make_lin(vdx.W, vdy.W, align_corners));
+    PDAC_LAUNCH_CHECK("bilinear_bwd_coop");
+    return PDAC_OK;
+  }
   bilinear_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(
       vdy, vdx, make_lin(vdx.H, vdy.H, align_corners), make_lin(vdx.W, vdy.W, align_corners));
   PDAC_LAUNCH_CHECK("bilinear_bwd");
@@ -515,6 +599,11 @@ extern "C" int pdac_adaptive_avgpool_fwd(const PdacView* x, const PdacView* y, v
   PDAC_REQUIRE(vy.N == vx.N && vy.C == vx.C, "adaptive_avgpool: shape mismatch");
   const long long total = (long long)vy.N * vy.H * vy.W * (vx.C / 8);
   if (!total) return PDAC_OK;
+  if ((long long)vx.H * vx.W >= 64LL * vy.H * vy.W && vx.C / 8 <= 128) {
+    adaptive_avgpool_fwd_coop_kernel<<<vy.N * vy.H * vy.W, 256, 0, (cudaStream_t)stream>>>(vx, vy);
+    PDAC_LAUNCH_CHECK("adaptive_avgpool_fwd_coop");
+    return PDAC_OK;
+  }
   adaptive_avgpool_fwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vx, vy);
   PDAC_LAUNCH_CHECK("adaptive_avgpool_fwd");
   return PDAC_OK;
