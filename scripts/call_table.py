@@ -13,8 +13,15 @@ if _mk == "unet":
     m = Unet(encoder_weights=None).cuda().train()
 else:
     from pdac_pathological_image_segmentation_b200 import smp as _P
-    _cls = {"fpn": _P.FPN, "pspnet": _P.PSPNet, "deeplabv3+": _P.DeepLabV3Plus}[_mk]
-    m = _cls(encoder_weights=None).cuda().train()
+    if _mk == "resunet":
+        import warnings
+        from pdac_pathological_image_segmentation_b200.resunet import ResUNet
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            m = ResUNet(num_classes=1, output_size=512).cuda().train()
+    else:
+        _cls = {"fpn": _P.FPN, "pspnet": _P.PSPNet, "deeplabv3+": _P.DeepLabV3Plus}[_mk]
+        m = _cls(encoder_weights=None).cuda().train()
 ts = TrainStep(m)
 img, mask = synthetic_batch(B, 512, seed=41)
 img, mask = img.cuda(), mask.cuda()
