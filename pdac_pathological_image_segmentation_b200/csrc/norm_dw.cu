@@ -418,49 +418,53 @@ __global__ void __launch_bounds__(256, 2) dw3x3_d1_kernel(ImgView x, int H, int 
   }
 }
 
-__global__ void __launch_bounds__(256) dw3x3_d1_wgrad_kernel(ImgView x, ImgView dy, int H, int W,
-                                                             float* __restrict__ dw, int cg, int ppb) {
+// Weight gradient, dilation 1: a thread owns (channel group, image row, kernel row r) and slides three packed columns of
+// input row h + r - 1 against dy row h: 24 accumulators per thread (3 blocks / SM) instead of 72 (1 block / SM).
+__global__ void __launch_bounds__(256, 3) dw3x3_d1_wgrad_kernel(ImgView x, ImgView dy, int H, int W,
+                                                                float* __restrict__ dw, int cg, int ppb) {
+  extern __shared__ float s_dw[];  // [cg * 8 channels][9 taps]
+  for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) s_dw[i] = 0.f;
+  __syncthreads();
   const int g = threadIdx.x % cg, pl = threadIdx.x / cg;
+  const int rows = ppb / 3, rl = pl / 3, r = pl - rl * 3;
   const int n = blockIdx.y;
-  const bool lane_ok = pl < ppb;
-  float acc[9][8];
+  const bool lane_ok = rl < rows;
+  float acc[3][8];
 #pragma unroll
-  for (int t = 0; t < 9; ++t)
+  for (int t = 0; t < 3; ++t)
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[t][i] = 0.f;
   const bf16* xb = x.ptr + (long long)n * x.sN + g * 8;
   const bf16* db = dy.ptr + (long long)n * dy.sN + g * 8;
   const uint4 zero = make_uint4(0, 0, 0, 0);
-  for (int h = blockIdx.x * ppb + pl; lane_ok && h < H; h += gridDim.x * ppb) {
-    uint4 c0[3], c1[3], c2[3];
-#pragma unroll
-    for (int r = 0; r < 3; ++r) {
-      const int hh = h + r - 1;
-      c0[r] = zero;
-      c1[r] = (hh >= 0 && hh < H) ? ld16(xb + (long long)(hh * W) * x.ps) : zero;
-    }
+  for (int h = blockIdx.x * rows + rl; lane_ok && h < H; h += gridDim.x * rows) {
+    const int hh = h + r - 1;
+    if (hh < 0 || hh >= H) continue;  // zero padding row: contributes nothing
+    const bf16* xr = xb + (long long)(hh * W) * x.ps;
+    const bf16* dr = db + (long long)(h * W) * dy.ps;
+    uint4 c0 = zero, c1 = ld16(xr), c2;
     for (int w = 0; w < W; ++w) {
-      const F8 d = unpack8(ld16_stream(db + (long long)(h * W + w) * dy.ps));
+      const F8 d = unpack8(ld16(dr + (long long)w * dy.ps));
+      c2 = (w + 1 < W) ? ld16(xr + (long long)(w + 1) * x.ps) : zero;
+      const F8 a0 = unpack8(c0), a1 = unpack8(c1), a2 = unpack8(c2);
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
-        const int hh = h + r - 1;
-        c2[r] = (hh >= 0 && hh < H && w + 1 < W) ? ld16(xb + (long long)(hh * W + w + 1) * x.ps) : zero;
+      for (int i = 0; i < 8; ++i) {
+        acc[0][i] = fmaf(a0.v[i], d.v[i], acc[0][i]);
+        acc[1][i] = fmaf(a1.v[i], d.v[i], acc[1][i]);
+        acc[2][i] = fmaf(a2.v[i], d.v[i], acc[2][i]);
       }
-#pragma unroll
-      for (int r = 0; r < 3; ++r) {
-        const F8 a0 = unpack8(c0[r]), a1 = unpack8(c1[r]), a2 = unpack8(c2[r]);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          acc[r * 3][i] = fmaf(a0.v[i], d.v[i], acc[r * 3][i]);
-          acc[r * 3 + 1][i] = fmaf(a1.v[i], d.v[i], acc[r * 3 + 1][i]);
-          acc[r * 3 + 2][i] = fmaf(a2.v[i], d.v[i], acc[r * 3 + 2][i]);
-        }
-        c0[r] = c1[r];
-        c1[r] = c2[r];
-      }
+      c0 = c1;
+      c1 = c2;
     }
   }
-  dw_flush(acc, lane_ok, g, cg, dw);
+  if (lane_ok) {
+#pragma unroll
+    for (int t = 0; t < 3; ++t)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(&s_dw[(g * 8 + i) * 9 + r * 3 + t], acc[t][i]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) atomicAdd(dw + i, s_dw[i]);
 }
 
 }  // namespace pdac
@@ -574,9 +578,9 @@ extern "C" int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int d
   if ((int)g.grid.x > cap) g.grid.x = cap;
   const size_t smem = (size_t)g.cg * 72 * sizeof(float);
   PDAC_REQUIRE(smem <= 48 * 1024, "dwconv wgrad: too many channels (%d)", x->C);
-  if (dil == 1 && x->W >= 16) {
-    int bands = ceil_div(x->H, g.ppb);
-    int per_img = (num_sms() * 4 + x->N - 1) / x->N;  // ~4 blocks per SM in total, each walking whole rows
+  if (dil == 1 && x->W >= 16 && g.ppb >= 3) {
+    int bands = ceil_div(x->H, g.ppb / 3);
+    int per_img = (num_sms() * 6 + x->N - 1) / x->N;  // ~6 blocks per SM in total, each walking whole rows
     if (per_img > bands) per_img = bands;
     dw3x3_d1_wgrad_kernel<<<dim3(per_img, x->N), 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dw, g.cg, g.ppb);
     PDAC_LAUNCH_CHECK("dw3x3_d1_wgrad_kernel");
