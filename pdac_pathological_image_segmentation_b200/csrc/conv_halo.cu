@@ -118,7 +118,9 @@ __device__ __forceinline__ void halo_issue(uint32_t tacc, uint32_t acc_step, uin
   }
 }
 
-template <int NACC, int KS, int DUAL>
+// AFF: folded-BatchNorm inference epilogue (per-channel scale and shift); a separate instantiation because the epilogue
+// sits at the register limit and the training kernels must not pay for it
+template <int NACC, int KS, int DUAL, int AFF>
 __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ? 2 : 1)
     conv_halo_kernel(const __grid_constant__ HaloMaps maps, const __grid_constant__ HaloParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -465,15 +467,29 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                 float f[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-                if (p.scale) {
+                if (AFF && p.bias && c0 + c + 16 <= nch) {
+                  // folded BatchNorm (inference): 8 vector loads instead of 32 scalar ones per 16 outputs
+                  const float4* sp = reinterpret_cast<const float4*>(p.scale + n0 + c0 + c);
+                  const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c0 + c);
 #pragma unroll
-                  for (int i = 0; i < 16; ++i)
-                    if (c0 + c + i < nch) f[i] *= __ldg(p.scale + n0 + c0 + c + i);
-                }
-                if (p.bias) {
+                  for (int i = 0; i < 4; ++i) {
+                    const float4 sv = __ldg(sp + i), bv = __ldg(bp + i);
+                    f[4 * i] = fmaf(f[4 * i], sv.x, bv.x);
+                    f[4 * i + 1] = fmaf(f[4 * i + 1], sv.y, bv.y);
+                    f[4 * i + 2] = fmaf(f[4 * i + 2], sv.z, bv.z);
+                    f[4 * i + 3] = fmaf(f[4 * i + 3], sv.w, bv.w);
+                  }
+                } else {
+                  if (p.scale) {
 #pragma unroll
-                  for (int i = 0; i < 16; ++i)
-                    if (c0 + c + i < nch) f[i] += __ldg(p.bias + n0 + c0 + c + i);
+                    for (int i = 0; i < 16; ++i)
+                      if (c0 + c + i < nch) f[i] *= __ldg(p.scale + n0 + c0 + c + i);
+                  }
+                  if (p.bias) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                      if (c0 + c + i < nch) f[i] += __ldg(p.bias + n0 + c0 + c + i);
+                  }
                 }
                 if (p.addend && valid) {
                   const bf16* ap = arow + c0 + c;
@@ -847,6 +863,8 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
                  "out/addend view must be 16-byte aligned");
   p.bias = bias;
   p.scale = epi_scale();
+  if (p.scale && bias)
+    PDAC_REQUIRE(((uintptr_t)p.scale & 15) == 0 && ((uintptr_t)bias & 15) == 0, "affine scale / shift must be 16-byte aligned");
   p.stats = stats;
   p.relu = tc->relu;
   p.err = device_err_flag();
@@ -865,23 +883,23 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   if (per_n < 1) per_n = 1;
   if (per_n > p.tiles_sp) per_n = p.tiles_sp;
   typedef void (*HaloKernel)(const HaloMaps, const HaloParams);
-  static const HaloKernel table[4][5] = {
-      {conv_halo_kernel<1, 1, 0>, conv_halo_kernel<1, 2, 0>, conv_halo_kernel<1, 4, 0>, conv_halo_kernel<1, 1, 1>,
-       conv_halo_kernel<1, 2, 1>},
-      {conv_halo_kernel<2, 1, 0>, conv_halo_kernel<2, 2, 0>, conv_halo_kernel<2, 4, 0>, conv_halo_kernel<2, 1, 1>,
-       conv_halo_kernel<2, 2, 1>},
-      {conv_halo_kernel<3, 1, 0>, conv_halo_kernel<3, 2, 0>, conv_halo_kernel<3, 4, 0>, conv_halo_kernel<3, 1, 1>,
-       conv_halo_kernel<3, 2, 1>},
-      {conv_halo_kernel<4, 1, 0>, conv_halo_kernel<4, 2, 0>, conv_halo_kernel<4, 4, 0>, conv_halo_kernel<4, 1, 1>,
-       conv_halo_kernel<4, 2, 1>}};
-  static bool attr_set[4][5] = {};
+#define HALO_ROW(n, aff)                                                                                       \
+  {                                                                                                             \
+    conv_halo_kernel<n, 1, 0, aff>, conv_halo_kernel<n, 2, 0, aff>, conv_halo_kernel<n, 4, 0, aff>,             \
+        conv_halo_kernel<n, 1, 1, aff>, conv_halo_kernel<n, 2, 1, aff>                                          \
+  }
+  static const HaloKernel table[2][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
+                                            {HALO_ROW(1, 1), HALO_ROW(2, 1), HALO_ROW(3, 1), HALO_ROW(4, 1)}};
+#undef HALO_ROW
+  static bool attr_set[2][4][5] = {};
+  const int ka = p.scale ? 1 : 0;
   const int ki = pl.nacc - 1, kj = (ck == 16 ? 0 : (ck == 32 ? 1 : 2)) + (dual ? 3 : 0);
-  HaloKernel kern = table[ki][kj];
-  if (!attr_set[ki][kj]) {
+  HaloKernel kern = table[ka][ki][kj];
+  if (!attr_set[ka][ki][kj]) {
     PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((dual ? 105 : 221) * 1024)));
     if (dual)
       PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    attr_set[ki][kj] = true;
+    attr_set[ka][ki][kj] = true;
   }
   kern<<<per_n * p.tiles_c, dual ? kHaloThreadsDual : kHaloThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_halo_kernel");
