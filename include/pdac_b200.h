@@ -228,6 +228,11 @@ int pdac_argmax_nchw(const float* logits, int N, int C, long long HW, uint8_t* o
  * the (slide_h x slide_w) band are dropped. */
 int pdac_stitch_tiles(const uint8_t* tiles, const int32_t* rows, const int32_t* cols, int T, int th, int tw,
                       uint8_t* slide, long long slide_h, long long slide_w, long long row0, void* stream);
+/* Tumour overlay (README.md:28-35; visualize/predict_overlay.ipynb is a missing blob, integer spec in
+ * oracle/util_oracle.py overlay_blend): rgb / out uint8 HWC [npix][3], mask uint8 [npix]; where mask != 0
+ * out = (rgb*(256-alpha_256) + color*alpha_256) >> 8, elsewhere out = rgb. out may alias rgb. */
+int pdac_overlay_blend(const uint8_t* rgb, const uint8_t* mask, long long npix, int color_r, int color_g, int color_b,
+                       int alpha_256, uint8_t* out, void* stream);
 /* torch.optim.Adam semantics over one flat fp32 arena; grads are multiplied by grad_scale first. */
 int pdac_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                    float beta1, float beta2, float eps, int step, float grad_scale, void* stream);

@@ -85,6 +85,7 @@ SIGNATURES = {
     "pdac_dice_score": [_p, _i, _p, _i, _ll, _p, _f, _p, _p],
     "pdac_argmax_nchw": [_p, _i, _i, _ll, _p, _p],
     "pdac_stitch_tiles": [_p, _p, _p, _i, _i, _i, _p, _ll, _ll, _ll, _p],
+    "pdac_overlay_blend": [_p, _p, _ll, _i, _i, _i, _i, _p, _p],
     "pdac_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _f, _p],
 }
 

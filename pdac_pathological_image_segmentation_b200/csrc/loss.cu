@@ -4,6 +4,7 @@
 //   mask                        train_worker.py:24,72; test.py:144   ge(sigmoid(x), 0.5).float()
 //   softmax-argmax              BASELINE.json configs[0]/[4] (classes >= 2): argmax_c x_c, ties -> lowest index
 //   stitch                      visualize/predict_overlay.ipynb (missing) per configs/visualize_config.yaml:3-15
+//   overlay                     README.md:28-35 tumour overlay (notebook missing): integer blend, spec in oracle/util_oracle.py
 //   Adam                        torch.optim.Adam(lr) at train_worker.py:184 (betas .9/.999, eps 1e-8, no weight decay)
 // Reductions accumulate per-thread in fp32, per-block and globally in fp64 (the reference's fp32 tree sum is only
 // approximately exact at 2^24+ elements), counts in int64.
@@ -168,6 +169,59 @@ __global__ void __launch_bounds__(256) stitch_kernel(const uint8_t* __restrict__
   }
 }
 
+// Overlay (oracle/util_oracle.py overlay_blend): where mask != 0, out = (rgb*(256-a) + color*a) >> 8, elsewhere rgb.
+// One work item = 16 pixels: one 16-byte mask load, three 16-byte HWC loads and stores. out may alias rgb.
+// Two bytes are blended per 32-bit multiply-add (v*(256-a) + c*a <= 65280 never carries out of a 16-bit lane); the
+// channel order of a 32-bit word repeats every three words (rgbr gbrg brgb), so the colour constants come in three
+// phases: ce[] for bytes 0/2 and co[] for bytes 1/3 of a word, each c*a in a 16-bit lane.
+struct OverlayConst {
+  uint32_t ce[3], co[3], ca[3], ia;
+};
+
+__device__ __forceinline__ uint32_t blend_word(uint32_t w, uint32_t sel, uint32_t ce, uint32_t co, uint32_t ia) {
+  const uint32_t e = (w & 0x00ff00ffu) * ia + ce;
+  const uint32_t o = ((w >> 8) & 0x00ff00ffu) * ia + co;
+  const uint32_t bl = ((e >> 8) & 0x00ff00ffu) | (o & 0xff00ff00u);
+  return (bl & sel) | (w & ~sel);
+}
+
+// 4 mask bytes -> 3 words of HWC bytes (12 bytes of 4 pixels)
+__device__ __forceinline__ void blend_4px(uint32_t m, uint32_t& w0, uint32_t& w1, uint32_t& w2, const OverlayConst& k) {
+  if (m == 0u) return;
+  const uint32_t nz = __vcmpne4(m, 0u);  // 0xff per non-zero mask byte
+  w0 = blend_word(w0, __byte_perm(nz, 0u, 0x1000), k.ce[0], k.co[0], k.ia);  // p0 p0 p0 p1
+  w1 = blend_word(w1, __byte_perm(nz, 0u, 0x2211), k.ce[1], k.co[1], k.ia);  // p1 p1 p2 p2
+  w2 = blend_word(w2, __byte_perm(nz, 0u, 0x3332), k.ce[2], k.co[2], k.ia);  // p2 p3 p3 p3
+}
+
+__global__ void __launch_bounds__(256) overlay_kernel(const uint8_t* rgb, const uint8_t* __restrict__ mask,
+                                                      long long npix, OverlayConst k, uint8_t* out, int vec_ok) {
+  const long long groups = vec_ok ? npix / 16 : 0;
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < groups; g += (long long)gridDim.x * blockDim.x) {
+    const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(mask) + g);
+    const uint4* src = reinterpret_cast<const uint4*>(rgb) + g * 3;
+    uint4 a = src[0], b = src[1], c = src[2];
+    blend_4px(m4.x, a.x, a.y, a.z, k);
+    blend_4px(m4.y, a.w, b.x, b.y, k);
+    blend_4px(m4.z, b.z, b.w, c.x, k);
+    blend_4px(m4.w, c.y, c.z, c.w, k);
+    uint4* dst = reinterpret_cast<uint4*>(out) + g * 3;
+    dst[0] = a;
+    dst[1] = b;
+    dst[2] = c;
+  }
+  // tail pixels (and the whole image when the pointers are not 16-byte aligned)
+  for (long long i = groups * 16 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < npix;
+       i += (long long)gridDim.x * blockDim.x) {
+    const bool on = mask[i] != 0;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      const uint32_t old = rgb[i * 3 + ch];
+      out[i * 3 + ch] = (uint8_t)(on ? (old * k.ia + k.ca[ch]) >> 8 : old);
+    }
+  }
+}
+
 // Adam over one flat fp32 arena (parameters, gradients and both moments share the element index)
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                    float* __restrict__ m, float* __restrict__ v, long long n, float lr,
@@ -280,6 +334,26 @@ extern "C" int pdac_stitch_tiles(const uint8_t* tiles, const int32_t* rows, cons
   stitch_kernel<<<rblocks(total), 256, 0, (cudaStream_t)stream>>>(tiles, rows, cols, T, th, tw, slide, slide_h, slide_w,
                                                                   row0);
   PDAC_LAUNCH_CHECK("stitch");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_overlay_blend(const uint8_t* rgb, const uint8_t* mask, long long npix, int color_r, int color_g,
+                                  int color_b, int alpha_256, uint8_t* out, void* stream) {
+  PDAC_REQUIRE(rgb && mask && out && npix >= 0, "overlay: bad arguments");
+  PDAC_REQUIRE(alpha_256 >= 0 && alpha_256 <= 256, "overlay: alpha_256 must lie in [0, 256]");
+  PDAC_REQUIRE(((color_r | color_g | color_b) & ~0xff) == 0, "overlay: colour components must lie in [0, 255]");
+  if (npix == 0) return PDAC_OK;
+  const int vec_ok = ((((uintptr_t)rgb | (uintptr_t)mask | (uintptr_t)out) & 15) == 0) ? 1 : 0;
+  const uint32_t a = (uint32_t)alpha_256;
+  const uint32_t cr = (uint32_t)color_r * a, cg = (uint32_t)color_g * a, cb = (uint32_t)color_b * a;
+  OverlayConst k;
+  k.ca[0] = cr, k.ca[1] = cg, k.ca[2] = cb, k.ia = 256u - a;
+  k.ce[0] = cr | (cb << 16), k.co[0] = cg | (cr << 16);  // word bytes r g b r
+  k.ce[1] = cg | (cr << 16), k.co[1] = cb | (cg << 16);  //            g b r g
+  k.ce[2] = cb | (cg << 16), k.co[2] = cr | (cb << 16);  //            b r g b
+  overlay_kernel<<<rblocks(vec_ok ? (npix + 15) / 16 : npix), 256, 0, (cudaStream_t)stream>>>(rgb, mask, npix, k, out,
+                                                                                             vec_ok);
+  PDAC_LAUNCH_CHECK("overlay");
   return PDAC_OK;
 }
 

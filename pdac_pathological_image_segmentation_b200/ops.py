@@ -559,6 +559,20 @@ def stitch_tiles(tiles, rows, cols, slide, row0=0):
     return slide
 
 
+def overlay_blend(rgb, mask, color=(255, 0, 0), alpha_256=102, out=None):
+    """rgb uint8 (..., H, W, 3), mask uint8 (..., H, W): tumour overlay by integer blend (oracle overlay_blend).
+    out=rgb blends in place."""
+    _need_cuda(rgb, "rgb")
+    assert rgb.dtype == torch.uint8 and mask.dtype == torch.uint8 and rgb.is_contiguous() and mask.is_contiguous()
+    assert rgb.shape[-1] == 3 and rgb.shape[:-1] == mask.shape
+    if out is None:
+        out = torch.empty_like(rgb)
+    assert out.dtype == torch.uint8 and out.is_contiguous() and out.shape == rgb.shape
+    call("pdac_overlay_blend", _ptr(rgb), _ptr(mask), mask.numel(), int(color[0]), int(color[1]), int(color[2]),
+         int(alpha_256), _ptr(out), _stream())
+    return out
+
+
 def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0):
     call("pdac_adam_step", _ptr(params), _ptr(grads), _ptr(exp_avg), _ptr(exp_avg_sq), params.numel(), lr, beta1, beta2,
          eps, step, grad_scale, _stream())

@@ -50,3 +50,10 @@ class SlideInference:
             mask = ops.argmax_nchw(out)
         ops.stitch_tiles(mask.contiguous(), rows, cols, self.band, row0=self.r0 * self.tile)
         return mask
+
+    def overlay(self, band_rgb, color=(255, 0, 0), alpha_256=102, out=None):
+        """Tumour overlay of this rank's band (README.md:28-35; the notebook that drew it is a missing blob, the
+        integer blend is specified in oracle/util_oracle.py overlay_blend). band_rgb: uint8 (band rows, slide
+        columns, 3) on the device, same pixel grid as self.band; out=band_rgb blends in place."""
+        assert tuple(band_rgb.shape) == (*self.band.shape, 3), "band_rgb must cover this rank's band"
+        return ops.overlay_blend(band_rgb, self.band, color, alpha_256, out=out)
