@@ -339,10 +339,11 @@ extern "C" int pdac_stitch_tiles(const uint8_t* tiles, const int32_t* rows, cons
 
 extern "C" int pdac_overlay_blend(const uint8_t* rgb, const uint8_t* mask, long long npix, int color_r, int color_g,
                                   int color_b, int alpha_256, uint8_t* out, void* stream) {
-  PDAC_REQUIRE(rgb && mask && out && npix >= 0, "overlay: bad arguments");
   PDAC_REQUIRE(alpha_256 >= 0 && alpha_256 <= 256, "overlay: alpha_256 must lie in [0, 256]");
   PDAC_REQUIRE(((color_r | color_g | color_b) & ~0xff) == 0, "overlay: colour components must lie in [0, 255]");
-  if (npix == 0) return PDAC_OK;
+  PDAC_REQUIRE(npix >= 0, "overlay: negative pixel count");
+  if (npix == 0) return PDAC_OK;  // empty band: the pointers may be null
+  PDAC_REQUIRE(rgb && mask && out, "overlay: null buffer");
   const int vec_ok = ((((uintptr_t)rgb | (uintptr_t)mask | (uintptr_t)out) & 15) == 0) ? 1 : 0;
   const uint32_t a = (uint32_t)alpha_256;
   const uint32_t cr = (uint32_t)color_r * a, cg = (uint32_t)color_g * a, cb = (uint32_t)color_b * a;
