@@ -57,6 +57,11 @@ def test_no_cpu_fallback_at_the_abi(lib):
     assert len(lib.pdac_last_error()) > 0
     rc = lib.pdac_dice_fwd(None, None, 0, 0, None, ctypes.c_float(1e-6), None, None)
     assert rc == -1 and b"null" in lib.pdac_last_error()
+    # argument validation of the overlay entry point happens before any launch
+    assert lib.pdac_overlay_blend(None, None, 16, 255, 0, 0, 300, None, None) != 0 and b"alpha" in lib.pdac_last_error()
+    assert lib.pdac_overlay_blend(None, None, 16, 256, 0, 0, 102, None, None) != 0 and b"colour" in lib.pdac_last_error()
+    assert lib.pdac_overlay_blend(None, None, 16, 255, 0, 0, 102, None, None) != 0 and b"null" in lib.pdac_last_error()
+    assert lib.pdac_overlay_blend(None, None, 0, 255, 0, 0, 102, None, None) == 0      # empty band: nothing to do
 
 
 def test_modules_refuse_cpu_tensors():
