@@ -120,3 +120,30 @@ def test_synthetic_generators_agree():
     from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
     a, b = R.synthetic_batch(2, 64, seed=5), synthetic_batch(2, 64, seed=5)
     assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_reference_checkpoint_file_round_trip(tmp_path):
+    """A .pth as train_worker.py:116-125 writes it ({"model", "optimizer", "epoch", "previous_best"}, DDP "module." key
+    prefix) loads through the loop of train_worker.py:185-196 / test.py:118-124 into our module, strictly and
+    value-for-value, and Adam's state loads onto our parameters."""
+    from collections import OrderedDict
+    from oracle import resunet_oracle as R
+    from pdac_pathological_image_segmentation_b200.resunet import ResUNet
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        ours = ResUNet(1, 64)
+    state = R.make_state(1, seed=3)                                   # reference key order / shapes (models/resunet.py)
+    opt = torch.optim.Adam(ours.parameters(), lr=1e-4)
+    ckpt = {"model": OrderedDict(("module." + k, v.clone()) for k, v in state.items()),
+            "optimizer": opt.state_dict(), "epoch": 7, "previous_best": 0.5}
+    path = str(tmp_path / "latest.pth")
+    torch.save(ckpt, path)
+    loaded = torch.load(path, weights_only=False)
+    new_state = OrderedDict()
+    for n, v in loaded["model"].items():
+        new_state[n.replace("module.", "")] = v
+    ours.load_state_dict(new_state)                                   # strict, as the reference calls it
+    for (k, v), (k2, v2) in zip(ours.state_dict().items(), ckpt["model"].items()):
+        assert "module." + k == k2 and torch.equal(v, v2), k
+    torch.optim.Adam(ours.parameters(), lr=1e-4).load_state_dict(loaded["optimizer"])
+    assert loaded["epoch"] == 7 and loaded["previous_best"] == 0.5
