@@ -41,6 +41,13 @@ extern "C" {
 #define PDAC_E_TIMEOUT (-3)  /* a device-side pipeline barrier timed out (see pdac_check_device_flag) */
 #define PDAC_E_NODEVICE (-4) /* no sm_100 device / driver entry point missing */
 
+/* Reproducibility (the reference requests cudnn.deterministic, train_main.py:36-43): no result of this library depends
+ * on the order in which thread blocks run. Cross-block reductions store one partial row per block into caller memory
+ * and add the rows in index order; PDAC_STAT_ROWS is the row capacity those tables need (4 blocks x 148 SMs). The
+ * split-K weight gradients and the bias gradient take an optional scratch buffer: with it they are reproducible,
+ * without it they fall back to fp32 atomics (faster by a few per cent, last-bit nondeterministic). */
+#define PDAC_STAT_ROWS 592
+
 /* NHWC view: element (n,h,w,c) lives at ptr + n*sN + h*sH + w*sW + c (in elements of the view's dtype). */
 typedef struct PdacView {
   void* ptr;
@@ -64,8 +71,12 @@ const char* pdac_last_error(void);
 /* Which tensor-core kernel this thread's last convolution call dispatched to: 1 conv_tc_kernel, 2 conv_halo_kernel,
  * 3 wgrad_tc_kernel, 4 wgrad_halo_kernel (0: none yet). Used by bench.py to attribute event times to kernels. */
 int pdac_last_kernel_id(void);
-/* Reads (and clears) the device-side pipeline error flag; synchronises `stream`. Debug/tests only. */
+/* Reads (and clears) the device-side pipeline error flag; synchronises `stream`. */
 int pdac_check_device_flag(void* stream);
+/* The same flag without synchronising: it lives in mapped pinned host memory, so the host sees what the kernels that
+ * have FINISHED so far reported (0 = fine). The product path polls it once per step / batch (trainer.py, wsi.py,
+ * module_base.py) and raises: a timed-out TMA / tcgen05 pipeline barrier never goes unnoticed into the optimizer. */
+int pdac_peek_device_flag(void);
 
 /* ---- tensor-core implicit-GEMM convolutions (conv_tc.cu) ----------------------------------------------------
  * Generalised "tap convolution": out[n,h,w,:] = act( sum_t W_t * cat_s(views[tap.src+s])[n, h+dh_t, w+dw_t, :]
@@ -85,8 +96,9 @@ typedef struct PdacTapConv {
   int32_t relu;
   PdacTap taps[PDAC_MAX_TAPS];
 } PdacTapConv;
-/* stats: optional fp32 [2][out->C]: per-channel sum and sum of squares of the stored (bf16-rounded) outputs are
- * atomically accumulated (BatchNorm batch statistics); caller zeroes it. */
+/* stats: optional fp32 [PDAC_STAT_ROWS][2][out->C], zeroed by the caller: every CTA (warpgroup) adds the per-channel
+ * sum and sum of squares of the outputs it stored (bf16-rounded values) into its own row — BatchNorm batch statistics
+ * as partial rows that pdac_bn_prepare adds in a fixed order. */
 int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
                      const float* bias, const PdacView* addend, const PdacView* out, float* stats, void* stream);
 /* Same with a per-channel affine epilogue: out = act( acc * scale[c] + shift[c] + addend ) — eval-mode BatchNorm
@@ -94,11 +106,14 @@ int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacView* views, 
 int pdac_tapconv_fwd_affine(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
                             const float* scale, const float* shift, const PdacView* addend, const PdacView* out,
                             void* stream);
-/* dw[t*tap_stride + a*a_stride + b*b_stride] += sum_pixels cat(views)[p + off_t, a] * dy[p, b]  (fp32 atomics;
- * caller zeroes dw). a runs over the concatenated source channels, b over the first b_valid channels of dy
- * (0 = all; dy may be channel-padded). */
+/* dw[t*tap_stride + a*a_stride + b*b_stride] += sum_pixels cat(views)[p + off_t, a] * dy[p, b]  (caller zeroes dw).
+ * a runs over the concatenated source channels, b over the first b_valid channels of dy (0 = all; dy may be
+ * channel-padded). scratch (fp32, 16-byte aligned, scratch_bytes >= n_taps * A * B * 4; 64 MB lets every layer of the
+ * networks here keep its full split-K width): the split-K shares are stored there and added in a fixed order
+ * (reproducible); scratch == NULL: fp32 atomics into dw. */
 int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy, float* dw,
-                       int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, void* stream);
+                       int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, float* scratch,
+                       long long scratch_bytes, void* stream);
 
 /* nn.Conv2d forward: out = [relu](conv(cat(src[0..n_src-1]), w) + bias + addend). w_packed: [R*S*wrows][Ctot] with
  * row (r*S+s)*wrows + cout. */
@@ -114,14 +129,15 @@ int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const void* w_pack
 /* dw += sum_pixels dy[p,cout] * cat(src)[p*stride + off, cin]. dw_layout 0: fp32 [R*S][Cout][Ctot];
  * dw_layout 1: the nn.Conv2d state_dict layout [cout_valid][Ctot][R][S] (gradients land where autograd wants them). */
 int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,
-                      int dw_layout, void* stream);
+                      int dw_layout, float* scratch, long long scratch_bytes, void* stream);
 /* nn.ConvTranspose2d(k=2, s=2): out[2i+a,2j+b,:] = W[a,b] x[i,j,:] + bias. w_packed: [4*wrows][Cin], row
  * (a*2+b)*wrows + cout; w_packed_t: [4*wrows][Cout], row (a*2+b)*wrows + cin. */
 int pdac_convt2x2_fwd(const PdacView* x, const void* w_packed, int wrows, const float* bias, int relu,
                       const PdacView* out, void* stream);
 int pdac_convt2x2_dgrad(const PdacView* dy, const void* w_packed_t, int wrows, const PdacView* dx, void* stream);
 /* dw_layout 0: [4][Cout][Cin]; 1: the nn.ConvTranspose2d state_dict layout [Cin][Cout][2][2]. */
-int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, int dw_layout, void* stream);
+int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, int dw_layout, float* scratch,
+                        long long scratch_bytes, void* stream);
 
 /* ---- layout / packing (layout.cu) --------------------------------------------------------------------------- */
 /* x: fp32 NCHW (N,C,H,W) -> out: NHWC bf16 view with out->C >= C (extra channels zeroed). */
@@ -147,19 +163,21 @@ int pdac_pack_stem_weight(const float* w, int O, void* wp, void* stream);
 int pdac_unpack_stem_wgrad(const float* dwp, int O, float* dw, void* stream);
 
 /* ---- BatchNorm / ReLU / residual (bn.cu) -------------------------------------------------------------------- */
-/* stats: fp32 [2][C] sum / sum-of-squares over `count` values per channel (from the conv epilogue). Writes
+/* stats: fp32 [n_rows][2][C] partial sums / sums of squares over `count` values per channel in total (the conv
+ * epilogues' rows; n_rows = PDAC_STAT_ROWS, or 1 for a plain [2][C] vector), added in a fixed order in double. Writes
  * scale_shift [2][C] (y = x*scale + shift), mean_invstd [2][C] (saved for backward) and, when training, updates
  * running_mean/var in place (momentum; unbiased variance) and increments the int64 num_batches_tracked scalar (may be
  * NULL). train=0 derives everything from the running stats. */
-int pdac_bn_prepare(const float* stats, double count, const float* gamma, const float* beta, float eps, float momentum,
-                    int train, float* running_mean, float* running_var, long long* num_batches_tracked,
-                    float* scale_shift, float* mean_invstd, int C, void* stream);
+int pdac_bn_prepare(const float* stats, int n_rows, double count, const float* gamma, const float* beta, float eps,
+                    float momentum, int train, float* running_mean, float* running_var,
+                    long long* num_batches_tracked, float* scale_shift, float* mean_invstd, int C, void* stream);
 /* y = [relu](x*scale[c] + shift[c] + residual); scale_shift / residual may be NULL. */
 int pdac_scale_shift_act(const PdacView* x, const float* scale_shift, const PdacView* residual, int relu,
                          const PdacView* y, void* stream);
-/* BN backward pass 1: dz = dy * (y > 0); sums[c] += sum dz, sums[C+c] += sum dz*xhat. ReLU mask: from y; or, with
- * y NULL and scale_shift (the forward's [2][C]) given, recomputed as x*scale + shift > 0 (y is then never read); with
- * both NULL there is no ReLU. */
+/* BN backward pass 1: dz = dy * (y > 0); sums[c] = sum dz, sums[C+c] = sum dz*xhat. sums: fp32
+ * [1 + PDAC_STAT_ROWS][2][C] (no zeroing needed): rows 1.. receive the blocks' partials, row 0 their fixed-order total,
+ * which is what pdac_bn_bwd_apply reads. ReLU mask: from y; or, with y NULL and scale_shift (the forward's [2][C])
+ * given, recomputed as x*scale + shift > 0 (y is then never read); with both NULL there is no ReLU. */
 int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
                        const float* scale_shift, float* sums, void* stream);
 /* BN backward pass 2: dx = gamma*invstd*(dz - sums0/count - xhat*sums1/count) (train) or gamma*invstd*dz (eval);
@@ -167,8 +185,10 @@ int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x,
 int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, const float* mean_invstd,
                       const float* gamma, const float* scale_shift, const float* sums, double count, int train,
                       const PdacView* dx, const PdacView* dz_out, float* dgamma, float* dbeta, void* stream);
-/* dz = dy * (y > 0) (y, dz may be NULL); dbias[c] += sum dz (may be NULL; caller zeroes). */
-int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias, void* stream);
+/* dz = dy * (y > 0) (y, dz may be NULL); dbias[c] += sum dz (may be NULL; caller zeroes). scratch: fp32
+ * [PDAC_STAT_ROWS][C] for the reproducible fixed-order sum, or NULL (fp32 atomics). */
+int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias, float* scratch,
+                       void* stream);
 
 /* ---- pooling / resampling (pool.cu) ------------------------------------------------------------------------- */
 /* idx: uint8 [N][Ho][Wo][C] arg-max tap (r*3+s), saved for backward (may be NULL in inference). */
@@ -212,7 +232,8 @@ int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int flip, const P
 int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, void* stream);
 
 /* ---- loss / metric / mask / stitch / optimiser (loss.cu) ---------------------------------------------------- */
-/* tgt_dtype: 0 = fp32, 1 = uint8. sums: 3 doubles (sum p*t, sum p, sum t), kept for backward. loss: 1 float. */
+/* tgt_dtype: 0 = fp32, 1 = uint8. sums: 3 * (1 + PDAC_STAT_ROWS) doubles: [0..2] = (sum p*t, sum p, sum t), kept for
+ * backward; the rest takes the blocks' partial rows, added in a fixed order (no zeroing needed). loss: 1 float. */
 int pdac_dice_fwd(const float* logits, const void* targets, int tgt_dtype, long long n, double* sums, float smooth,
                   float* loss, void* stream);
 int pdac_dice_bwd(const float* logits, const void* targets, int tgt_dtype, long long n, const double* sums, float smooth,

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PDAC_B200_LIB") or os.path.join(_HERE, "libpdac_b200.so")  # override: diagnostic builds
 
 PDAC_MAX_TAPS = 16
+PDAC_STAT_ROWS = 592  # include/pdac_b200.h: row capacity of the fixed-order partial-sum tables
 
 
 class PdacView(C.Structure):
@@ -40,15 +41,15 @@ _p, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
 SIGNATURES = {
     "pdac_check_device_flag": [_p],
     "pdac_tapconv_fwd": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
-    "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _i, _p],
+    "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _i, _p, _ll, _p],
     "pdac_conv2d_fwd": [C.POINTER(PdacConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
     "pdac_conv2d_fwd_affine": [C.POINTER(PdacConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
     "pdac_tapconv_fwd_affine": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
     "pdac_conv2d_dgrad": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, _p],
-    "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _i, _p],
+    "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _i, _p, _ll, _p],
     "pdac_convt2x2_fwd": [_VP, _p, _i, _p, _i, _VP, _p],
     "pdac_convt2x2_dgrad": [_VP, _p, _i, _VP, _p],
-    "pdac_convt2x2_wgrad": [_VP, _VP, _p, _i, _p],
+    "pdac_convt2x2_wgrad": [_VP, _VP, _p, _i, _p, _ll, _p],
     "pdac_nchw_f32_to_nhwc_bf16": [_p, _i, _i, _i, _i, _VP, _p],
     "pdac_nhwc_bf16_to_nchw_f32": [_VP, _i, _p, _p],
     "pdac_stem_prep_f32": [_p, _i, _i, _i, _p, _p],
@@ -56,11 +57,11 @@ SIGNATURES = {
     "pdac_pack_conv_weight": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
     "pdac_pack_stem_weight": [_p, _i, _p, _p],
     "pdac_unpack_stem_wgrad": [_p, _i, _p, _p],
-    "pdac_bn_prepare": [_p, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _p, _i, _p],
+    "pdac_bn_prepare": [_p, _i, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _p, _i, _p],
     "pdac_scale_shift_act": [_VP, _p, _VP, _i, _VP, _p],
     "pdac_bn_bwd_reduce": [_VP, _VP, _VP, _p, _p, _p, _p],
     "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],
-    "pdac_relu_bwd_bias": [_VP, _VP, _VP, _p, _p],
+    "pdac_relu_bwd_bias": [_VP, _VP, _VP, _p, _p, _p],
     "pdac_maxpool3x3s2_fwd": [_VP, _VP, _p, _p],
     "pdac_maxpool3x3s2_bwd": [_VP, _p, _VP, _p],
     "pdac_upsample_nearest2x_fwd": [_VP, _VP, _p],
@@ -109,6 +110,8 @@ def load():
     lib.pdac_last_error.argtypes = []
     lib.pdac_last_kernel_id.restype = C.c_int
     lib.pdac_last_kernel_id.argtypes = []
+    lib.pdac_peek_device_flag.restype = C.c_int
+    lib.pdac_peek_device_flag.argtypes = []
     for name, args in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype = C.c_int
@@ -147,3 +150,12 @@ def call(name, *args, flops=0, nbytes=0, tag=""):
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.pdac_last_error().decode()}")
     return rc
+
+
+def peek_device_flag():
+    """Polls the pipeline error flag (mapped pinned host memory) WITHOUT synchronising: raises if any kernel that has
+    finished so far reported a timed-out TMA / tcgen05 barrier. Called once per step / batch by the product path."""
+    lib = load()
+    rc = lib.pdac_peek_device_flag()
+    if rc != 0:
+        raise RuntimeError(f"pdac_b200 device pipeline error ({rc}): {lib.pdac_last_error().decode()}")

@@ -52,17 +52,39 @@ static EwGrid ew_grid(long long npix, int C, int resident) {
   const long long pfirst = (long long)blockIdx.x * (ppb_) + pl;
 
 // ------------------------------------------------------------------------------------------------ bn_prepare
-__global__ void bn_prepare_kernel(const float* __restrict__ stats, double count, const float* __restrict__ gamma,
+// stats: [n_rows][2][C] partial sums (one row per producing CTA / warpgroup, unused rows zero). The rows are added in
+// a fixed order (8 interleaved row groups per channel, combined in index order), in double: bit-reproducible batch
+// statistics whatever order the producers ran in.
+__global__ void __launch_bounds__(256) bn_prepare_kernel(const float* __restrict__ stats, int n_rows, double count,
+                                  const float* __restrict__ gamma,
                                   const float* __restrict__ beta, float eps, float momentum, int train,
                                   float* running_mean, float* running_var, long long* num_batches_tracked,
                                   float* __restrict__ scale_shift, float* __restrict__ mean_invstd, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+  __shared__ double part[8][32][2];
+  const int cl = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  if (train) {
+    double a0 = 0.0, a1 = 0.0;
+    if (c < C)
+      for (int r = rg; r < n_rows; r += 8) {
+        a0 += (double)stats[((size_t)r * 2) * C + c];
+        a1 += (double)stats[((size_t)r * 2 + 1) * C + c];
+      }
+    part[rg][cl][0] = a0;
+    part[rg][cl][1] = a1;
+  }
+  __syncthreads();
+  if (rg != 0 || c >= C) return;
   if (c == 0 && train && num_batches_tracked) *num_batches_tracked += 1;
   float mean, var;
   if (train) {
-    const double m = (double)stats[c] / count;
-    double v = (double)stats[C + c] / count - m * m;
+    double t0 = 0.0, t1 = 0.0;
+    for (int g = 0; g < 8; ++g) {
+      t0 += part[g][cl][0];
+      t1 += part[g][cl][1];
+    }
+    const double m = t0 / count;
+    double v = t1 / count - m * m;
     if (v < 0) v = 0;
     mean = (float)m;
     var = (float)v;
@@ -84,6 +106,30 @@ __global__ void bn_prepare_kernel(const float* __restrict__ stats, double count,
     mean_invstd[c] = mean;
     mean_invstd[C + c] = invstd;
   }
+}
+
+// out[c] (+)= sum_r rows[r][c], r = 0 .. n_rows-1 in a fixed order: the deterministic second stage of every
+// cross-block reduction (each block stores its partial row with plain stores; no floating-point atomics).
+__global__ void __launch_bounds__(256) rows_sum_kernel(const float* __restrict__ rows, int n_rows, int ncols,
+                                                       float* __restrict__ out, int accumulate) {
+  __shared__ float part[8][32];
+  const int cl = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  float a = 0.f;
+  if (c < ncols)
+    for (int r = rg; r < n_rows; r += 8) a += rows[(size_t)r * ncols + c];
+  part[rg][cl] = a;
+  __syncthreads();
+  if (rg == 0 && c < ncols) {
+    float t = 0.f;
+    for (int g = 0; g < 8; ++g) t += part[g][cl];
+    out[c] = accumulate ? out[c] + t : t;
+  }
+}
+int rows_sum(const float* rows, int n_rows, int ncols, float* out, int accumulate, cudaStream_t stream) {
+  rows_sum_kernel<<<ceil_div(ncols, 32), 256, 0, stream>>>(rows, n_rows, ncols, out, accumulate);
+  PDAC_LAUNCH_CHECK("rows_sum");
+  return PDAC_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ y = act(x*s + b + r)
@@ -200,10 +246,12 @@ __global__ void __launch_bounds__(256, XMASK ? 3 : 2) bn_bwd_reduce_kernel(Flat 
     float acc = 0.f;
     for (int q = 0; q < ppb; ++q) acc += red[q * cg + gg][slot];
     const int c = gg * 8 + (slot & 7);
+    // this block's row of the [blocks][2][C] partial table (rows_sum adds the rows in a fixed order afterwards)
+    float* row = sums + (size_t)blockIdx.x * 2 * dy.C;
     if (slot < 8)
-      atomicAdd(sums + c, acc);
-    else if (x.ptr)
-      atomicAdd(sums + dy.C + c, acc * (mi ? mi[dy.C + c] : 1.f));
+      row[c] = acc;
+    else
+      row[dy.C + c] = x.ptr ? acc * (mi ? mi[dy.C + c] : 1.f) : 0.f;
   }
 }
 
@@ -287,8 +335,8 @@ __global__ void __launch_bounds__(256, XMASK ? 3 : 2) bn_bwd_apply_kernel(Flat d
 }
 
 // dz = dy * (y > 0); dbias[c] += sum dz  (conv+bias+ReLU layers without BatchNorm: models/resunet.py:36-46)
-__global__ void __launch_bounds__(256) relu_bwd_bias_kernel(Flat dy, Flat y, Flat dz, float* __restrict__ dbias, int cg,
-                                                            int ppb) {
+__global__ void __launch_bounds__(256) relu_bwd_bias_kernel(Flat dy, Flat y, Flat dz, float* __restrict__ dbias,
+                                                            float* __restrict__ rows, int cg, int ppb) {
   __shared__ float red[256][9];
   EW_SETUP(cg, ppb)
   float s0[8];
@@ -315,7 +363,10 @@ __global__ void __launch_bounds__(256) relu_bwd_bias_kernel(Flat dy, Flat y, Fla
     const int gg = t / 8, slot = t % 8;
     float acc = 0.f;
     for (int q = 0; q < ppb; ++q) acc += red[q * cg + gg][slot];
-    atomicAdd(dbias + gg * 8 + slot, acc);
+    if (rows)
+      rows[(size_t)blockIdx.x * dy.C + gg * 8 + slot] = acc;  // deterministic: fixed-order row sum afterwards
+    else
+      atomicAdd(dbias + gg * 8 + slot, acc);
   }
 }
 
@@ -323,17 +374,17 @@ __global__ void __launch_bounds__(256) relu_bwd_bias_kernel(Flat dy, Flat y, Fla
 
 using namespace pdac;
 
-extern "C" int pdac_bn_prepare(const float* stats, double count, const float* gamma, const float* beta, float eps,
-                               float momentum, int train, float* running_mean, float* running_var,
+extern "C" int pdac_bn_prepare(const float* stats, int n_rows, double count, const float* gamma, const float* beta,
+                               float eps, float momentum, int train, float* running_mean, float* running_var,
                                long long* num_batches_tracked, float* scale_shift, float* mean_invstd, int C,
                                void* stream) {
   PDAC_REQUIRE(scale_shift && C > 0, "bn_prepare: null/empty");
-  PDAC_REQUIRE(train ? (stats != nullptr) : (running_mean && running_var),
+  PDAC_REQUIRE(train ? (stats != nullptr && n_rows >= 1) : (running_mean && running_var),
                "bn_prepare: train needs stats, eval needs running stats");
   if (train) PDAC_REQUIRE(count > 1.0, "Expected more than 1 value per channel when training (count=%g)", count);
-  bn_prepare_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
-      stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, num_batches_tracked, scale_shift,
-      mean_invstd, C);
+  bn_prepare_kernel<<<ceil_div(C, 32), 256, 0, (cudaStream_t)stream>>>(
+      stats, n_rows, count, gamma, beta, eps, momentum, train, running_mean, running_var, num_batches_tracked,
+      scale_shift, mean_invstd, C);
   PDAC_LAUNCH_CHECK("bn_prepare");
   return PDAC_OK;
 }
@@ -363,18 +414,24 @@ extern "C" int pdac_bn_bwd_reduce(const PdacView* dy, const PdacView* y, const P
   if (x) PDAC_TRY(flatten(x, &fx, "x"));
   PDAC_REQUIRE(sums, "bn_bwd_reduce: null sums");
   PDAC_REQUIRE(fd.C <= 2048, "bn_bwd_reduce: too many channels");
+  // sums: [1 + PDAC_STAT_ROWS][2][C]; rows 1.. take the blocks' partials, row 0 the fixed-order total
+  float* rows = sums + 2 * (size_t)fd.C;
+  int blocks = 0;
   if (scale_shift && !y && x && mean_invstd) {
     static const int resident = resident_blocks(bn_bwd_reduce_kernel<true>);
-    const EwGrid g = ew_grid(fd.npix, fd.C, resident);
-    bn_bwd_reduce_kernel<true><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums,
+    const EwGrid g = ew_grid(fd.npix, fd.C, resident < PDAC_STAT_ROWS ? resident : PDAC_STAT_ROWS);
+    blocks = g.blocks;
+    bn_bwd_reduce_kernel<true><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, rows,
                                                                           g.cg, g.ppb);
   } else {
     static const int resident = resident_blocks(bn_bwd_reduce_kernel<false>);
-    const EwGrid g = ew_grid(fd.npix, fd.C, resident);
-    bn_bwd_reduce_kernel<false><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, sums,
+    const EwGrid g = ew_grid(fd.npix, fd.C, resident < PDAC_STAT_ROWS ? resident : PDAC_STAT_ROWS);
+    blocks = g.blocks;
+    bn_bwd_reduce_kernel<false><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fx, mean_invstd, scale_shift, rows,
                                                                            g.cg, g.ppb);
   }
   PDAC_LAUNCH_CHECK("bn_bwd_reduce");
+  PDAC_TRY(rows_sum(rows, blocks, 2 * fd.C, sums, 0, (cudaStream_t)stream));
   return PDAC_OK;
 }
 
@@ -409,14 +466,17 @@ extern "C" int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const Pd
 }
 
 extern "C" int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias,
-                                  void* stream) {
+                                  float* scratch, void* stream) {
   Flat fd, fy = {nullptr, 0, 0, 0}, fdz = {nullptr, 0, 0, 0};
   PDAC_TRY(flatten(dy, &fd, "dy"));
   if (y) PDAC_TRY(flatten(y, &fy, "y"));
   if (dz) PDAC_TRY(flatten(dz, &fdz, "dz"));
   static const int resident = resident_blocks(relu_bwd_bias_kernel);
-  const EwGrid g = ew_grid(fd.npix, fd.C, resident);
-  relu_bwd_bias_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fdz, dbias, g.cg, g.ppb);
+  const bool det = dbias && scratch;
+  const EwGrid g = ew_grid(fd.npix, fd.C, det && resident > PDAC_STAT_ROWS ? PDAC_STAT_ROWS : resident);
+  relu_bwd_bias_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fdz, dbias, det ? scratch : nullptr, g.cg,
+                                                                   g.ppb);
   PDAC_LAUNCH_CHECK("relu_bwd_bias");
+  if (det) PDAC_TRY(rows_sum(scratch, g.blocks, fd.C, dbias, 1, (cudaStream_t)stream));
   return PDAC_OK;
 }

@@ -29,15 +29,33 @@ static thread_local int g_last_kernel = 0;
 void note_kernel(int id) { g_last_kernel = id; }
 int last_kernel() { return g_last_kernel; }
 
-__device__ int g_pipeline_err_flag = 0;
+// Pipeline error flag: one int per device in mapped pinned host memory. A kernel whose mbarrier wait times out stores 1
+// through the device alias; the host reads its own alias without synchronising (pdac_peek_device_flag).
+static const int kMaxDevices = 64;
+static int* g_flag_host[kMaxDevices] = {};
+static int* g_flag_dev[kMaxDevices] = {};
+
+static int flag_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return -1;
+  if (!g_flag_dev[dev]) {
+    int* h = nullptr;
+    void* d = nullptr;
+    if (cudaHostAlloc((void**)&h, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) return -1;
+    *h = 0;
+    if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) {
+      cudaFreeHost(h);
+      return -1;
+    }
+    g_flag_host[dev] = h;
+    g_flag_dev[dev] = (int*)d;
+  }
+  return dev;
+}
 
 int* device_err_flag() {
-  static int* p = nullptr;
-  if (!p) {
-    void* q = nullptr;
-    if (cudaGetSymbolAddress(&q, g_pipeline_err_flag) == cudaSuccess) p = (int*)q;
-  }
-  return p;
+  const int dev = flag_slot();
+  return dev < 0 ? nullptr : g_flag_dev[dev];
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -117,14 +135,19 @@ int pdac_last_kernel_id(void) { return pdac::last_kernel(); }
 int pdac_check_device_flag(void* stream) {
   using namespace pdac;
   PDAC_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-  int* p = device_err_flag();
-  if (!p) return fail(PDAC_E_NODEVICE, "no device symbol for the pipeline error flag");
-  int h = 0;
-  PDAC_CUDA(cudaMemcpy(&h, p, sizeof(int), cudaMemcpyDeviceToHost));
-  if (h) {
-    int z = 0;
-    PDAC_CUDA(cudaMemcpy(p, &z, sizeof(int), cudaMemcpyHostToDevice));
-    return fail(PDAC_E_TIMEOUT, "a tcgen05/TMA pipeline barrier timed out on the device (flag=%d)", h);
+  return pdac_peek_device_flag();
+}
+
+int pdac_peek_device_flag(void) {
+  using namespace pdac;
+  const int dev = flag_slot();
+  if (dev < 0) return fail(PDAC_E_NODEVICE, "no pipeline error flag (no CUDA device?)");
+  volatile int* h = g_flag_host[dev];
+  const int v = *h;
+  if (v) {
+    *h = 0;
+    return fail(PDAC_E_TIMEOUT, "a tcgen05/TMA pipeline barrier timed out on device %d (flag=%d): results of the "
+                                "kernels launched since the last check are invalid", dev, v);
   }
   return PDAC_OK;
 }

@@ -40,7 +40,7 @@ int encode_tiled_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t
 // Tensor map over an NHWC bf16 view with box (ck, tw, th, tn).
 int encode_view_map(CUtensorMap* m, const PdacView* v, int ck, int tw, int th, int tn);
 
-int* device_err_flag();  // device pointer to the pipeline error flag
+int* device_err_flag();  // device alias of the current device's pipeline error flag (mapped pinned host memory)
 
 // Which convolution kernel the last pdac_conv* / pdac_tapconv* call of this thread dispatched to (bench attribution).
 enum { KID_NONE = 0, KID_CONV_TC = 1, KID_CONV_HALO = 2, KID_WGRAD_TC = 3, KID_WGRAD_HALO = 4 };
@@ -50,6 +50,16 @@ void note_kernel(int id);
 // eval-mode BatchNorm folded into the GEMM epilogue as y = act(acc * scale + shift + addend)).
 void set_epi_scale(const float* scale);
 const float* epi_scale();
+
+// Deterministic cross-block reductions (no floating-point atomics): out[c] (+)= sum over rows 0..n_rows-1 of
+// rows[r][c], added in a fixed order (bn.cu).
+int rows_sum(const float* rows, int n_rows, int ncols, float* out, int accumulate, cudaStream_t stream);
+// Deterministic split-K of the weight-gradient kernels (conv_tc.cu): partial tensors in a caller scratch buffer, added
+// in share order.
+int wgrad_plan_partials(float* scratch, long long scratch_bytes, int n_taps, int A, int B, int* splits, float** part,
+                        long long* part_stride);
+int wgrad_reduce(const float* part, int splits, long long part_stride, int n_taps, int B, int A, float* dw,
+                 long long tap_stride, long long a_stride, long long b_stride, void* stream);
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int pow2_ceil(int x) {
@@ -63,14 +73,15 @@ inline int ilog2(int x) {
   return l;
 }
 inline int num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
+  static int n[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!n[dev]) {
+    cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (n[dev] <= 0) n[dev] = 148;
   }
-  return n;
+  return n[dev];
 }
 
 }  // namespace pdac

@@ -132,7 +132,6 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
   __shared__ long long s_rowoff[4][128];
-  __shared__ float s_stats[256];  // per-CTA BatchNorm partial sums: [0..127] sum, [128..255] sum of squares
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -171,7 +170,6 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
     }
     fence_barrier_init();
   }
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + 256) s_stats[threadIdx.x - 64] = 0.f;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.a[0]);
     tma_prefetch_desc(&maps.w);
@@ -578,9 +576,13 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
       PROF_PUT(6, w_tf);
     }
 #endif
-    // BatchNorm partial sums: lanes sharing a channel column -> one lane per column -> shared -> (after the final
-    // CTA barrier) one global atomic per channel and CTA
+    // BatchNorm partial sums, in a FIXED order (bit-reproducible statistics; the reference trains with
+    // cudnn.deterministic, train_main.py:40): lanes sharing a channel column -> one lane per column -> this warp's
+    // slot in the (now idle) staging area -> after the final CTA barrier one thread per channel adds the warps'
+    // slots in index order and stores the CTA's row of the [rows][2][Cout] partial table (no atomics anywhere).
     if (p.stats && vec) {
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // the last tile's staging has been consumed
+      float* wslot = reinterpret_cast<float*>(smem_stg + (size_t)wg * 128 * spitch) + q * 256;
 #pragma unroll
       for (int pass = 0; pass < NPASS; ++pass) {
         const int c0 = pass * 64;
@@ -598,8 +600,8 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
             for (int i = 0; i < 8; ++i) {
               const int chn = c0 + lane * 8 + i;
               if (chn < nch) {
-                atomicAdd(&s_stats[chn], acc[pass][i]);
-                atomicAdd(&s_stats[128 + chn], acc[pass][8 + i]);
+                wslot[chn] = acc[pass][i];
+                wslot[128 + chn] = acc[pass][8 + i];
               }
             }
           }
@@ -612,7 +614,15 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
   __syncthreads();
   if (p.stats && (int)threadIdx.x < 2 * p.block_n) {
     const int which = threadIdx.x >= p.block_n, chn = threadIdx.x - which * p.block_n;
-    if (chn < min(p.block_n, p.Cout - n0)) atomicAdd(p.stats + which * p.Cout + n0 + chn, s_stats[which * 128 + chn]);
+    if (chn < min(p.block_n, p.Cout - n0)) {
+      const int sc = p.block_n < 64 ? p.block_n : 64;
+      const int spitch = sc * 2 + 16;
+      float v = 0.f;
+      for (int w = 0; w < p.n_wg; ++w)
+        for (int qq = 0; qq < 4; ++qq)
+          v += reinterpret_cast<const float*>(smem_stg + (size_t)w * 128 * spitch)[qq * 256 + which * 128 + chn];
+      p.stats[((size_t)sp0 * 2 + which) * p.Cout + n0 + chn] = v;  // row sp0 belongs to this CTA column alone
+    }
   }
   if (warp == 1) {
     tc_fence_after();
@@ -882,6 +892,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   int per_n = (dual ? 2 : 1) * num_sms() / p.tiles_c;
   if (per_n < 1) per_n = 1;
   if (per_n > p.tiles_sp) per_n = p.tiles_sp;
+  PDAC_REQUIRE(!stats || per_n <= PDAC_STAT_ROWS, "internal: %d statistics rows exceed PDAC_STAT_ROWS", per_n);
   typedef void (*HaloKernel)(const HaloMaps, const HaloParams);
 #define HALO_ROW(n, aff)                                                                                       \
   {                                                                                                             \

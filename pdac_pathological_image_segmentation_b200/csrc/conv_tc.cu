@@ -205,6 +205,30 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
     const bool stat_thread = p.stats && sg < groups && pairs <= 128;
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
     int stat_n0 = -1;
+    // Deterministic flush of the channel-pair partials of N tile `fn0` (called by all 128 threads of the warpgroup):
+    // partials -> staging -> thread `pr` adds the `groups` row-groups in index order into this warpgroup's own row of
+    // the [rows][2][Cout] table (row = CTA * 2 + warpgroup: a single writer per element, so plain adds).
+    auto flush_stats = [&](int fn0) {
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // staging no longer read by the write-out
+      float4* slot = reinterpret_cast<float4*>(stg);
+      if (stat_thread) slot[sg * pairs + pr] = make_float4(s0, s1, q0, q1);
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+      if (e < pairs && pairs <= 128 && 2 * e < min(p.block_n, p.Cout - fn0)) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int g = 0; g < groups; ++g) {
+          const float4 v = slot[g * pairs + e];
+          t.x += v.x;
+          t.y += v.y;
+          t.z += v.z;
+          t.w += v.w;
+        }
+        float* st = p.stats + (size_t)(blockIdx.x * kEpiWG + wg) * 2 * p.Cout + fn0 + 2 * e;
+        st[0] += t.x;
+        st[1] += t.y;
+        st[p.Cout] += t.z;
+        st[p.Cout + 1] += t.w;
+      }
+    };
 
     int lt = 0;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++lt) {
@@ -215,14 +239,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
       const long long ooff = (long long)img * p.osN + (long long)h * p.osH + (long long)w * p.osW;
       const long long aoff = (long long)img * p.asN + (long long)h * p.asH + (long long)w * p.asW;
       const int nch = min(p.block_n, p.Cout - n0);  // valid channels of this N tile
-      if (stat_thread && stat_n0 != n0) {
-        if (stat_n0 >= 0 && 2 * pr < min(p.block_n, p.Cout - stat_n0)) {
-          float* st = p.stats + stat_n0 + 2 * pr;
-          atomicAdd(st, s0);
-          atomicAdd(st + 1, s1);
-          atomicAdd(st + p.Cout, q0);
-          atomicAdd(st + p.Cout + 1, q1);
-        }
+      if (p.stats && stat_n0 != n0) {  // uniform over the warpgroup
+        if (stat_n0 >= 0) flush_stats(stat_n0);
         s0 = s1 = q0 = q1 = 0.f;
         stat_n0 = n0;
       }
@@ -324,13 +342,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const __grid_const
         }
       }
     }
-    if (stat_thread && stat_n0 >= 0 && 2 * pr < min(p.block_n, p.Cout - stat_n0)) {
-      float* st = p.stats + stat_n0 + 2 * pr;
-      atomicAdd(st, s0);
-      atomicAdd(st + 1, s1);
-      atomicAdd(st + p.Cout, q0);
-      atomicAdd(st + p.Cout + 1, q1);
-    }
+    if (p.stats && stat_n0 >= 0) flush_stats(stat_n0);
   }
 #undef DECODE_TILE
 
@@ -358,6 +370,9 @@ struct WgradKParams {
   float* dw;
   long long tap_stride, a_stride, b_stride;
   int Cout;
+  float* part;  // deterministic mode, see WhParams in wgrad_halo.cu
+  long long part_stride;
+  int part_A;
   int* err;
 };
 
@@ -511,14 +526,23 @@ __global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_co
           a_ch = koff + c * p.ck + within;
         }
         float* base = p.dw + (long long)t * p.tap_stride + (long long)a_ch * p.a_stride + (long long)n0 * p.b_stride;
+        float* pbase = p.part ? p.part + (long long)blockIdx.x * p.part_stride +
+                                    ((long long)t * p.Cout + n0) * p.part_A + a_ch
+                              : nullptr;
         for (int c = 0; c < p.block_n; c += 16) {
           uint32_t v[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * p.block_n + c), v);
           tmem_ld_wait();
           if (rvalid) {
+            if (pbase) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (c + i < nch) atomicAdd(base + (long long)(c + i) * p.b_stride, __uint_as_float(v[i]));
+              for (int i = 0; i < 16; ++i)
+                if (c + i < nch) pbase[(long long)(c + i) * p.part_A] = __uint_as_float(v[i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (c + i < nch) atomicAdd(base + (long long)(c + i) * p.b_stride, __uint_as_float(v[i]));
+            }
           }
         }
       }
@@ -582,7 +606,53 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
                   const PdacView* addend, const PdacView* out, float* stats, void* stream, int* handled);
 
 int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy, float* dw,
-                   int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, void* stream, int* handled);
+                   int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, float* scratch,
+                   long long scratch_bytes, void* stream, int* handled);
+
+// Deterministic split-K: with a scratch buffer the split-K shares are stored as partial tensors [share][tap][B][A]
+// (A = concatenated input channels, fastest) and added in share order by wgrad_reduce_kernel. The number of shares is
+// capped by the scratch size; a single share still goes through the scratch (dw is accumulated into, not overwritten).
+int wgrad_plan_partials(float* scratch, long long scratch_bytes, int n_taps, int A, int B, int* splits, float** part,
+                        long long* part_stride) {
+  *part = nullptr;
+  *part_stride = 0;
+  if (!scratch) return PDAC_OK;
+  PDAC_REQUIRE(((uintptr_t)scratch & 15) == 0, "wgrad scratch must be 16-byte aligned");
+  const long long per = (((long long)n_taps * A * B + 3) / 4) * 4;
+  const long long fit = scratch_bytes / (per * (long long)sizeof(float));
+  PDAC_REQUIRE(fit >= 1, "wgrad scratch too small: %lld bytes given, %lld needed per split-K share", scratch_bytes,
+               per * (long long)sizeof(float));
+  if (*splits > fit) *splits = (int)fit;
+  *part = scratch;
+  *part_stride = per;
+  return PDAC_OK;
+}
+
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ part, int splits,
+                                                           long long part_stride, int B, int A, long long total,
+                                                           float* __restrict__ dw, long long tap_stride,
+                                                           long long a_stride, long long b_stride) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += part[(long long)s * part_stride + i];
+    const int a = (int)(i % A);
+    const long long r = i / A;
+    const int b = (int)(r % B);
+    const long long t = r / B;
+    dw[t * tap_stride + (long long)a * a_stride + (long long)b * b_stride] += acc;
+  }
+}
+
+int wgrad_reduce(const float* part, int splits, long long part_stride, int n_taps, int B, int A, float* dw,
+                 long long tap_stride, long long a_stride, long long b_stride, void* stream) {
+  const long long total = (long long)n_taps * B * A;
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
+  wgrad_reduce_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(part, splits, part_stride, B, A, total, dw,
+                                                                    tap_stride, a_stride, b_stride);
+  PDAC_LAUNCH_CHECK("wgrad_reduce_kernel");
+  return PDAC_OK;
+}
 
 static int check_dev_ptr(const void* p, const char* what) {
   cudaPointerAttributes at;
@@ -687,6 +757,7 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
   }
   int ctas = num_sms();
   if (ctas > p.total_tiles) ctas = p.total_tiles;
+  if (stats && ctas * kEpiWG > PDAC_STAT_ROWS) ctas = PDAC_STAT_ROWS / kEpiWG;
   conv_tc_kernel<<<ctas, kThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("conv_tc_kernel");
   note_kernel(KID_CONV_TC);
@@ -695,7 +766,7 @@ extern "C" int pdac_tapconv_fwd(const PdacTapConv* tc, int n_views, const PdacVi
 
 extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy,
                                   float* dw, int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid,
-                                  void* stream) {
+                                  float* scratch, long long scratch_bytes, void* stream) {
   PDAC_REQUIRE(tc && views && dy && dw, "null argument");
   PDAC_REQUIRE(b_valid >= 0 && b_valid <= dy->C, "b_valid=%d out of range (dY has %d channels)", b_valid, dy->C);
   PDAC_TRY(check_dev_ptr(dw, "dw"));
@@ -706,7 +777,8 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
   {
     // stride-1 multi-tap weight gradients with <= 128 output channels take the halo-tile kernel (wgrad_halo.cu)
     int handled = 0;
-    PDAC_TRY(wgrad_halo_try(tc, n_views, views, dy, dw, tap_stride, a_stride, b_stride, b_valid, stream, &handled));
+    PDAC_TRY(wgrad_halo_try(tc, n_views, views, dy, dw, tap_stride, a_stride, b_stride, b_valid, scratch,
+                            scratch_bytes, stream, &handled));
     if (handled) return PDAC_OK;
   }
   const PdacView* v0 = views + tc->taps[0].src;
@@ -764,6 +836,9 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
   int splits = (2 * num_sms()) / (y * z);
   if (splits < 1) splits = 1;
   if (splits > p.n_kblocks) splits = p.n_kblocks;
+  const int a_total = p.chunks_total * ck;
+  PDAC_TRY(wgrad_plan_partials(scratch, scratch_bytes, p.n_taps, a_total, p.Cout, &splits, &p.part, &p.part_stride));
+  p.part_A = a_total;
   size_t smem = (size_t)stages_a * 32 * 1024 + 2 * (size_t)b_tile + 1024;
   static bool attr_set = false;
   if (!attr_set) {
@@ -773,6 +848,9 @@ extern "C" int pdac_tapconv_wgrad(const PdacTapConv* tc, int n_views, const Pdac
   dim3 grid(splits, y, z);
   wgrad_tc_kernel<<<grid, kWgradThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_tc_kernel");
+  if (p.part)
+    PDAC_TRY(wgrad_reduce(p.part, splits, p.part_stride, p.n_taps, p.Cout, a_total, dw, tap_stride, a_stride, b_stride,
+                          stream));
   note_kernel(KID_WGRAD_TC);
   return PDAC_OK;
 }
@@ -892,7 +970,7 @@ extern "C" int pdac_tapconv_fwd_affine(const PdacTapConv* tc, int n_views, const
 }
 
 extern "C" int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,
-                                 int dw_layout, void* stream) {
+                                 int dw_layout, float* scratch, long long scratch_bytes, void* stream) {
   PDAC_REQUIRE(cv && src && dy && dw, "null argument");
   PdacTapConv tc;
   PdacView views[4];
@@ -902,8 +980,9 @@ extern "C" int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* 
   const int cv_valid = cv->cout_valid > 0 ? cv->cout_valid : dy->C;
   if (dw_layout == 1)  // nn.Conv2d state_dict layout [Cout][Ctot][R][S]
     return pdac_tapconv_wgrad(&tc, nv, views, dy, dw, 1, (int64_t)cv->R * cv->S, (int64_t)ctot * cv->R * cv->S,
-                              cv_valid, stream);
-  return pdac_tapconv_wgrad(&tc, nv, views, dy, dw, (int64_t)dy->C * ctot, 1, ctot, cv_valid, stream);
+                              cv_valid, scratch, scratch_bytes, stream);
+  return pdac_tapconv_wgrad(&tc, nv, views, dy, dw, (int64_t)dy->C * ctot, 1, ctot, cv_valid, scratch, scratch_bytes,
+                            stream);
 }
 
 extern "C" int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const void* w_packed_t,
@@ -1014,7 +1093,8 @@ extern "C" int pdac_convt2x2_dgrad(const PdacView* dy, const void* w_packed_t, i
   return pdac_tapconv_fwd(&tc, 4, views, w_packed_t, nullptr, nullptr, dx, nullptr, stream);
 }
 
-extern "C" int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, int dw_layout, void* stream) {
+extern "C" int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float* dw, int dw_layout, float* scratch,
+                                   long long scratch_bytes, void* stream) {
   PDAC_REQUIRE(x && dy && dw, "null argument");
   // dW[a,b][cout][cin] = sum_{i,j} dy[2i+a, 2j+b, cout] * x[i, j, cin]: tapped operand = dy parity views, fixed = x.
   PdacTapConv tc;
@@ -1028,6 +1108,6 @@ extern "C" int pdac_convt2x2_wgrad(const PdacView* x, const PdacView* dy, float*
       tc.taps[a * 2 + b].src = a * 2 + b;
     }
   if (dw_layout == 1)  // nn.ConvTranspose2d state_dict layout [Cin][Cout][2][2]
-    return pdac_tapconv_wgrad(&tc, 4, views, x, dw, 1, 4, (int64_t)dy->C * 4, 0, stream);
-  return pdac_tapconv_wgrad(&tc, 4, views, x, dw, (int64_t)dy->C * x->C, x->C, 1, 0, stream);
+    return pdac_tapconv_wgrad(&tc, 4, views, x, dw, 1, 4, (int64_t)dy->C * 4, 0, scratch, scratch_bytes, stream);
+  return pdac_tapconv_wgrad(&tc, 4, views, x, dw, (int64_t)dy->C * x->C, x->C, 1, 0, scratch, scratch_bytes, stream);
 }

@@ -57,16 +57,29 @@ __global__ void __launch_bounds__(256) dice_fwd_kernel(const float* __restrict__
   I = block_sum_d(I, sh);
   P = block_sum_d(P, sh);
   Tt = block_sum_d(Tt, sh);
-  if (threadIdx.x == 0) {
-    atomicAdd(sums, I);
-    atomicAdd(sums + 1, P);
-    atomicAdd(sums + 2, Tt);
+  if (threadIdx.x == 0) {  // this block's row of the partial table sums[3 + 3 * block]
+    double* row = sums + 3 + 3 * (long long)blockIdx.x;
+    row[0] = I;
+    row[1] = P;
+    row[2] = Tt;
   }
 }
-__global__ void dice_finalize_kernel(const double* __restrict__ sums, float smooth, float* __restrict__ loss) {
-  const float I = (float)sums[0], P = (float)sums[1], T = (float)sums[2];
-  const float dice = (2.0f * I + smooth) / (P + T + smooth);
-  *loss = 1.0f - dice;
+// One warp adds the block rows in a fixed order (lane-strided, then a fixed shuffle tree): the loss and the sums the
+// backward pass reads are bit-reproducible (no floating-point atomics).
+__global__ void dice_finalize_kernel(double* __restrict__ sums, int n_rows, float smooth, float* __restrict__ loss) {
+  double a[3] = {0.0, 0.0, 0.0};
+  for (int r = threadIdx.x; r < n_rows; r += 32)
+    for (int k = 0; k < 3; ++k) a[k] += sums[3 + 3 * (long long)r + k];
+  for (int k = 0; k < 3; ++k)
+    for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+  if (threadIdx.x == 0) {
+    sums[0] = a[0];
+    sums[1] = a[1];
+    sums[2] = a[2];
+    const float I = (float)a[0], P = (float)a[1], T = (float)a[2];
+    const float dice = (2.0f * I + smooth) / (P + T + smooth);
+    *loss = 1.0f - dice;
+  }
 }
 // dL/dx = -gout * [2 t D - (2I + s)] / D^2 * p (1 - p),  D = P + T + s
 template <typename T>
@@ -253,15 +266,17 @@ using namespace pdac;
 extern "C" int pdac_dice_fwd(const float* logits, const void* targets, int tgt_dtype, long long n, double* sums,
                              float smooth, float* loss, void* stream) {
   PDAC_REQUIRE(logits && targets && sums && loss && n >= 0, "dice_fwd: null argument");
-  PDAC_CUDA(cudaMemsetAsync(sums, 0, 3 * sizeof(double), (cudaStream_t)stream));
+  int blocks = 0;
   if (n > 0) {
+    blocks = rblocks(n);
+    if (blocks > PDAC_STAT_ROWS) blocks = PDAC_STAT_ROWS;
     if (tgt_dtype == 0)
-      dice_fwd_kernel<float><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const float*)targets, n, sums);
+      dice_fwd_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>(logits, (const float*)targets, n, sums);
     else
-      dice_fwd_kernel<uint8_t><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const uint8_t*)targets, n, sums);
+      dice_fwd_kernel<uint8_t><<<blocks, 256, 0, (cudaStream_t)stream>>>(logits, (const uint8_t*)targets, n, sums);
     PDAC_LAUNCH_CHECK("dice_fwd");
   }
-  dice_finalize_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sums, smooth, loss);
+  dice_finalize_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(sums, blocks, smooth, loss);
   PDAC_LAUNCH_CHECK("dice_finalize");
   return PDAC_OK;
 }

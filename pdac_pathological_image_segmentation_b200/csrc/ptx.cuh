@@ -40,13 +40,16 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity
       : "memory");
   return ok;
 }
-// Bounded wait: a lost arrive must never hang the GPU box. On timeout the error flag is raised and
-// the caller proceeds (results are garbage, the host reports PDAC_E_TIMEOUT after the launch).
+// Bounded wait: a lost arrive must never hang the GPU box. On timeout the error flag is raised and the caller
+// proceeds (results are garbage); the host polls the flag once per step / batch and raises PDAC_E_TIMEOUT.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int* err_flag) {
   for (uint32_t it = 0; it < (1u << 22); ++it) {
     if (mbar_try_wait(bar, parity)) return;
   }
-  if (err_flag) atomicExch(err_flag, 1);
+  if (err_flag) {
+    *reinterpret_cast<volatile int*>(err_flag) = 1;  // mapped host memory: visible to pdac_peek_device_flag()
+    __threadfence_system();
+  }
 }
 
 // ---------------------------------------------------------------- TMA

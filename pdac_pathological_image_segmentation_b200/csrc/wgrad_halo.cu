@@ -53,6 +53,11 @@ struct WhParams {
   float* dw;
   long long tap_stride, a_stride, b_stride;
   int Cout;
+  // deterministic mode: split-K share blockIdx.x stores its partial [tap][Cout][A] at part + blockIdx.x * part_stride
+  // (plain coalesced stores; wgrad_reduce adds the shares in index order) instead of fp32 atomics into dw
+  float* part;
+  long long part_stride;
+  int part_A;
   int* err;
 };
 
@@ -201,14 +206,23 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
         const int a_ch = p.slabs[s].sub_c[sub] * p.ck + within;
         float* base = p.dw + (long long)(rvalid ? t : 0) * p.tap_stride + (long long)a_ch * p.a_stride +
                       (long long)n0 * p.b_stride;
+        float* pbase = p.part ? p.part + (long long)blockIdx.x * p.part_stride +
+                                    ((long long)(rvalid ? t : 0) * p.Cout + n0) * p.part_A + a_ch
+                              : nullptr;
         for (int c = 0; c < p.block_n; c += 16) {
           uint32_t v[16];
           tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((s - slab0) * p.block_n + c), v);
           tmem_ld_wait();
           if (rvalid) {
+            if (pbase) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (c + i < nch) atomicAdd(base + (long long)(c + i) * p.b_stride, __uint_as_float(v[i]));
+              for (int i = 0; i < 16; ++i)
+                if (c + i < nch) pbase[(long long)(c + i) * p.part_A] = __uint_as_float(v[i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (c + i < nch) atomicAdd(base + (long long)(c + i) * p.b_stride, __uint_as_float(v[i]));
+            }
           }
         }
       }
@@ -231,7 +245,8 @@ namespace pdac {
 // Returns PDAC_OK with *handled = 1 when the halo kernel was launched, *handled = 0 when the geometry is not eligible
 // (the caller falls back to the generic kernel), or an error code.
 int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, const PdacView* dy, float* dw,
-                   int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, void* stream, int* handled) {
+                   int64_t tap_stride, int64_t a_stride, int64_t b_stride, int b_valid, float* scratch,
+                   long long scratch_bytes, void* stream, int* handled) {
   *handled = 0;
   static int disabled = -1;
   if (disabled < 0) {
@@ -401,6 +416,9 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   int splits = (dual ? 2 : 1) * num_sms() / (ygroups * zgroups);
   if (splits < 1) splits = 1;
   if (splits > p.n_kblocks) splits = p.n_kblocks;
+  const int a_total = p.n_chunks * ck;
+  PDAC_TRY(wgrad_plan_partials(scratch, scratch_bytes, tc->n_taps, a_total, p.Cout, &splits, &p.part, &p.part_stride));
+  p.part_A = a_total;
   const size_t smem = (size_t)stages_a * a_stage + 2 * (size_t)b_tile + 1024;
   static bool attr_set = false;
   if (!attr_set) {
@@ -416,6 +434,9 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   else
     wgrad_halo_kernel<0><<<grid, kWhThreads, smem, (cudaStream_t)stream>>>(maps, p);
   PDAC_LAUNCH_CHECK("wgrad_halo_kernel");
+  if (p.part)
+    PDAC_TRY(wgrad_reduce(p.part, splits, p.part_stride, tc->n_taps, p.Cout, a_total, dw, tap_stride, a_stride, b_stride,
+                          stream));
   note_kernel(KID_WGRAD_HALO);
   *handled = 1;
   return PDAC_OK;

@@ -216,7 +216,7 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         st = _bn_prepare(tape, bn, None, 1, dev)
         return ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, relu=relu, bias=st.ss[1],
                               addend=residual, scale=st.ss[0], out=out)
-    stats = torch.zeros((2, m.cout), dtype=F32, device=dev) if tape.training else None
+    stats = ops.new_stats(m.cout, dev) if tape.training else None
     x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
     keep_x = tape.enabled
@@ -230,7 +230,7 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         dy = tape.pop(y)
         if dy is None:
             return
-        sums = torch.zeros((2, m.cout), dtype=F32, device=dev)
+        sums = ops.new_bwd_sums(m.cout, dev)
         # without a residual the ReLU mask is recomputed from x and the forward's scale / shift: y is not re-read
         ymask = y if (relu and residual is not None) else None
         ssm = st.ss if (relu and residual is None) else None
@@ -254,7 +254,7 @@ def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
     if not tape.training and not tape.enabled:
         st = _bn_prepare(tape, bn, None, 1, dev)
         return ops.stem_conv_fwd(z, wp, m.cout, scale=st.ss[0], shift=st.ss[1], relu=True)
-    stats = torch.zeros((2, m.cout), dtype=F32, device=dev) if tape.training else None
+    stats = ops.new_stats(m.cout, dev) if tape.training else None
     x = ops.stem_conv_fwd(z, wp, m.cout, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
     y = ops.scale_shift_act(x, st.ss, None, relu=True, out=None if tape.enabled else x)
@@ -264,7 +264,7 @@ def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
         dy = tape.pop(y)
         if dy is None:
             return
-        sums = torch.zeros((2, m.cout), dtype=F32, device=dev)
+        sums = ops.new_bwd_sums(m.cout, dev)
         ops.bn_bwd_reduce(dy, None, x, st.mi, sums, scale_shift=st.ss)
         ops.bn_bwd_apply(dy, None, x, st.mi, bn.weight.detach(), sums, st.count, training, dx=dy,
                          dgamma=tape.arena.slot(bn.weight), dbeta=tape.arena.slot(bn.bias), scale_shift=st.ss)

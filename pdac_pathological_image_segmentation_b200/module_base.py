@@ -76,6 +76,9 @@ class SegModule(nn.Module):
         if p.device != x.device:
             raise RuntimeError(f"module parameters are on {p.device} but the input is on {x.device}")
         _lib.load()
+        # non-blocking poll of the device pipeline error flag: anything a finished kernel reported since the last call
+        # (a timed-out TMA / tcgen05 barrier) raises here instead of flowing on into losses and optimizers
+        _lib.peek_device_flag()
 
     def forward(self, x):
         self._check_input(x)

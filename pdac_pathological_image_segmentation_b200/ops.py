@@ -7,6 +7,7 @@ Activations are NHWC bf16 tensors of shape (N, H, W, C) whose last stride is 1 (
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -14,6 +15,42 @@ from . import _lib
 from ._lib import PdacConv, PdacTapConv, PdacView, call
 
 BF16 = torch.bfloat16
+STAT_ROWS = _lib.PDAC_STAT_ROWS
+
+# Reproducible by default, as the reference requests (train_main.py:36-43 cudnn.deterministic = True): BatchNorm
+# statistics, BN / bias gradient sums, the Dice sums and the split-K weight gradients are all added in a fixed order.
+# PDAC_NONDETERMINISTIC=1 (or ops.deterministic = False) lets the weight / bias gradients use fp32 atomics instead.
+deterministic = os.environ.get("PDAC_NONDETERMINISTIC", "0") != "1"
+SCRATCH_BYTES = 64 << 20
+_scratch_cache = {}
+
+
+def scratch(device):
+    """The per-device fp32 scratch buffer of the deterministic reductions (partial split-K weight gradients, bias
+    partial rows). One buffer per device: its users are ordered by the stream they run on."""
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    t = _scratch_cache.get(key)
+    if t is None:
+        t = torch.empty(SCRATCH_BYTES // 4, dtype=torch.float32, device=device)
+        _scratch_cache[key] = t
+    return t
+
+
+def _scratch_args(device):
+    if not deterministic:
+        return None, 0
+    t = scratch(device)
+    return C.c_void_p(t.data_ptr()), t.numel() * 4
+
+
+def new_stats(c, device):
+    """Zeroed [STAT_ROWS, 2, c] table of the conv epilogues' BatchNorm partial sums (one row per CTA)."""
+    return torch.zeros((STAT_ROWS, 2, c), dtype=torch.float32, device=device)
+
+
+def new_bwd_sums(c, device):
+    """[1 + STAT_ROWS, 2, c] table of bn_bwd_reduce: row 0 = the totals, the rest = per-block partials."""
+    return torch.empty((1 + STAT_ROWS, 2, c), dtype=torch.float32, device=device)
 
 
 def _stream():
@@ -72,6 +109,12 @@ def conv_out_hw(h, w, R, S, stride, pad, dil):
     return ((h + 2 * pad - dil * (R - 1) - 1) // stride + 1, (w + 2 * pad - dil * (S - 1) - 1) // stride + 1)
 
 
+def _check_stats(stats, cout):
+    if stats is not None:
+        assert stats.dtype == torch.float32 and stats.is_contiguous() and tuple(stats.shape) == (STAT_ROWS, 2, cout), \
+            f"stats must be the zeroed [STAT_ROWS, 2, {cout}] table of ops.new_stats, got {tuple(stats.shape)}"
+
+
 def _act_bytes(*ts):
     return sum(t.numel() * t.element_size() for t in ts if t is not None)
 
@@ -86,6 +129,7 @@ def conv2d_fwd(srcs, wp, cout, R, S, stride=1, pad=0, dil=1, relu=False, bias=No
     ktot = sum(s.shape[3] for s in srcs)
     wrows = wp.shape[0] // (R * S)
     assert wp.dtype == BF16 and wp.is_contiguous() and wp.shape[1] == ktot, (wp.shape, ktot)
+    _check_stats(stats, out.shape[3])
     cv = _conv_struct(R, S, stride, pad, dil, relu, wrows)
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
     if scale is not None:        # out = act(acc * scale + bias + addend): eval-mode BatchNorm folded into the epilogue
@@ -125,7 +169,8 @@ def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None, oihw=False, c
         out = torch.zeros(shape, dtype=torch.float32, device=dy.device)
     cv = _conv_struct(R, S, stride, pad, dil, False, 0, cout_valid)
     views = (PdacView * len(srcs))(*[view(s) for s in srcs])
-    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), int(bool(oihw)), _stream(),
+    sp, sb = _scratch_args(dy.device)
+    call("pdac_conv2d_wgrad", C.byref(cv), len(srcs), views, _vp(dy), _ptr(out), int(bool(oihw)), sp, sb, _stream(),
          flops=2 * dy.shape[0] * dy.shape[1] * dy.shape[2] * (cout_valid or dy.shape[3]) * ktot * R * S,
          nbytes=_act_bytes(dy, *srcs),
          tag=f"wgrad {R}x{S}s{stride}d{dil} {dy.shape[0]}x{dy.shape[1]}x{dy.shape[2]} {ktot}->{dy.shape[3]}")
@@ -155,7 +200,8 @@ def convt2x2_wgrad(x, dy, out=None, iohw=False):
     if out is None:
         shape = (x.shape[3], dy.shape[3], 2, 2) if iohw else (4, dy.shape[3], x.shape[3])
         out = torch.zeros(shape, dtype=torch.float32, device=x.device)
-    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), int(bool(iohw)), _stream(),
+    sp, sb = _scratch_args(x.device)
+    call("pdac_convt2x2_wgrad", _vp(x), _vp(dy), _ptr(out), int(bool(iohw)), sp, sb, _stream(),
          flops=2 * dy.numel() * x.shape[3], nbytes=_act_bytes(x, dy))
     return out
 
@@ -173,6 +219,7 @@ def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=Non
     epilogue is act(acc * scale + bias + addend) (pdac_tapconv_fwd_affine; no statistics)."""
     tc = _tapconv(taps, n_cat, wp.shape[0] // len(taps), relu)
     vs = (PdacView * len(views))(*[view(v) for v in views])
+    _check_stats(stats, out.shape[3])
     if scale is not None:
         assert stats is None and bias is not None
         call("pdac_tapconv_fwd_affine", C.byref(tc), len(views), vs, _ptr(wp), _ptr(scale), _ptr(bias), _vp(addend),
@@ -186,8 +233,9 @@ def tapconv_fwd(views, taps, wp, out, n_cat=1, relu=False, bias=None, addend=Non
 def tapconv_wgrad(views, taps, dy, dw, tap_stride, a_stride, b_stride, n_cat=1, b_valid=0, flops=0):
     tc = _tapconv(taps, n_cat, 0, False)
     vs = (PdacView * len(views))(*[view(v) for v in views])
+    sp, sb = _scratch_args(dy.device)
     call("pdac_tapconv_wgrad", C.byref(tc), len(views), vs, _vp(dy), _ptr(dw), tap_stride, a_stride, b_stride, b_valid,
-         _stream(), flops=flops, nbytes=_act_bytes(dy, *views[:n_cat]))
+         sp, sb, _stream(), flops=flops, nbytes=_act_bytes(dy, *views[:n_cat]))
     return dw
 
 
@@ -317,8 +365,10 @@ def stem_prep_u8(img, mask=None, aug=None, mean=IMAGENET_MEAN, std=IMAGENET_STD,
 # ------------------------------------------------------------------------------------------------ BN / elementwise
 def bn_prepare(stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd,
                num_batches_tracked=None):
+    """stats: fp32 [rows, 2, C] partial sums (new_stats) or a plain [2, C] vector; None in eval mode."""
     c = scale_shift.shape[-1]
-    call("pdac_bn_prepare", _ptr(stats), float(count), _ptr(gamma), _ptr(beta), eps, momentum, int(bool(train)),
+    n_rows = 0 if stats is None else (stats.shape[0] if stats.dim() == 3 else 1)
+    call("pdac_bn_prepare", _ptr(stats), n_rows, float(count), _ptr(gamma), _ptr(beta), eps, momentum, int(bool(train)),
          _ptr(running_mean), _ptr(running_var), _ptr(num_batches_tracked), _ptr(scale_shift), _ptr(mean_invstd), c,
          _stream())
 
@@ -330,8 +380,12 @@ def scale_shift_act(x, scale_shift=None, residual=None, relu=False, out=None):
     return out
 
 
-def bn_bwd_reduce(dy, y, x, mean_invstd, sums, scale_shift=None):
-    """y: ReLU output for the mask, or None with scale_shift given to recompute the mask from x (y is not read)."""
+def bn_bwd_reduce(dy, y, x, mean_invstd, sums=None, scale_shift=None):
+    """y: ReLU output for the mask, or None with scale_shift given to recompute the mask from x (y is not read).
+    sums: new_bwd_sums table; sums[0] holds (sum dz, sum dz*xhat) afterwards."""
+    if sums is None:
+        sums = new_bwd_sums(dy.shape[3], dy.device)
+    assert sums.shape == (1 + STAT_ROWS, 2, dy.shape[3]) and sums.is_contiguous()
     call("pdac_bn_bwd_reduce", _vp(dy), _vp(y), _vp(x), _ptr(mean_invstd), _ptr(scale_shift), _ptr(sums), _stream())
     return sums
 
@@ -347,7 +401,12 @@ def bn_bwd_apply(dy, y, x, mean_invstd, gamma, sums, count, train, dx=None, dz_o
 
 
 def relu_bwd_bias(dy, y=None, dz=None, dbias=None):
-    call("pdac_relu_bwd_bias", _vp(dy), _vp(y), _vp(dz), _ptr(dbias), _stream())
+    sp = None
+    if dbias is not None and deterministic:
+        sc = scratch(dy.device)
+        assert STAT_ROWS * dy.shape[3] <= sc.numel()
+        sp = C.c_void_p(sc.data_ptr())
+    call("pdac_relu_bwd_bias", _vp(dy), _vp(y), _vp(dz), _ptr(dbias), sp, _stream())
     return dz
 
 
@@ -491,13 +550,13 @@ def _tgt(t):
 
 
 def dice_fwd(logits, targets, smooth=1e-6):
-    """-> (loss fp32 scalar tensor, sums fp64[3] saved for backward)."""
+    """-> (loss fp32 scalar tensor, sums fp64 (the first 3 entries are sum p*t, sum p, sum t) saved for backward)."""
     _need_cuda(logits, "logits")
     logits = logits.contiguous()
     assert logits.dtype == torch.float32
     t, kind = _tgt(targets)
     assert t.numel() == logits.numel(), "DiceLoss: inputs and targets must have the same number of elements"
-    sums = torch.empty(3, dtype=torch.float64, device=logits.device)
+    sums = torch.empty(3 * (1 + STAT_ROWS), dtype=torch.float64, device=logits.device)   # [0:3] totals + block rows
     loss = torch.empty((), dtype=torch.float32, device=logits.device)
     call("pdac_dice_fwd", _ptr(logits), _ptr(t), kind, logits.numel(), _ptr(sums), smooth, _ptr(loss), _stream())
     return loss, sums
@@ -579,4 +638,10 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.9
 
 
 def check_device_flag():
+    """Synchronises the current stream, then raises if a pipeline barrier timed out (tests)."""
     call("pdac_check_device_flag", _stream())
+
+
+def peek_device_flag():
+    """Non-blocking poll of the pipeline error flag (see _lib.peek_device_flag)."""
+    _lib.peek_device_flag()

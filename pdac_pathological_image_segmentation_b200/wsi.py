@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import torch
 
-from . import ops
+from . import _lib, ops
 from .engine import Tape
 
 
@@ -43,6 +43,7 @@ class SlideInference:
     @torch.no_grad()
     def run_batch(self, img_u8, rows, cols):
         """img_u8 (B, tile, tile, 3) uint8 on the device; rows / cols (B,) int32 grid coordinates. Returns the tile masks."""
+        _lib.peek_device_flag()          # non-blocking: raises if an earlier batch's kernels reported a pipeline time-out
         out = self.logits(img_u8)
         if out.shape[1] == 1:
             mask = ops.sigmoid_mask(out, as_uint8=True).view(out.shape[0], out.shape[2], out.shape[3])

@@ -16,7 +16,7 @@ for i in range(0, len(args), 4):
     xs = [torch.randn(B, hw, hw, c, device="cuda").to(torch.bfloat16) for c in cins]
     w = torch.randn(cout, cin, 3, 3, device="cuda") * 0.05
     wp, _ = ops.pack_conv_weight(w, want_dgrad=False, cout_pad=cout)
-    stats = torch.zeros(2, cout, device="cuda")
+    stats = ops.new_stats(cout, torch.device("cuda"))
     out = ops.empty_act(B, hw, hw, cout, "cuda")
     for _ in range(3):
         ops.conv2d_fwd(xs, wp, cout, 3, 3, 1, 1, 1, stats=stats, out=out)

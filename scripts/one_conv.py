@@ -9,7 +9,7 @@ cins = [cin] if cin <= 512 else [cin // 2, cin // 2]
 xs = [torch.randn(B, hw, hw, c, device="cuda").to(torch.bfloat16) for c in cins]
 w = torch.randn(cout, cin, 3, 3, device="cuda") * 0.05
 wp, _ = ops.pack_conv_weight(w, want_dgrad=False, cout_pad=cout)
-stats = torch.zeros(2, cout, device="cuda")
+stats = ops.new_stats(cout, torch.device("cuda"))
 out = ops.empty_act(B, hw, hw, cout, "cuda")
 for _ in range(2):
     ops.conv2d_fwd(xs, wp, cout, 3, 3, 1, 1, 1, stats=stats, out=out)

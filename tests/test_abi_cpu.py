@@ -34,7 +34,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
     assert len(names) >= 40
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/pdac_b200.h but not exported by libpdac_b200.so"
-    bound = set(_lib.SIGNATURES) | {"pdac_version", "pdac_last_error", "pdac_last_kernel_id"}
+    bound = set(_lib.SIGNATURES) | {"pdac_version", "pdac_last_error", "pdac_last_kernel_id", "pdac_peek_device_flag"}
     assert bound == set(names), f"ctypes table and header disagree: {bound ^ set(names)}"
     assert lib.pdac_version() >= 100
 

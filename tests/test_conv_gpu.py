@@ -81,7 +81,7 @@ def test_conv_fwd(case):
         ref = ref.relu()
     cpad = ops.pad16(cout) if cout % 8 else cout
     wp, _ = ops.pack_conv_weight(w.float().contiguous(), want_dgrad=False, cout_pad=cpad)
-    stats = torch.zeros(2, cpad, device=DEV)
+    stats = ops.new_stats(cpad, DEV)
     bias_p = None
     if bias is not None:
         bias_p = torch.zeros(cpad, device=DEV)
@@ -95,6 +95,7 @@ def test_conv_fwd(case):
     o32 = out.float()[..., :cout]
     s_ref = o32.sum((0, 1, 2))
     q_ref = (o32 * o32).sum((0, 1, 2))
+    stats = stats.sum(0)
     assert torch.allclose(stats[0, :cout], s_ref, rtol=1e-3, atol=1e-2 * o32.abs().max().item() + 1e-3)
     assert torch.allclose(stats[1, :cout], q_ref, rtol=1e-3, atol=1e-3)
 

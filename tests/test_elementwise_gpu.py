@@ -71,7 +71,7 @@ def test_batchnorm_fwd_bwd(shape, train, residual):
         assert torch.allclose(rm, bn.running_mean, rtol=1e-4, atol=1e-5)
         assert torch.allclose(rv, bn.running_var, rtol=1e-4, atol=1e-5)
     # backward (mask from OUR y so both sides agree on the ReLU mask up to rounding at 0)
-    sums = torch.zeros(2, C, device=DEV)
+    sums = ops.new_bwd_sums(C, DEV)
     dyh = _nhwc(dy)
     ops.bn_bwd_reduce(dyh, y, xh, mi, sums)
     dgamma = torch.empty(C, device=DEV)
