@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--size", type=int, default=512)
     ap.add_argument("--cpu-batch", type=int, default=2, help="patches per CPU-baseline step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true",
+                    help="skip the short runs of the other BASELINE configurations that the default line records")
     ap.add_argument("--no-graph", action="store_true",
                     help="train: time the eager step instead of the CUDA-graph replay of forward + loss + backward")
     ap.add_argument("--workload", default="train", choices=["train", "wsi"],
@@ -64,15 +66,23 @@ def peaks():
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm / baseline
-def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None, model_name="unet"):
+REF_DIR = "/root/reference"       # exists in the build container only, never on the GPU box
+
+
+def _host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None, model_name="unet", want_state=False):
     """The reference's step (train_worker.py:68-80) on the host cores: oracle restatement of smp.Unet(resnet18) +
-    DiceLoss + Adam in stock torch fp32 (smp is absent from the reference tree, see oracle/smp_oracle.py)."""
+    DiceLoss + Adam in stock torch fp32 (smp is absent from the reference tree, see oracle/smp_oracle.py).
+    -> (patches/s, cores, steps done, seconds, first-step loss, initial state_dict or None)."""
     import torch
 
     from oracle import resunet_oracle as R
     from oracle import smp_oracle as S
     from oracle import util_oracle as U
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    cores = _host_cores()
     torch.set_num_threads(cores)
     torch.manual_seed(41)
     if model_name == "resunet":
@@ -91,31 +101,112 @@ def cpu_train_patches_per_s(batch, size, steps, warmup, budget_s=None, model_nam
                 sd.update({k: p for k, p in zip(self.keys, self.ps)})
                 return R.forward(sd, x, x.shape[-1], training=True)
         model = _ResUNetOracle().train()
+        state0 = None
     else:
         model = S.build({"unet": "unet_smp"}.get(model_name, model_name), classes=1).train()
+        state0 = {k: v.detach().clone() for k, v in model.state_dict().items()} if want_state else None
     opt = torch.optim.Adam(model.parameters(), lr=1e-4)
     img, mask = R.synthetic_batch(batch, size, seed=41)
     x = R.normalize(img)
     label = mask.unsqueeze(1)
+    first_loss = None
     for _ in range(warmup):
-        U.train_step(model, opt, x, label)
+        _, l, _ = U.train_step(model, opt, x, label)
+        first_loss = l.item() if first_loss is None else first_loss
     t0 = time.perf_counter()
     done = 0
     for _ in range(steps):
-        U.train_step(model, opt, x, label)
+        _, l, _ = U.train_step(model, opt, x, label)
+        first_loss = l.item() if first_loss is None else first_loss
         done += 1
         if budget_s is not None and time.perf_counter() - t0 > budget_s:
             break
     dt = time.perf_counter() - t0
-    return done * batch / dt, cores, done, dt
+    return done * batch / dt, cores, done, dt, first_loss, state0
+
+
+def cpu_config1_patches_per_s(steps=3, warmup=1, batch=4, size=512, budget_s=20.0):
+    """BASELINE.json configs[0] as BASELINE.md section 5 words it: the reference's OWN ResUNet (models/resunet.py:7-58,
+    ResNet18 encoder), num_classes = 2, fp32, fwd + DiceLoss (util.py:6-19) + bwd + Adam on the host cores, batch 4 of
+    synthetic 512 x 512 patches. When /root/reference is present (the build container) the reference's modules are
+    imported unmodified (kind "reference-import"; only the ImageNet download is bypassed, as oracle/make_golden.py
+    does); on the GPU box that tree does not exist and the oracle restatement pinned to it runs instead (kind "port")."""
+    import torch
+
+    from oracle import resunet_oracle as R
+    from oracle import util_oracle as U
+    cores = _host_cores()
+    torch.set_num_threads(cores)
+    img, mask = R.synthetic_batch(batch, size, seed=41)
+    x = R.normalize(img)
+    target = torch.stack([1 - mask, mask], 1).float()          # 2-class one-hot so DiceLoss's flatten shapes agree
+    state = R.make_state(2, seed=41)
+    kind = "port"
+    if os.path.isdir(os.path.join(REF_DIR, "models")):
+        try:
+            from oracle.make_golden import import_reference
+            ResUNet, DiceLoss, _ = import_reference()
+            model = ResUNet(num_classes=2, output_size=size)
+            model.load_state_dict(state, strict=True)
+            model.train()
+            crit = DiceLoss()
+            opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+
+            def step():
+                opt.zero_grad()
+                loss = crit(torch.squeeze(model(x)), target)
+                loss.backward()
+                opt.step()
+                return loss.item()
+            kind = "reference-import"
+        except Exception:
+            kind = "port"
+    if kind == "port":
+        sd = R.grad_state(state)
+        params = [v for v in sd.values() if v.requires_grad]
+        opt = torch.optim.Adam(params, lr=1e-4)
+
+        def step():
+            opt.zero_grad()
+            loss = U.dice_loss(torch.squeeze(R.forward(sd, x, size, training=True)), target)
+            loss.backward()
+            opt.step()
+            return loss.item()
+    first = None
+    for _ in range(warmup):
+        l = step()
+        first = l if first is None else first
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        step()
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": done * batch / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{done} steps x {batch} patches of {size}x{size} ({dt:.1f} s): ResUNet(num_classes=2) fp32 fwd + "
+                      f"DiceLoss + bwd + Adam on {cores} host threads", "first_loss": first}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, args.size, args.steps, min(args.warmup, 1),
-                                                 model_name=args.model)
+    if args.model == "resunet":        # configs[0]: the reference's own module when its tree is present
+        c1 = cpu_config1_patches_per_s(steps=args.steps, warmup=min(args.warmup, 1), batch=4, size=args.size, budget_s=120.0)
+        line = {"impl": "reference", "metric": f"{MODEL_NAMES['resunet']} {args.size}x{args.size} train patches/s",
+                "value": c1["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": min(args.warmup, 1), "ms_per_step": 4000.0 / c1["value"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "BASELINE configs[0]: ResUNet (models/resunet.py, ResNet18 encoder) fwd+bwd+Adam "
+                                       f"on CPU, {args.size}x{args.size} RGB patches, batch 4, 2 classes"},
+                "cpu_baseline": {k: c1[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": c1["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return
+    v, cores, done, dt, _, _ = cpu_train_patches_per_s(args.cpu_batch, args.size, args.steps, min(args.warmup, 1),
+                                                      model_name=args.model)
     sample = (f"{done} steps x {args.cpu_batch} patches of {args.size}x{args.size} on {cores} host threads "
               f"(oracle port of the reference step, torch fp32 CPU)")
     metric = METRIC if args.model == "unet" else f"{MODEL_NAMES[args.model]} {args.size}x{args.size} bf16 train patches/s"
@@ -175,12 +266,92 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ our arm
+def build_model(name, size):
+    from pdac_pathological_image_segmentation_b200 import smp as P
+    kw = dict(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None)
+    if name == "unet":
+        return P.Unet(**kw)
+    if name == "fpn":
+        return P.FPN(**kw)
+    if name == "pspnet":
+        return P.PSPNet(psp_use_batchnorm=True, **kw)
+    if name == "deeplabv3+":
+        return P.DeepLabV3Plus(decoder_atrous_rates=(3, 6, 9), **kw)
+    import warnings
+
+    from pdac_pathological_image_segmentation_b200.resunet import ResUNet
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        return ResUNet(num_classes=1, output_size=size)
+
+
+def quick_train(name, dev, batch, size, steps=5, warmup=4):
+    """Short device-resident run of the train step on another network (BASELINE configs[2..3], the reference's own
+    ResUNet): same harness, same timing rules, fewer steps. -> dict for the `other_configs` record."""
+    import torch
+
+    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
+    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
+    torch.manual_seed(41)
+    model = build_model(name, size).to(dev).train()
+    ts = TrainStep(model, lr=1e-4, graph=True)
+    img, mask = (t.to(dev) for t in synthetic_batch(batch, size, seed=41))
+    for _ in range(warmup):
+        loss, _ = ts.step(img, mask)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss, _ = ts.step(img, mask)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    out = {"metric": f"{MODEL_NAMES[name]} {size}x{size} bf16 train patches/s", "value": batch / (ms / 1000), "unit": UNIT,
+           "ms_per_step": ms, "batch": batch, "steps": steps, "warmup": warmup, "loss": loss.item(),
+           "launch": "CUDA graph" if ts._g is not None else "eager (active Dropout draws host seeds)",
+           "tc_fraction_of_step": TRAIN_GF[name] * 1e9 * batch / (ms / 1000) / (peaks()[0].get("bf16_tflops_sustained", 1400.0) * 1e12)}
+    del ts, model
+    torch.cuda.empty_cache()
+    return out
+
+
+def quick_wsi(dev, batch, size, steps=5, warmup=3):
+    """Short run of BASELINE configs[4] on this GPU's band (see run_wsi)."""
+    import torch
+
+    from pdac_pathological_image_segmentation_b200.wsi import SlideInference
+    torch.manual_seed(41)
+    model = build_model("unet", size).to(dev)
+    side = 200
+    inf = SlideInference(model, 8, side, tile=size)           # an 8-row band of the 200-column slide
+    g = torch.Generator().manual_seed(41)
+    tiles = torch.randint(0, 256, (batch, size, size, 3), dtype=torch.uint8, generator=g).to(dev)
+    t = torch.arange(batch, dtype=torch.int64)
+    rows, cols = (t // side).to(torch.int32).to(dev), (t % side).to(torch.int32).to(dev)
+    for _ in range(warmup):
+        inf.run_batch(tiles, rows, cols)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        inf.run_batch(tiles, rows, cols)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    out = {"metric": "smp Unet-ResNet18 512x512 bf16 WSI inference tiles/s (fwd + mask + stitch)",
+           "value": batch / (ms / 1000), "unit": "tiles/s", "ms_per_step": ms, "batch": batch, "steps": steps,
+           "warmup": warmup, "time_for_40k_tiles_s_on_8_gpus": 40000 / 8 / (batch / (ms / 1000))}
+    del inf, model
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
     from pdac_pathological_image_segmentation_b200 import _lib
-    from pdac_pathological_image_segmentation_b200 import smp as P
+    from pdac_pathological_image_segmentation_b200 import ops as ops_mod
     from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
     from pdac_pathological_image_segmentation_b200.trainer import TrainStep
 
@@ -197,23 +368,7 @@ def run_ours(args):
 
     B, S = args.batch, args.size
     torch.manual_seed(41)
-    kw = dict(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None)
-    if args.model == "unet":
-        model = P.Unet(**kw)
-    elif args.model == "fpn":
-        model = P.FPN(**kw)
-    elif args.model == "pspnet":
-        model = P.PSPNet(psp_use_batchnorm=True, **kw)
-    elif args.model == "deeplabv3+":
-        model = P.DeepLabV3Plus(decoder_atrous_rates=(3, 6, 9), **kw)
-    else:
-        import warnings
-
-        from pdac_pathological_image_segmentation_b200.resunet import ResUNet
-        with warnings.catch_warnings():
-            warnings.simplefilter("ignore")
-            model = ResUNet(num_classes=1, output_size=S)
-    model.to(dev).train()
+    model = build_model(args.model, S).to(dev).train()
     ts = TrainStep(model, lr=1e-4)
     ts.broadcast_parameters()
 
@@ -224,8 +379,6 @@ def run_ours(args):
         img, mask = synthetic_batch(B, S, seed=41 + rank * 100 + i)
         host.append((img.pin_memory(), mask.pin_memory()))
     dev_batches = [(i.to(dev), m.to(dev)) for i, m in host]
-    img_d = torch.empty_like(dev_batches[0][0])
-    mask_d = torch.empty_like(dev_batches[0][1])
 
     def sync_all():
         torch.cuda.synchronize()
@@ -279,18 +432,48 @@ def run_ours(args):
     value = world * B * args.steps / (ms / 1000)
 
     # ---- timed region 2: end to end through TrainStep with host buffers ---------------------------------------
+    # Every step copies its own batch from pinned host memory and its loss is read on the host. The copy of step i+1
+    # runs on a copy stream while step i computes (two device buffers), and the loss of step i is read after step i+1
+    # has been enqueued (the reference reads it right away, train_worker.py:83, and stalls the pipeline on it).
+    copy_stream = torch.cuda.Stream(device=dev)
+    bufs = [(torch.empty_like(dev_batches[0][0]), torch.empty_like(dev_batches[0][1])) for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    loss_host = torch.empty(args.steps, dtype=torch.float32).pin_memory()
+
+    def prefetch(i):
+        ih, mh = host[i % n_host]
+        b = i % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[b])          # the step that last read this buffer has finished with it
+            bufs[b][0].copy_(ih, non_blocking=True)
+            bufs[b][1].copy_(mh, non_blocking=True)
+            ready[b].record(copy_stream)
+
     sync_all()
+    for b in range(2):
+        consumed[b].record()
     w0 = time.perf_counter()
     e0.record()
+    prefetch(0)
     last = 0.0
+    cur = torch.cuda.current_stream(dev)
     for i in range(args.steps):
-        ih, mh = host[i % n_host]
-        img_d.copy_(ih, non_blocking=True)
-        mask_d.copy_(mh, non_blocking=True)
-        loss, score = ts.step(img_d, mask_d)
-        last = loss.item()                       # device -> host read of the step's result (train_worker.py:83)
+        b = i % 2
+        if i + 1 < args.steps:
+            prefetch(i + 1)
+        cur.wait_event(ready[b])
+        loss, score = ts.step(*bufs[b])
+        consumed[b].record(cur)
+        loss_host[i].copy_(loss, non_blocking=True)      # device -> host read of the step's result
+        loss_ev[b].record(cur)
+        if i > 0:
+            loss_ev[(i - 1) % 2].synchronize()           # the host runs one step ahead of the device, no further
+            last = float(loss_host[i - 1])
     e1.record()
     sync_all()
+    last = float(loss_host[args.steps - 1])
     ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - w0) * 1000)      # device span or host wall, the larger
     t = torch.tensor([ms_e2e], device=dev)
     if world > 1:
@@ -317,14 +500,16 @@ def run_ours(args):
     gms, gfl, gnb, gcalls = groups[dom]
     tc_peak = pk.get("bf16_tflops_sustained") or pk.get("bf16_tflops")
     achieved = gfl / (gms / 1000) / 1e12
-    traffic = None
-    try:        # dram bytes per launch of the dominant kernel from the committed ncu --set full capture, if any
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            traffic = json.load(f).get(dom, {}).get("dram_bytes_per_launch")
+    traffic = traffic_note = None
+    try:        # dram bytes per launch of the dominant kernel from the committed ncu --set full capture at THIS workload
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            tj = json.load(f).get(dom, {})
+        traffic, traffic_note = tj.get("dram_bytes_per_launch"), tj.get("note")
     except Exception:
         traffic = None
     roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": tc_peak, "unit": "TFLOP/s",
-                "frac": achieved / tc_peak, "traffic": traffic, "peak_source": f"{pk_src} bf16_tflops_sustained",
+                "frac": achieved / tc_peak, "traffic": traffic, "traffic_note": traffic_note,
+                "algorithmic_bytes_per_launch": gnb / max(gcalls, 1), "peak_source": f"{pk_src} bf16_tflops_sustained",
                 "calls_per_step": gcalls / args.steps, "ms_per_step_in_kernel": gms / args.steps,
                 "share_of_step": gms / ms_eager,
                 "measured_in": "eager pass of the same K steps, CUDA events around each conv C-ABI call"
@@ -338,18 +523,51 @@ def run_ours(args):
             "config": {"workload": f"{MODEL_NAMES[args.model]} train step (fwd + Dice loss + bwd + allreduce + Adam), "
                                    f"{S}x{S} RGB uint8 patches, 1 class, batch {B}/GPU",
                        "global_batch": B * world, "parallelism": f"dp{world}",
-                       "launch": "CUDA graph replay of forward + loss + backward; allreduce + Adam eager" if use_graph
-                                 else "eager", "ms_per_step_eager": ms_eager / args.steps,
+                       "launch": ("CUDA graph replay of the whole step (prep, forward, loss, backward, bucketed allreduce "
+                                  "overlapped on a side stream, Adam)" if ts._comm_in_graph else
+                                  "CUDA graph replay of prep + forward + loss + backward; allreduce + Adam eager")
+                                 if use_graph else "eager",
+                       "ms_per_step_eager": ms_eager / args.steps, "deterministic": bool(ops_mod.deterministic),
+                       "allreduce_overlap": bool(ts.overlap) if world > 1 else None,
                        "l2": "inputs and activations (GBs per step) far exceed the 126 MB L2; no explicit flush"},
             "tc_fraction_of_step": TRAIN_GF[args.model] * 1e9 * value / world / (tc_peak * 1e12) if S == 512 else None,
             "loss": last, "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "roofline": roofline}
     if not args.no_cpu_baseline and world == 1:
-        v, cores, done, dt = cpu_train_patches_per_s(args.cpu_batch, S, 1000, 1, budget_s=15.0, model_name=args.model)
+        v, cores, done, dt, cpu_loss, state0 = cpu_train_patches_per_s(args.cpu_batch, S, 1000, 1, budget_s=15.0,
+                                                                       model_name=args.model, want_state=True)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{done} steps x {args.cpu_batch} patches ({dt:.1f} s) of the same train step, "
                                           f"oracle torch fp32 on {cores} host threads"}
+        if state0 is not None:
+            # checker leg: our first-step loss on the CPU sample's batch and weights against the fp32 oracle's
+            from oracle.resunet_oracle import synthetic_batch as oracle_batch
+            chk = build_model(args.model, S)
+            chk.load_state_dict(state0, strict=True)
+            if hasattr(chk, "p_drop"):
+                chk.p_drop = 0.0
+            chk_ts = TrainStep(chk.to(dev).train(), lr=1e-4)
+            ci, cm = (t.to(dev) for t in oracle_batch(args.cpu_batch, S, seed=41))
+            ours_loss = chk_ts.step(ci, cm)[0].item()
+            line["loss_check"] = {"ours_bf16": ours_loss, "oracle_fp32_cpu": cpu_loss, "abs_err": abs(ours_loss - cpu_loss),
+                                  "tolerance": 5e-3, "batch": args.cpu_batch}
+            assert abs(ours_loss - cpu_loss) <= 5e-3, f"first-step loss {ours_loss} differs from the fp32 oracle's {cpu_loss}"
+            del chk_ts, chk
+        line["cpu_baseline_config1"] = cpu_config1_patches_per_s(steps=3, warmup=1)
+    if world == 1 and not args.no_other_configs and args.model == "unet":
+        # driver-side record of BASELINE configs[2..4] and the reference's own network: short runs of the same harness
+        others = {}
+        for name, b in (("fpn", 64), ("pspnet", 64), ("deeplabv3+", 64), ("resunet", 64)):
+            try:
+                others[name] = quick_train(name, dev, min(b, B), S)
+            except Exception as exc:      # never lose the headline line to a secondary configuration
+                others[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        try:
+            others["wsi"] = quick_wsi(dev, min(64, B), S)
+        except Exception as exc:
+            others["wsi"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        line["other_configs"] = others
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

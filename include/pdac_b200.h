@@ -257,6 +257,12 @@ int pdac_overlay_blend(const uint8_t* rgb, const uint8_t* mask, long long npix, 
 /* torch.optim.Adam semantics over one flat fp32 arena; grads are multiplied by grad_scale first. */
 int pdac_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                    float beta1, float beta2, float eps, int step, float grad_scale, void* stream);
+/* The same update with the step counter and the hyper-parameters in DEVICE memory, so that a whole train step replays
+ * from one CUDA graph and a scheduler changes the learning rate by writing hyper[0] (ReduceLROnPlateau at
+ * train_worker.py:240): *step += 1 first; hyper = float[8]: [0] lr, [1] beta1, [2] beta2, [3] eps, [4] grad_scale,
+ * [5..6] written by the library (lr / (1 - beta1^t), sqrt(1 - beta2^t), computed in double). */
+int pdac_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float* hyper,
+                       long long* step, void* stream);
 
 #ifdef __cplusplus
 }

@@ -88,6 +88,7 @@ SIGNATURES = {
     "pdac_stitch_tiles": [_p, _p, _p, _i, _i, _i, _p, _ll, _ll, _ll, _p],
     "pdac_overlay_blend": [_p, _p, _ll, _i, _i, _i, _i, _p, _p],
     "pdac_adam_step": [_p, _p, _p, _p, _ll, _f, _f, _f, _f, _i, _f, _p],
+    "pdac_adam_step_dev": [_p, _p, _p, _p, _ll, _p, _p, _p],
 }
 
 _lib = None

@@ -251,6 +251,31 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// Device-side step counter and hyper-parameters: the whole train step (incl. Adam) replays from one CUDA graph, and a
+// learning-rate scheduler changes lr by writing hyper[0]. hyper: [0] lr [1] beta1 [2] beta2 [3] eps [4] grad_scale
+// [5] (out) lr / (1 - beta1^t) [6] (out) sqrt(1 - beta2^t); bias corrections in double, as torch.optim.Adam has them.
+__global__ void adam_tick_kernel(float* __restrict__ hyper, long long* __restrict__ step) {
+  const long long t = *step + 1;
+  *step = t;
+  const double bc1 = 1.0 - pow((double)hyper[1], (double)t);
+  const double bc2 = 1.0 - pow((double)hyper[2], (double)t);
+  hyper[5] = (float)((double)hyper[0] / bc1);
+  hyper[6] = (float)sqrt(bc2);
+}
+__global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                       float* __restrict__ m, float* __restrict__ v, long long n,
+                                                       const float* __restrict__ hyper) {
+  const float b1 = hyper[1], b2 = hyper[2], eps = hyper[3], grad_scale = hyper[4], step = hyper[5], bc2_sqrt = hyper[6];
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i] * grad_scale;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step * mi / (sqrtf(vi) / bc2_sqrt + eps);
+  }
+}
+
 static int rblocks(long long n) {
   long long b = (n + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
@@ -382,5 +407,16 @@ extern "C" int pdac_adam_step(float* params, const float* grads, float* exp_avg,
   adam_kernel<<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps,
                                                             bc1, sqrtf(bc2), grad_scale);
   PDAC_LAUNCH_CHECK("adam");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n,
+                                  float* hyper, long long* step, void* stream) {
+  PDAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && hyper && step, "adam: null argument");
+  adam_tick_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(hyper, step);
+  PDAC_LAUNCH_CHECK("adam_tick");
+  if (n <= 0) return PDAC_OK;
+  adam_dev_kernel<<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, hyper);
+  PDAC_LAUNCH_CHECK("adam_dev");
   return PDAC_OK;
 }

@@ -3,6 +3,12 @@ DDP semantics kept: gradients are averaged over ranks; buckets are contiguous ra
 from the LAST registered parameter backwards (those gradients are complete first in backward), at most `bucket_mb`
 each (torch's default 25 MB); parameters that never receive a gradient (ResUNet's encoder.fc, PSPNet's layer3/4) are
 simply not in the arena, which replaces find_unused_parameters=True's per-iteration graph walk.
+
+Overlap with backward (what torch's reducer does during loss.backward(), train_worker.py:79): the engine's tape reports
+after every backward step which parameters it completed (`ready`); when the last parameter of a bucket is complete an
+event is recorded on the compute stream and the bucket's all_reduce is enqueued on a side stream that waits for that
+event only — the rest of backward keeps running on the compute stream. `finish` joins the side stream before the
+optimizer. All of it is stream-ordered, so it can be captured into the train step's CUDA graph.
 Device-agnostic (flat CPU tensors + gloo in the CPU tests, CUDA + NCCL on the box)."""
 from __future__ import annotations
 
@@ -29,26 +35,70 @@ def make_buckets(param_offsets, total, bucket_mb=25.0, elem_bytes=4):
 
 
 class BucketReducer:
-    def __init__(self, flat: torch.Tensor, spans, process_group=None):
+    def __init__(self, flat: torch.Tensor, spans, process_group=None, param_offsets=None):
+        """param_offsets: {key: arena offset} of every parameter that reports readiness (key = id(parameter))."""
         self.flat, self.spans, self.pg = flat, list(spans), process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.stream = torch.cuda.Stream(device=flat.device) if (flat.is_cuda and self.world > 1) else None
+        self.bucket_of, self.members = {}, [0] * len(self.spans)
+        for key, off in (param_offsets or {}).items():
+            for b, (lo, hi) in enumerate(self.spans):
+                if lo <= off < hi:
+                    self.bucket_of[key] = b
+                    self.members[b] += 1
+                    break
+        self.begin()
+        self.launch_order = []          # bucket indices in the order their all_reduce was enqueued (tests / profiling)
 
-    def allreduce_sum(self, upto=None):
-        """Sums every bucket over the ranks (the mean's 1/world is folded into the optimizer's grad_scale). On CUDA the
-        collectives run on a side stream that waits for the producing stream and is joined before the optimizer."""
+    # -- overlapped protocol: begin() ... ready(keys) per backward step ... finish() ------------------------------------
+    def begin(self):
+        self._left = list(self.members)
+        self._sent = [False] * len(self.spans)
+        self._seen = set()
+        self.launch_order = []
+
+    def ready(self, keys):
+        """The gradient slots of these parameters are complete on the current stream."""
         if self.world == 1:
             return
+        for k in keys:
+            b = self.bucket_of.get(k)
+            if b is None or k in self._seen:
+                continue
+            self._seen.add(k)
+            self._left[b] -= 1
+            if self._left[b] == 0 and not self._sent[b]:
+                self._launch(b)
+
+    def _launch(self, b):
+        lo, hi = self.spans[b]
+        self._sent[b] = True
+        self.launch_order.append(b)
         if self.stream is None:
-            for lo, hi in self.spans:
-                dist.all_reduce(self.flat[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
+            dist.all_reduce(self.flat[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
             return
-        cur = torch.cuda.current_stream(self.flat.device)
-        self.stream.wait_stream(cur)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.flat.device))
+        self.stream.wait_event(ev)
         with torch.cuda.stream(self.stream):
-            for lo, hi in self.spans:
-                dist.all_reduce(self.flat[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
-        cur.wait_stream(self.stream)
+            dist.all_reduce(self.flat[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
+
+    def finish(self):
+        """Reduces whatever has not been sent yet (buckets whose parameters never reported) and makes the current
+        stream wait for all collectives: after this the arena holds the SUM over ranks (1/world is folded into the
+        optimizer's grad_scale)."""
+        if self.world == 1:
+            return
+        for b in range(len(self.spans)):
+            if not self._sent[b]:
+                self._launch(b)
+        if self.stream is not None:
+            torch.cuda.current_stream(self.flat.device).wait_stream(self.stream)
+
+    def allreduce_sum(self):
+        """Non-overlapped form: every bucket after the producing stream has finished all of backward."""
+        self.begin()
+        self.finish()
 
     def broadcast(self, tensors, src=0):
         if self.world > 1:

@@ -114,9 +114,11 @@ class Tape:
         self.nograd = set()
         self.host_rng = False
 
-    def record(self, fn):
+    def record(self, fn, params=()):
+        """fn: the layer's backward step; params: the parameters whose gradient slots that step completes (the
+        data-parallel reducer launches a bucket's allreduce as soon as all of its parameters are complete)."""
         if self.enabled:
-            self.steps.append(fn)
+            self.steps.append((fn, tuple(p for p in params if p is not None)))
 
     def no_grad_for(self, t):
         self.nograd.add(id(t))
@@ -137,9 +139,11 @@ class Tape:
     def pop(self, t):
         return self.grads.pop(id(t), None)
 
-    def backward(self):
-        for fn in reversed(self.steps):
+    def backward(self, on_params_done=None):
+        for fn, params in reversed(self.steps):
             fn()
+            if on_params_done is not None and params:
+                on_params_done(params)
         self.steps = []
         self.grads = {}
 
@@ -183,7 +187,7 @@ def conv_bias_act(tape: Tape, m: Conv2d, srcs, relu):
             dbias = tape.arena.slot(m.bias, padded=True)[:dy.shape[3]] if m.bias is not None else None
             ops.relu_bwd_bias(dy, y if relu else None, dy if relu else None, dbias)
         _conv_backward(tape, m, srcs, dy, wp_t)
-    tape.record(bwd)
+    tape.record(bwd, (m.weight, m.bias))
     return y
 
 
@@ -243,7 +247,7 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         if want_res:
             tape.put(residual, dy)
         _conv_backward(tape, m, srcs, dxr, wp_t)
-    tape.record(bwd)
+    tape.record(bwd, (m.weight, bn.weight, bn.bias))
     return y
 
 
@@ -270,7 +274,7 @@ def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
                          dgamma=tape.arena.slot(bn.weight), dbeta=tape.arena.slot(bn.bias), scale_shift=st.ss)
         dwp = ops.stem_conv_wgrad(z, dy)
         ops.unpack_stem_wgrad(dwp, m.cout, out=tape.arena.slot(m.weight))
-    tape.record(bwd)
+    tape.record(bwd, (m.weight, bn.weight, bn.bias))
     return y
 
 
@@ -298,7 +302,7 @@ def convt2x2(tape: Tape, m: ConvTranspose2d, x):
         ops.convt2x2_wgrad(x, dy, out=tape.arena.slot(m.weight), iohw=True)
         if tape.wants(x):
             tape.put(x, ops.convt2x2_dgrad(dy, wp_t, m.cin))
-    tape.record(bwd)
+    tape.record(bwd, (m.weight, m.bias))
     return y
 
 
@@ -351,7 +355,7 @@ def conv_gn_relu(tape: Tape, m: Conv2d, gn, srcs):
         dx = ops.groupnorm_bwd(dy, y, x, gn.num_groups, stats, gn.weight.detach(), gn.eps,
                                dgamma=tape.arena.slot(gn.weight), dbeta=tape.arena.slot(gn.bias), out=dy)
         _conv_backward(tape, m, srcs, dx, wp_t)
-    tape.record(bwd)
+    tape.record(bwd, (m.weight, gn.weight, gn.bias))
     return y
 
 
@@ -388,7 +392,7 @@ def depthwise3x3(tape: Tape, m: Conv2d, x):
             if old is not None:
                 ops.add(old, dx, out=dx)
             tape.put(x, dx)
-    tape.record(bwd)
+    tape.record(bwd, (m.weight,))
     return y
 
 

@@ -637,6 +637,14 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.9
          eps, step, grad_scale, _stream())
 
 
+def adam_step_dev(params, grads, exp_avg, exp_avg_sq, hyper, step):
+    """Adam with the step counter (int64 scalar) and hyper-parameters (fp32 [8]: lr, beta1, beta2, eps, grad_scale,
+    2 outputs) on the device: graph-capturable, lr changeable between replays."""
+    assert hyper.dtype == torch.float32 and hyper.numel() >= 8 and step.dtype == torch.int64
+    call("pdac_adam_step_dev", _ptr(params), _ptr(grads), _ptr(exp_avg), _ptr(exp_avg_sq), params.numel(), _ptr(hyper),
+         _ptr(step), _stream())
+
+
 def check_device_flag():
     """Synchronises the current stream, then raises if a pipeline barrier timed out (tests)."""
     call("pdac_check_device_flag", _stream())

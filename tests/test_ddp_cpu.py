@@ -62,10 +62,34 @@ def _worker(rank, world, port, out):
         for p in params:
             arena.slot(p).copy_(p.grad)
         offs = [arena.offsets[id(p)][0] for p in params]
-        red = BucketReducer(arena.flat, make_buckets(offs, arena.size, bucket_mb=0.0005))
+        red = BucketReducer(arena.flat, make_buckets(offs, arena.size, bucket_mb=0.0005), None,
+                            {id(p): arena.offsets[id(p)][0] for p in params})
         assert red.world == world and len(red.spans) >= 3
+        local = arena.flat.clone()
         red.allreduce_sum()
         ok = all(torch.allclose(arena.slot(p) / world, w, rtol=1e-6, atol=1e-7) for p, w in zip(params, want))
+        # the overlapped protocol: parameters report in backward order (last registered first); each bucket's
+        # all_reduce is launched the moment its last parameter reports, buckets in index order, every bucket once,
+        # and the result equals the non-overlapped reduction
+        summed = arena.flat.clone()
+        arena.flat.copy_(local)
+        red.begin()
+        sent_after = []
+        for p in reversed(params):
+            red.ready([id(p)])
+            red.ready([id(p)])                       # reporting twice is harmless
+            sent_after.append(len(red.launch_order))
+        assert red.launch_order == list(range(len(red.spans))) and sent_after[-1] == len(red.spans)
+        assert sent_after[0] <= 1 and sent_after == sorted(sent_after)
+        assert sent_after[len(params) // 2] >= 1, "no bucket was sent before the last parameter reported: no overlap"
+        red.finish()
+        ok = ok and torch.equal(arena.flat, summed)
+        # parameters that never report are flushed by finish()
+        arena.flat.copy_(local)
+        red.begin()
+        red.ready([id(params[-1])])
+        red.finish()
+        ok = ok and torch.equal(arena.flat, summed) and sorted(red.launch_order) == list(range(len(red.spans)))
         assert unused.weight.grad is None
         # construction-time broadcast
         t = torch.full((5,), float(rank))

@@ -154,117 +154,3 @@ def test_train_step_matches_oracle(name, train):
                 assert (diff <= atol + 5e-2 * sa[k].abs()).all(), (k, diff.max().item())
             if k.endswith("num_batches_tracked"):
                 assert int(so[k]) == int(sa[k]), k
-
-
-def test_trainstep_matches_autograd_path():
-    """The fused training harness (uint8 patches -> ... -> Adam) computes the same loss, gradients and parameter
-    update as the drop-in module under torch autograd + torch.optim.Adam on the same prepared input
-    (train_worker.py:68-80)."""
-    import copy
-
-    from pdac_pathological_image_segmentation_b200 import ops
-    from pdac_pathological_image_segmentation_b200.module_base import _NetFn
-    from pdac_pathological_image_segmentation_b200.smp import Unet
-    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
-    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
-    from pdac_pathological_image_segmentation_b200.util import DiceLoss
-    torch.manual_seed(3)
-    m1 = Unet(encoder_weights=None).to(DEV).train()
-    m2 = copy.deepcopy(m1)
-    img, mask = synthetic_batch(2, 64, seed=7)
-    img, mask = img.to(DEV), mask.to(DEV)
-    ts = TrainStep(m1, lr=1e-3)
-    before = ts.flat_params.clone()
-    loss1, score1 = ts.step(img, mask)
-    g1 = {k: ts.arena.slot(p).clone() for k, p in m1.named_parameters()}
-    # the drop-in path on the SAME prepared stem input (the u8 -> bf16 normalisation is one kernel either way)
-    z, _ = ops.stem_prep_u8(img, mask, None)
-    opt = torch.optim.Adam(m2.parameters(), lr=1e-3)
-    out = _NetFn.apply(m2, z, *m2._trainable())
-    loss2 = DiceLoss()(torch.squeeze(out), mask.float())
-    loss2.backward()
-    opt.step()
-    # BatchNorm batch statistics are summed with fp32 atomics: their order (hence a few bf16 roundings downstream)
-    # differs between two launches of the very same kernels
-    assert abs(loss1.item() - loss2.item()) <= 5e-4
-    assert 0.0 <= score1.item() <= 1.0
-    # Same kernels on the same input, but the BatchNorm batch statistics are summed with fp32 atomics whose order differs
-    # from launch to launch; a last-bit change of a scale flips a few bf16 roundings in the first layers and those cascade
-    # (every flip is a 2^-8 relative step): two launches of the SAME path differ like two realisations of bf16 storage
-    # noise -- scripts/diag_determinism.py measures a whole-gradient spread of 0.28-0.38 between identical TrainStep runs
-    # on this random-init network (0.01 only when the tensors are small enough for a fixed atomic order). Train mode
-    # therefore only gets a sanity bound here; the exact comparison of the two paths is the eval-mode block below.
-    num = den = 0.0
-    for k, p2 in m2.named_parameters():
-        r = p2.grad.double()
-        num += ((g1[k].double() - r).norm().item()) ** 2
-        den += r.norm().item() ** 2
-    assert (num / den) ** 0.5 <= 0.7, (num / den) ** 0.5
-    moved = (ts.flat_params - before).abs().max().item()
-    assert 0.5e-3 <= moved <= 1.01e-3      # Adam's first step moves weights by ~lr
-    ts.step(img, mask)                    # second step runs on re-packed weights
-    assert torch.isfinite(ts.flat_params).all()
-
-
-def test_trainstep_gradients_equal_autograd_path_eval_mode():
-    """With BatchNorm in eval mode the forward has no atomics (running statistics), so the fused harness and the drop-in
-    module under torch autograd must produce the same gradients up to the fp32 atomic order of the split-K weight
-    gradients (train_worker.py trains in eval mode from epoch 2 on)."""
-    import copy
-
-    from pdac_pathological_image_segmentation_b200 import ops
-    from pdac_pathological_image_segmentation_b200.module_base import _NetFn
-    from pdac_pathological_image_segmentation_b200.smp import Unet
-    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
-    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
-    from pdac_pathological_image_segmentation_b200.util import DiceLoss
-    torch.manual_seed(5)
-    m1 = Unet(encoder_weights=None).to(DEV).eval()
-    m2 = copy.deepcopy(m1)
-    img, mask = synthetic_batch(2, 128, seed=9)
-    img, mask = img.to(DEV), mask.to(DEV)
-    ts = TrainStep(m1, lr=1e-3)
-    loss1, _ = ts.step(img, mask)
-    g1 = {k: ts.arena.slot(p).clone() for k, p in m1.named_parameters()}
-    z, _ = ops.stem_prep_u8(img, mask, None)
-    opt = torch.optim.Adam(m2.parameters(), lr=1e-3)
-    out = _NetFn.apply(m2, z, *m2._trainable())
-    loss2 = DiceLoss()(torch.squeeze(out), mask.float())
-    loss2.backward()
-    opt.step()
-    assert abs(loss1.item() - loss2.item()) <= 1e-6
-    for (k, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
-        frac = ((p1 - p2).abs() > 2e-4).float().mean().item()   # fused Adam == torch.optim.Adam; sign flips of ~0 gradients only
-        assert frac <= 0.02, (k, frac)
-    for k, p2 in m2.named_parameters():
-        r = p2.grad.double()
-        rel = ((g1[k].double() - r).norm() / (r.norm() + 1e-30)).item()
-        assert rel <= 1e-3, (k, rel)
-
-
-def test_trainstep_cuda_graph_replays_the_eager_step():
-    """TrainStep(graph=True) replays forward + loss + backward from a CUDA graph. In eval mode (no atomics in the
-    forward) the replay and an eager forward_backward of the SAME harness on the same batch give the same loss, score
-    and gradient arena, step after step, with Adam updates (and weight re-packs) in between."""
-    from pdac_pathological_image_segmentation_b200.smp import Unet
-    from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
-    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
-    torch.manual_seed(11)
-    m = Unet(encoder_weights=None).to(DEV).eval()
-    ts = TrainStep(m, lr=1e-5, graph=True)
-    batches = [tuple(x.to(DEV) for x in synthetic_batch(2, 128, seed=20 + i)) for i in range(3)]
-    for it in range(6):                         # steps 0-1 eager warm-up, step 2 captures + replays, 3-5 replay
-        img, mask = batches[it % 3]
-        l2, s2 = ts._graph_forward_backward(img, mask, None)
-        g2 = ts.arena.flat.double().clone()
-        l1, s1 = ts.forward_backward(img, mask)
-        g1 = ts.arena.flat.double()
-        assert g1.norm().item() > 1e-3          # the comparison below is about real gradients
-        assert abs(l1.item() - l2.item()) <= 1e-6 and abs(s1.item() - s2.item()) <= 1e-6, (it, l1.item(), l2.item())
-        assert ((g1 - g2).norm() / g1.norm()).item() <= 1e-3, it
-        ts.optimizer_step()
-    assert ts._g is not None
-    # and through the public call
-    before = ts.flat_params.clone()
-    loss, _ = ts.step(*batches[0])
-    assert torch.isfinite(loss) and (ts.flat_params - before).abs().max().item() > 0
