@@ -24,7 +24,7 @@
  *                                    train_worker.py:24,72 and test.py:144 (sigmoid >= 0.5 mask)
  *   adam                          -> torch.optim.Adam(model.parameters(), lr) at train_worker.py:184, step at :80
  *   stitch                        -> visualize/predict_overlay.ipynb (missing blob) per configs/visualize_config.yaml:3-15
- *   prep                          -> dataset.py:24-30 + train_main.py:70-75 (Normalize / flips / rot90)
+ *   prep                          -> dataset.py:24-30 + train_main.py:70-80 (Normalize / ColorJitter / OneOf flips, rot90)
  */
 #ifndef PDAC_B200_H
 #define PDAC_B200_H
@@ -152,6 +152,22 @@ int pdac_stem_prep_f32(const float* x, int N, int H, int W, void* out, void* str
  * same geometry (mask_in/mask_out may be NULL). mean/stdv are HOST pointers to 3 floats. */
 int pdac_stem_prep_u8(const uint8_t* img, const uint8_t* mask_in, const int32_t* aug, int N, int H, int W,
                       const float* mean, const float* stdv, void* out, uint8_t* mask_out, void* stream);
+/* Training augmentation fused into the stem input preparation (train_main.py:70-80: Normalize -> ColorJitter(0.3 x 4) ->
+ * OneOf([HorizontalFlip, RandomRotate90, VerticalFlip], p=0.3)), drawn on the device from a counter-based hash of
+ * (seed, *step, patch, draw): no host random numbers, so the step replays from a CUDA graph. Semantics: csrc/augment.cu
+ * header (albumentations is absent and unpinned: PARITY UNPINNED; executable restatement oracle/augment_oracle.py). */
+typedef struct PdacAugment {
+  float brightness, contrast, saturation, hue; /* ColorJitter ranges: factors ~ U(1-r, 1+r), hue shift ~ U(-r, r) */
+  float p_color;                               /* probability that ColorJitter is applied to a patch (library: 0.5) */
+  float p_geom;                                /* probability of the OneOf group (reference: 0.3) */
+  unsigned long long seed;
+} PdacAugment;
+/* step: optional DEVICE pointer to a step counter mixed into the seed. params: fp32 [N][8] written per patch:
+ * [0] ColorJitter applied, [1] operation order 0..23, [2..4] brightness / contrast / saturation factors, [5] hue shift,
+ * [6] geometry (0 none, 1 hflip, 2 vflip, 3/4/5 rot90 x 1/2/3 counter-clockwise), [7] the contrast step's gray mean. */
+int pdac_stem_prep_u8_augment(const uint8_t* img, const uint8_t* mask_in, int N, int H, int W, const float* mean,
+                              const float* stdv, const PdacAugment* cfg, const long long* step, float* params,
+                              void* out, uint8_t* mask_out, void* stream);
 /* state_dict weight fp32 [O][I][R][S] -> wp_f bf16 [R*S][wrows_f][kf] (row = o, col = i; forward) and/or
  * wp_t bf16 [R*S][wrows_t][kt] (row = i, col = o; data gradient). Padding rows/cols are zeroed. s2_pad >= 0 orders
  * wp_t's taps by stride-2 output parity class (see pdac_conv2d_dgrad), -1 keeps (r,s) order.
@@ -223,8 +239,11 @@ int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacV
 int pdac_groupnorm_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, int G, const float* stats,
                              const float* gamma, float eps, const float* gsums, const PdacView* dx, void* stream);
 /* y = x * keep / (1 - p) with keep a counter-based hash of (seed, image, channel) (per_channel = 1: nn.Dropout2d) or
- * of (seed, element) (nn.Dropout); the backward pass is the same call on the gradient. Not torch's Philox stream. */
-int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long long seed, int per_channel, void* stream);
+ * of (seed, element) (nn.Dropout); the backward pass is the same call on the gradient. Not torch's Philox stream.
+ * step: optional DEVICE pointer to a step counter that is mixed into the seed when the kernel runs (a fresh mask per
+ * training step under CUDA-graph replay, where `seed` is baked into the graph). */
+int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long long seed, const long long* step,
+                 int per_channel, void* stream);
 /* Depthwise 3x3, stride 1, padding = dilation. w: fp32 [C][9] (the state_dict (C,1,3,3) tensor). flip = 1 applies the
  * transposed taps (data gradient). */
 int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int flip, const PdacView* y, void* stream);
@@ -259,8 +278,9 @@ int pdac_adam_step(float* params, const float* grads, float* exp_avg, float* exp
                    float beta1, float beta2, float eps, int step, float grad_scale, void* stream);
 /* The same update with the step counter and the hyper-parameters in DEVICE memory, so that a whole train step replays
  * from one CUDA graph and a scheduler changes the learning rate by writing hyper[0] (ReduceLROnPlateau at
- * train_worker.py:240): *step += 1 first; hyper = float[8]: [0] lr, [1] beta1, [2] beta2, [3] eps, [4] grad_scale,
- * [5..6] written by the library (lr / (1 - beta1^t), sqrt(1 - beta2^t), computed in double). */
+ * train_worker.py:240): *step += 1 first; hyper = float[12]: [0] lr, [1] beta1, [2] beta2, [3] eps, [4] grad_scale,
+ * [7] 1 - beta1, [8] 1 - beta2 (the caller rounds them from double, as torch.optim.Adam does); [5..6] are written by
+ * the library (lr / (1 - beta1^t), sqrt(1 - beta2^t), computed in double). */
 int pdac_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float* hyper,
                        long long* step, void* stream);
 

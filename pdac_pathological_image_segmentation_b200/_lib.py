@@ -25,6 +25,11 @@ class PdacConv(C.Structure):
                 ("relu", C.c_int32), ("wrows", C.c_int32), ("cout_valid", C.c_int32)]
 
 
+class PdacAugment(C.Structure):
+    _fields_ = [("brightness", C.c_float), ("contrast", C.c_float), ("saturation", C.c_float), ("hue", C.c_float),
+                ("p_color", C.c_float), ("p_geom", C.c_float), ("seed", C.c_ulonglong)]
+
+
 class PdacTap(C.Structure):
     _fields_ = [("src", C.c_int32), ("dh", C.c_int32), ("dw", C.c_int32)]
 
@@ -54,6 +59,8 @@ SIGNATURES = {
     "pdac_nhwc_bf16_to_nchw_f32": [_VP, _i, _p, _p],
     "pdac_stem_prep_f32": [_p, _i, _i, _i, _p, _p],
     "pdac_stem_prep_u8": [_p, _p, _p, _i, _i, _i, C.POINTER(_f), C.POINTER(_f), _p, _p, _p],
+    "pdac_stem_prep_u8_augment": [_p, _p, _i, _i, _i, C.POINTER(_f), C.POINTER(_f), C.POINTER(PdacAugment), _p, _p, _p, _p,
+                                  _p],
     "pdac_pack_conv_weight": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
     "pdac_pack_stem_weight": [_p, _i, _p, _p],
     "pdac_unpack_stem_wgrad": [_p, _i, _p, _p],
@@ -77,7 +84,7 @@ SIGNATURES = {
     "pdac_groupnorm_fwd": [_VP, _i, _p, _p, _p, _f, _i, _VP, _p],
     "pdac_groupnorm_bwd_reduce": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _p, _p, _p],
     "pdac_groupnorm_bwd_apply": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _VP, _p],
-    "pdac_dropout": [_VP, _VP, _f, C.c_ulonglong, _i, _p],
+    "pdac_dropout": [_VP, _VP, _f, C.c_ulonglong, _p, _i, _p],
     "pdac_dwconv3x3": [_VP, _p, _i, _i, _VP, _p],
     "pdac_dwconv3x3_wgrad": [_VP, _VP, _i, _p, _p],
     "pdac_dice_fwd": [_p, _p, _i, _ll, _p, _f, _p, _p],

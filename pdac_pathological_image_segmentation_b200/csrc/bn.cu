@@ -53,23 +53,39 @@ static EwGrid ew_grid(long long npix, int C, int resident) {
 
 // ------------------------------------------------------------------------------------------------ bn_prepare
 // stats: [n_rows][2][C] partial sums (one row per producing CTA / warpgroup, unused rows zero). The rows are added in
-// a fixed order (8 interleaved row groups per channel, combined in index order), in double: bit-reproducible batch
-// statistics whatever order the producers ran in.
-__global__ void __launch_bounds__(256) bn_prepare_kernel(const float* __restrict__ stats, int n_rows, double count,
+// a fixed order (32 interleaved row groups per channel, four independent loads in flight per thread, groups combined in
+// index order), in double: bit-reproducible batch statistics whatever order the producers ran in.
+__global__ void __launch_bounds__(1024) bn_prepare_kernel(const float* __restrict__ stats, int n_rows, double count,
                                   const float* __restrict__ gamma,
                                   const float* __restrict__ beta, float eps, float momentum, int train,
                                   float* running_mean, float* running_var, long long* num_batches_tracked,
                                   float* __restrict__ scale_shift, float* __restrict__ mean_invstd, int C) {
-  __shared__ double part[8][32][2];
+  __shared__ double part[32][32][2];
   const int cl = threadIdx.x & 31, rg = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + cl;
   if (train) {
     double a0 = 0.0, a1 = 0.0;
-    if (c < C)
-      for (int r = rg; r < n_rows; r += 8) {
+    if (c < C) {
+      int r = rg;
+      for (; r + 96 < n_rows; r += 128) {  // four rows (r, r+32, r+64, r+96) per trip: eight loads in flight
+        const float* p0 = stats + ((size_t)r * 2) * C + c;
+        const size_t st = (size_t)64 * C;
+        const float x0 = p0[0], y0 = p0[C], x1 = p0[st], y1 = p0[st + C];
+        const float x2 = p0[2 * st], y2 = p0[2 * st + C], x3 = p0[3 * st], y3 = p0[3 * st + C];
+        a0 += (double)x0;
+        a0 += (double)x1;
+        a0 += (double)x2;
+        a0 += (double)x3;
+        a1 += (double)y0;
+        a1 += (double)y1;
+        a1 += (double)y2;
+        a1 += (double)y3;
+      }
+      for (; r < n_rows; r += 32) {
         a0 += (double)stats[((size_t)r * 2) * C + c];
         a1 += (double)stats[((size_t)r * 2 + 1) * C + c];
       }
+    }
     part[rg][cl][0] = a0;
     part[rg][cl][1] = a1;
   }
@@ -79,7 +95,7 @@ __global__ void __launch_bounds__(256) bn_prepare_kernel(const float* __restrict
   float mean, var;
   if (train) {
     double t0 = 0.0, t1 = 0.0;
-    for (int g = 0; g < 8; ++g) {
+    for (int g = 0; g < 32; ++g) {
       t0 += part[g][cl][0];
       t1 += part[g][cl][1];
     }
@@ -110,24 +126,35 @@ __global__ void __launch_bounds__(256) bn_prepare_kernel(const float* __restrict
 
 // out[c] (+)= sum_r rows[r][c], r = 0 .. n_rows-1 in a fixed order: the deterministic second stage of every
 // cross-block reduction (each block stores its partial row with plain stores; no floating-point atomics).
-__global__ void __launch_bounds__(256) rows_sum_kernel(const float* __restrict__ rows, int n_rows, int ncols,
-                                                       float* __restrict__ out, int accumulate) {
-  __shared__ float part[8][32];
+__global__ void __launch_bounds__(1024) rows_sum_kernel(const float* __restrict__ rows, int n_rows, int ncols,
+                                                        float* __restrict__ out, int accumulate) {
+  __shared__ float part[32][33];
   const int cl = threadIdx.x & 31, rg = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + cl;
   float a = 0.f;
-  if (c < ncols)
-    for (int r = rg; r < n_rows; r += 8) a += rows[(size_t)r * ncols + c];
+  if (c < ncols) {
+    int r = rg;
+    for (; r + 96 < n_rows; r += 128) {
+      const float* p0 = rows + (size_t)r * ncols + c;
+      const size_t st = (size_t)32 * ncols;
+      const float x0 = p0[0], x1 = p0[st], x2 = p0[2 * st], x3 = p0[3 * st];
+      a += x0;
+      a += x1;
+      a += x2;
+      a += x3;
+    }
+    for (; r < n_rows; r += 32) a += rows[(size_t)r * ncols + c];
+  }
   part[rg][cl] = a;
   __syncthreads();
   if (rg == 0 && c < ncols) {
     float t = 0.f;
-    for (int g = 0; g < 8; ++g) t += part[g][cl];
+    for (int g = 0; g < 32; ++g) t += part[g][cl];
     out[c] = accumulate ? out[c] + t : t;
   }
 }
 int rows_sum(const float* rows, int n_rows, int ncols, float* out, int accumulate, cudaStream_t stream) {
-  rows_sum_kernel<<<ceil_div(ncols, 32), 256, 0, stream>>>(rows, n_rows, ncols, out, accumulate);
+  rows_sum_kernel<<<ceil_div(ncols, 32), 1024, 0, stream>>>(rows, n_rows, ncols, out, accumulate);
   PDAC_LAUNCH_CHECK("rows_sum");
   return PDAC_OK;
 }
@@ -382,7 +409,7 @@ extern "C" int pdac_bn_prepare(const float* stats, int n_rows, double count, con
   PDAC_REQUIRE(train ? (stats != nullptr && n_rows >= 1) : (running_mean && running_var),
                "bn_prepare: train needs stats, eval needs running stats");
   if (train) PDAC_REQUIRE(count > 1.0, "Expected more than 1 value per channel when training (count=%g)", count);
-  bn_prepare_kernel<<<ceil_div(C, 32), 256, 0, (cudaStream_t)stream>>>(
+  bn_prepare_kernel<<<ceil_div(C, 32), 1024, 0, (cudaStream_t)stream>>>(
       stats, n_rows, count, gamma, beta, eps, momentum, train, running_mean, running_var, num_batches_tracked,
       scale_shift, mean_invstd, C);
   PDAC_LAUNCH_CHECK("bn_prepare");

@@ -253,12 +253,14 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
 
 // Device-side step counter and hyper-parameters: the whole train step (incl. Adam) replays from one CUDA graph, and a
 // learning-rate scheduler changes lr by writing hyper[0]. hyper: [0] lr [1] beta1 [2] beta2 [3] eps [4] grad_scale
-// [5] (out) lr / (1 - beta1^t) [6] (out) sqrt(1 - beta2^t); bias corrections in double, as torch.optim.Adam has them.
+// [5] (out) lr / (1 - beta1^t) [6] (out) sqrt(1 - beta2^t) [7] 1 - beta1 [8] 1 - beta2 (rounded from double by the
+// caller, as torch.optim.Adam computes them); bias corrections in double from the fp64 betas hyper64[0..1].
 __global__ void adam_tick_kernel(float* __restrict__ hyper, long long* __restrict__ step) {
   const long long t = *step + 1;
   *step = t;
-  const double bc1 = 1.0 - pow((double)hyper[1], (double)t);
-  const double bc2 = 1.0 - pow((double)hyper[2], (double)t);
+  const double b1 = 1.0 - (double)hyper[7], b2 = 1.0 - (double)hyper[8];
+  const double bc1 = 1.0 - pow(b1, (double)t);
+  const double bc2 = 1.0 - pow(b2, (double)t);
   hyper[5] = (float)((double)hyper[0] / bc1);
   hyper[6] = (float)sqrt(bc2);
 }
@@ -266,10 +268,11 @@ __global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, co
                                                        float* __restrict__ m, float* __restrict__ v, long long n,
                                                        const float* __restrict__ hyper) {
   const float b1 = hyper[1], b2 = hyper[2], eps = hyper[3], grad_scale = hyper[4], step = hyper[5], bc2_sqrt = hyper[6];
+  const float omb1 = hyper[7], omb2 = hyper[8];
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float gi = g[i] * grad_scale;
-    const float mi = b1 * m[i] + (1.f - b1) * gi;
-    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    const float mi = b1 * m[i] + omb1 * gi;
+    const float vi = b2 * v[i] + omb2 * gi * gi;
     m[i] = mi;
     v[i] = vi;
     p[i] -= step * mi / (sqrtf(vi) / bc2_sqrt + eps);

@@ -236,9 +236,11 @@ __device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned 
 // y = x * keep / (1 - p); keep is a function of (seed, n, c) for Dropout2d and of (seed, element) for Dropout, so the
 // backward pass is the same call on the gradient.
 __global__ void __launch_bounds__(256) dropout_kernel(ImgView x, ImgView y, float p, unsigned long long seed,
-                                                      int per_channel, int cg, int ppb) {
+                                                      const long long* __restrict__ step, int per_channel, int cg,
+                                                      int ppb) {
   IMG_SETUP(cg, ppb)
   if (!active) return;
+  if (step) seed += (unsigned long long)(*step) * 0xD6E8FEB86659FD93ull;  // a fresh mask per optimizer step, no host value
   const float inv = 1.f / (1.f - p);
   float f[8];
   if (per_channel) {
@@ -537,14 +539,14 @@ extern "C" int pdac_groupnorm_bwd_apply(const PdacView* dy, const PdacView* y, c
   return PDAC_OK;
 }
 
-extern "C" int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long long seed, int per_channel,
-                            void* stream) {
+extern "C" int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long long seed,
+                            const long long* step, int per_channel, void* stream) {
   ImgView xv, yv;
   PDAC_TRY(img_view(x, &xv, "dropout x"));
   PDAC_TRY(img_view(y, &yv, "dropout y"));
   PDAC_REQUIRE(p >= 0.f && p < 1.f, "dropout probability %g out of range [0, 1)", (double)p);
   const ImgGrid g = img_grid(xv.npix, x->C, x->N);
-  dropout_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, yv, p, seed, per_channel, g.cg, g.ppb);
+  dropout_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, yv, p, seed, step, per_channel, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("dropout_kernel");
   return PDAC_OK;
 }

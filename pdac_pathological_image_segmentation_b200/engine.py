@@ -104,10 +104,15 @@ class GradArena:
 
 # ------------------------------------------------------------------------------------------------ tape
 class Tape:
-    def __init__(self, packs: PackCache, training: bool, arena: GradArena | None):
+    def __init__(self, packs: PackCache, training: bool, arena: GradArena | None, step_dev=None, base_seed=0):
+        """step_dev / base_seed: the trainer's device-side step counter and a per-trainer seed; with them the random
+        layers (Dropout) draw no host numbers per step, so the step can be replayed from a CUDA graph."""
         self.packs = packs
         self.training = training
         self.arena = arena
+        self.step_dev = step_dev
+        self.base_seed = int(base_seed)
+        self.n_random = 0
         self.enabled = arena is not None
         self.steps = []
         self.grads = {}
@@ -364,14 +369,20 @@ def dropout(tape: Tape, x, p, per_channel):
     drawn from torch's CPU generator, so torch.manual_seed makes runs reproducible; it is NOT torch's Philox stream)."""
     if not tape.training or p <= 0.0:
         return x
-    seed = int(torch.randint(0, 2 ** 62, (1,)).item())
-    tape.host_rng = True   # a per-step host value is baked into the launch: such a step must not be replayed from a graph
-    y = ops.dropout(x, p, seed, per_channel)
+    step = tape.step_dev
+    if step is not None:
+        # trainer path: the seed is (trainer seed, index of this layer call); the device step counter is mixed in by the kernel
+        seed = (tape.base_seed + 0x9E3779B97F4A7C15 * (tape.n_random + 1)) & (2 ** 62 - 1)
+        tape.n_random += 1
+    else:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        tape.host_rng = True   # a per-step host value is baked into the launch: such a step must not be replayed from a graph
+    y = ops.dropout(x, p, seed, per_channel, step=step)
 
     def bwd():
         dy = tape.pop(y)
         if dy is not None:
-            tape.put(x, ops.dropout(dy, p, seed, per_channel, out=dy))
+            tape.put(x, ops.dropout(dy, p, seed, per_channel, out=dy, step=step))
     tape.record(bwd)
     return y
 

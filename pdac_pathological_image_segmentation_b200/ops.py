@@ -362,6 +362,40 @@ def stem_prep_u8(img, mask=None, aug=None, mean=IMAGENET_MEAN, std=IMAGENET_STD,
     return out, mask_out
 
 
+class Augment:
+    """The reference's training augmentation (train_main.py:70-80), drawn and applied on the GPU: ColorJitter ranges,
+    the probability that ColorJitter is applied to a patch (albumentations' default p = 0.5), the OneOf group's p."""
+
+    def __init__(self, brightness=0.3, contrast=0.3, saturation=0.3, hue=0.3, p_color=0.5, p_geom=0.3, seed=0):
+        self.brightness, self.contrast, self.saturation, self.hue = brightness, contrast, saturation, hue
+        self.p_color, self.p_geom, self.seed = p_color, p_geom, int(seed)
+
+    def struct(self):
+        return _lib.PdacAugment(self.brightness, self.contrast, self.saturation, self.hue, self.p_color, self.p_geom,
+                                self.seed & 0xFFFFFFFFFFFFFFFF)
+
+
+def stem_prep_u8_augment(img, mask, cfg, step=None, mean=IMAGENET_MEAN, std=IMAGENET_STD, out=None, mask_out=None,
+                         params=None):
+    """uint8 (N,H,W,3) patches (+ uint8 masks) -> augmented stem input. -> (z, mask_out, params fp32 [N, 8]: the drawn
+    per-patch parameters, see include/pdac_b200.h). step: int64 device scalar mixed into the seed."""
+    _need_cuda(img, "image batch")
+    assert img.dtype == torch.uint8 and img.is_contiguous() and img.shape[3] == 3
+    n, h, w, _ = img.shape
+    if out is None:
+        out = empty_act(n, h // 2, w // 2, 16, img.device)
+    if mask is not None and mask_out is None:
+        mask_out = torch.empty_like(mask)
+    if params is None:
+        params = torch.empty((n, 8), dtype=torch.float32, device=img.device)
+    m = (C.c_float * 3)(*mean)
+    s = (C.c_float * 3)(*std)
+    st = cfg.struct()
+    call("pdac_stem_prep_u8_augment", _ptr(img), _ptr(mask), n, h, w, m, s, C.byref(st), _ptr(step), _ptr(params),
+         _ptr(out), _ptr(mask_out), _stream())
+    return out, mask_out, params
+
+
 # ------------------------------------------------------------------------------------------------ BN / elementwise
 def bn_prepare(stats, count, gamma, beta, eps, momentum, train, running_mean, running_var, scale_shift, mean_invstd,
                num_batches_tracked=None):
@@ -515,11 +549,13 @@ def groupnorm_bwd(dy, y, x, groups, stats, gamma, eps, dgamma=None, dbeta=None, 
     return out
 
 
-def dropout(x, p, seed, per_channel, out=None):
-    """nn.Dropout2d (per_channel) / nn.Dropout with a counter-based hash mask; backward = same call on the gradient."""
+def dropout(x, p, seed, per_channel, out=None, step=None):
+    """nn.Dropout2d (per_channel) / nn.Dropout with a counter-based hash mask; backward = same call on the gradient.
+    step: optional int64 device scalar mixed into the seed at run time (fresh masks under CUDA-graph replay)."""
     if out is None:
         out = torch.empty_like(x)
-    call("pdac_dropout", _vp(x), _vp(out), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(per_channel)), _stream())
+    call("pdac_dropout", _vp(x), _vp(out), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, _ptr(step), int(bool(per_channel)),
+         _stream())
     return out
 
 
@@ -638,9 +674,9 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.9
 
 
 def adam_step_dev(params, grads, exp_avg, exp_avg_sq, hyper, step):
-    """Adam with the step counter (int64 scalar) and hyper-parameters (fp32 [8]: lr, beta1, beta2, eps, grad_scale,
-    2 outputs) on the device: graph-capturable, lr changeable between replays."""
-    assert hyper.dtype == torch.float32 and hyper.numel() >= 8 and step.dtype == torch.int64
+    """Adam with the step counter (int64 scalar) and hyper-parameters (fp32 [12]: lr, beta1, beta2, eps, grad_scale,
+    2 outputs, 1 - beta1, 1 - beta2) on the device: graph-capturable, lr changeable between replays."""
+    assert hyper.dtype == torch.float32 and hyper.numel() >= 12 and step.dtype == torch.int64
     call("pdac_adam_step_dev", _ptr(params), _ptr(grads), _ptr(exp_avg), _ptr(exp_avg_sq), params.numel(), _ptr(hyper),
          _ptr(step), _stream())
 

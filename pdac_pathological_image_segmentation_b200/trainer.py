@@ -83,10 +83,12 @@ class ArenaAdam(torch.optim.Optimizer):
 
 class TrainStep:
     def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, process_group=None, bucket_mb=25.0, graph=False,
-                 overlap=True):
+                 overlap=True, augment=None):
         """graph=True: after two eager steps per input shape the WHOLE step (input prep, forward, loss, backward, the
         bucketed NCCL all_reduces on their side stream, Adam) is captured once into a CUDA graph and replayed.
-        overlap=False keeps all collectives behind the end of backward (for A/B timing)."""
+        overlap=False keeps all collectives behind the end of backward (for A/B timing).
+        augment: None, True (the reference's ColorJitter + OneOf pipeline, train_main.py:70-80) or an ops.Augment:
+        drawn on the device per step from (seed, device step counter) — graph-replayable, reproducible."""
         self.model = model
         self.use_graph = bool(graph)
         self.overlap = bool(overlap) and os.environ.get("PDAC_DDP_OVERLAP", "1") != "0"
@@ -116,8 +118,11 @@ class TrainStep:
         self.optimizer = ArenaAdam(self, model.parameters(), lr, betas, eps)
         # device-side Adam state: step counter and hyper-parameters (the graph reads them, schedulers write lr)
         self.step_dev = torch.zeros((), dtype=torch.int64, device=dev)
-        self.hyper = torch.zeros(8, dtype=torch.float32, device=dev)
+        self.hyper = torch.zeros(12, dtype=torch.float32, device=dev)
         self._hyper_host = None
+        self._seed = int(torch.randint(0, 2 ** 62, (1,)).item())      # Dropout masks / augmentation draws (torch.manual_seed)
+        self.augment = ops.Augment(seed=self._seed) if augment is True else augment
+        self.last_aug_params = None
         self._sync_hyper()
         model._packs.invalidate()
 
@@ -132,9 +137,10 @@ class TrainStep:
 
     def _sync_hyper(self):
         g = self.optimizer.param_groups[0]
-        host = (float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), 1.0 / self.world)
+        b1, b2 = float(g["betas"][0]), float(g["betas"][1])
+        host = (float(g["lr"]), b1, b2, float(g["eps"]), 1.0 / self.world, 0.0, 0.0, 1.0 - b1, 1.0 - b2)
         if host != self._hyper_host:
-            self.hyper[:5].copy_(torch.tensor(host, dtype=torch.float32), non_blocking=False)
+            self.hyper[:9].copy_(torch.tensor(host, dtype=torch.float32), non_blocking=False)
             self._hyper_host = host
 
     @property
@@ -156,8 +162,11 @@ class TrainStep:
         """-> (loss, dice score) as 0-d device tensors. img_u8 (B,H,W,3) uint8, mask_u8 (B,H,W) uint8 {0,1}. With
         reduce=True the gradient arena holds the SUM over the ranks when the returned work has run."""
         model = self.model
-        z, mask = ops.stem_prep_u8(img_u8, mask_u8, aug)
-        tape = Tape(model._packs, model.training, self.arena)
+        if self.augment is not None and aug is None and model.training:
+            z, mask, self.last_aug_params = ops.stem_prep_u8_augment(img_u8, mask_u8, self.augment, step=self.step_dev)
+        else:
+            z, mask = ops.stem_prep_u8(img_u8, mask_u8, aug)
+        tape = Tape(model._packs, model.training, self.arena, step_dev=self.step_dev, base_seed=self._seed)
         logits, feed = model._run(tape, z)
         self._host_rng = bool(getattr(tape, "host_rng", False))
         if logits.shape[1] != 1:
