@@ -174,6 +174,15 @@ int pdac_stem_prep_u8_augment(const uint8_t* img, const uint8_t* mask_in, int N,
  * nn.ConvTranspose2d weights [Cin][Cout][2][2] pack with O=Cin, I=Cout: wp_f is then the dgrad matrix, wp_t the forward. */
 int pdac_pack_conv_weight(const float* w, int O, int I, int R, int S, int wrows_f, int kf, void* wp_f, int wrows_t,
                           int kt, void* wp_t, int s2_pad, void* stream);
+/* The same packing for n weight tensors in one launch per 24 tensors (descs is a HOST array): after an optimizer step
+ * the whole network is re-packed at once. Fields as the arguments of pdac_pack_conv_weight. */
+typedef struct PdacPackDesc {
+  const float* w;
+  void* wp_f;
+  void* wp_t;
+  int32_t O, I, R, S, wrows_f, kf, wrows_t, kt, s2_pad;
+} PdacPackDesc;
+int pdac_pack_conv_weights_batched(const PdacPackDesc* descs, int n, void* stream);
 /* stem weight fp32 [O][3][7][7] -> bf16 [16][O][16] for the 4x4 space-to-depth form; and its gradient back. */
 int pdac_pack_stem_weight(const float* w, int O, void* wp, void* stream);
 int pdac_unpack_stem_wgrad(const float* dwp, int O, float* dw, void* stream);
@@ -209,7 +218,10 @@ int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz
 /* ---- pooling / resampling (pool.cu) ------------------------------------------------------------------------- */
 /* idx: uint8 [N][Ho][Wo][C] arg-max tap (r*3+s), saved for backward (may be NULL in inference). */
 int pdac_maxpool3x3s2_fwd(const PdacView* x, const PdacView* y, uint8_t* idx, void* stream);
-int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, const PdacView* dx, void* stream);
+/* dx = scatter(dy by idx) (+ addend: the gradient another consumer of the pooled tensor's input has already left; may
+ * alias dx). */
+int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, const PdacView* addend, const PdacView* dx,
+                          void* stream);
 int pdac_upsample_nearest2x_fwd(const PdacView* x, const PdacView* y, void* stream);
 int pdac_upsample_nearest2x_bwd(const PdacView* dy, const PdacView* addend, const PdacView* dx, void* stream);
 int pdac_bilinear_fwd(const PdacView* x, int align_corners, const PdacView* y, void* stream);
@@ -226,15 +238,19 @@ int pdac_add(const PdacView* a, const PdacView* b, int relu, const PdacView* y, 
 /* ---- GroupNorm / dropout / depthwise 3x3 (norm_dw.cu) ------------------------------------------------------
  * The layers smp.FPN / PSPNet / DeepLabV3Plus add to the ResNet18 path (train_worker.py:152-182):
  * nn.GroupNorm(32, 128) of Conv3x3GNReLU, nn.Dropout2d / nn.Dropout, SeparableConv2d's depthwise 3x3 (dilated). */
-/* stats: fp32 [N][G][2] (sum, sum of squares per image and group; caller zeroes). */
-int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, void* stream);
+/* stats: fp32 [N][G][2] (sum, sum of squares per image and group). scratch (fp32, >= 1184 * G * 2 floats): the
+ * blocks' partial rows are added in a fixed order and stats is overwritten (reproducible); scratch == NULL: fp32
+ * atomics into stats, which the caller zeroes. */
+int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, float* scratch, void* stream);
 /* y = [relu]((x - mean) * rstd * gamma + beta), mean / rstd from stats (biased variance, eps inside the sqrt). */
 int pdac_groupnorm_fwd(const PdacView* x, int G, const float* stats, const float* gamma, const float* beta, float eps,
                        int relu, const PdacView* y, void* stream);
-/* dz = dy * (y > 0) (y may be NULL); gsums fp32 [N][G][2] += (sum dz*gamma, sum dz*gamma*xhat) (caller zeroes);
- * dgamma[c] += sum dz*xhat, dbeta[c] += sum dz (may be NULL). */
+/* dz = dy * (y > 0) (y may be NULL); gsums fp32 [N][G][2] = (sum dz*gamma, sum dz*gamma*xhat);
+ * dgamma[c] += sum dz*xhat, dbeta[c] += sum dz (may be NULL). scratch (fp32, >= 1184 * 2 * C floats): reproducible
+ * fixed-order sums (gsums overwritten); NULL: fp32 atomics (gsums zeroed by the caller). */
 int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, int G, const float* stats,
-                              const float* gamma, float eps, float* gsums, float* dgamma, float* dbeta, void* stream);
+                              const float* gamma, float eps, float* gsums, float* dgamma, float* dbeta, float* scratch,
+                              void* stream);
 /* dx = rstd * (dz*gamma - (gsums0 + xhat*gsums1) / (H*W*C/G)). */
 int pdac_groupnorm_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, int G, const float* stats,
                              const float* gamma, float eps, const float* gsums, const PdacView* dx, void* stream);
@@ -247,8 +263,9 @@ int pdac_dropout(const PdacView* x, const PdacView* y, float p, unsigned long lo
 /* Depthwise 3x3, stride 1, padding = dilation. w: fp32 [C][9] (the state_dict (C,1,3,3) tensor). flip = 1 applies the
  * transposed taps (data gradient). */
 int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int flip, const PdacView* y, void* stream);
-/* dw[c][r*3+s] += sum dy[n,h,w,c] * x[n, h+(r-1)*dil, w+(s-1)*dil, c] (fp32 atomics, caller zeroes). */
-int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, void* stream);
+/* dw[c][r*3+s] += sum dy[n,h,w,c] * x[n, h+(r-1)*dil, w+(s-1)*dil, c] (caller zeroes). scratch (fp32, >= 1184 * C * 9
+ * floats): reproducible fixed-order sum over the blocks; NULL: fp32 atomics. */
+int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, float* scratch, void* stream);
 
 /* ---- loss / metric / mask / stitch / optimiser (loss.cu) ---------------------------------------------------- */
 /* tgt_dtype: 0 = fp32, 1 = uint8. sums: 3 * (1 + PDAC_STAT_ROWS) doubles: [0..2] = (sum p*t, sum p, sum t), kept for

@@ -30,6 +30,11 @@ class PdacAugment(C.Structure):
                 ("p_color", C.c_float), ("p_geom", C.c_float), ("seed", C.c_ulonglong)]
 
 
+class PdacPackDesc(C.Structure):
+    _fields_ = [("w", C.c_void_p), ("wp_f", C.c_void_p), ("wp_t", C.c_void_p)] + \
+               [(n, C.c_int32) for n in ("O", "I", "R", "S", "wrows_f", "kf", "wrows_t", "kt", "s2_pad")]
+
+
 class PdacTap(C.Structure):
     _fields_ = [("src", C.c_int32), ("dh", C.c_int32), ("dw", C.c_int32)]
 
@@ -62,6 +67,7 @@ SIGNATURES = {
     "pdac_stem_prep_u8_augment": [_p, _p, _i, _i, _i, C.POINTER(_f), C.POINTER(_f), C.POINTER(PdacAugment), _p, _p, _p, _p,
                                   _p],
     "pdac_pack_conv_weight": [_p, _i, _i, _i, _i, _i, _i, _p, _i, _i, _p, _i, _p],
+    "pdac_pack_conv_weights_batched": [C.POINTER(PdacPackDesc), _i, _p],
     "pdac_pack_stem_weight": [_p, _i, _p, _p],
     "pdac_unpack_stem_wgrad": [_p, _i, _p, _p],
     "pdac_bn_prepare": [_p, _i, _d, _p, _p, _f, _f, _i, _p, _p, _p, _p, _p, _i, _p],
@@ -70,7 +76,7 @@ SIGNATURES = {
     "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],
     "pdac_relu_bwd_bias": [_VP, _VP, _VP, _p, _p, _p],
     "pdac_maxpool3x3s2_fwd": [_VP, _VP, _p, _p],
-    "pdac_maxpool3x3s2_bwd": [_VP, _p, _VP, _p],
+    "pdac_maxpool3x3s2_bwd": [_VP, _p, _VP, _VP, _p],
     "pdac_upsample_nearest2x_fwd": [_VP, _VP, _p],
     "pdac_upsample_nearest2x_bwd": [_VP, _VP, _VP, _p],
     "pdac_bilinear_fwd": [_VP, _i, _VP, _p],
@@ -80,13 +86,13 @@ SIGNATURES = {
     "pdac_adaptive_avgpool_fwd": [_VP, _VP, _p],
     "pdac_adaptive_avgpool_bwd": [_VP, _VP, _p],
     "pdac_add": [_VP, _VP, _i, _VP, _p],
-    "pdac_groupnorm_stats": [_VP, _i, _p, _p],
+    "pdac_groupnorm_stats": [_VP, _i, _p, _p, _p],
     "pdac_groupnorm_fwd": [_VP, _i, _p, _p, _p, _f, _i, _VP, _p],
-    "pdac_groupnorm_bwd_reduce": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _p, _p, _p],
+    "pdac_groupnorm_bwd_reduce": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _p, _p, _p, _p],
     "pdac_groupnorm_bwd_apply": [_VP, _VP, _VP, _i, _p, _p, _f, _p, _VP, _p],
     "pdac_dropout": [_VP, _VP, _f, C.c_ulonglong, _p, _i, _p],
     "pdac_dwconv3x3": [_VP, _p, _i, _i, _VP, _p],
-    "pdac_dwconv3x3_wgrad": [_VP, _VP, _i, _p, _p],
+    "pdac_dwconv3x3_wgrad": [_VP, _VP, _i, _p, _p, _p],
     "pdac_dice_fwd": [_p, _p, _i, _ll, _p, _f, _p, _p],
     "pdac_dice_bwd": [_p, _p, _i, _ll, _p, _f, _p, _p, _p],
     "pdac_sigmoid_mask": [_p, _ll, _p, _p, _p],

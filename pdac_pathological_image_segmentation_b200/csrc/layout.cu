@@ -4,6 +4,7 @@
 // (state_dict fp32 OIHW -> bf16 K-major GEMM matrices, and the stem's 7x7 s2 -> 4x4 s1 x 16ch rewrite).
 #include "common.h"
 #include "vec.cuh"
+#include <string.h>
 
 namespace pdac {
 
@@ -155,6 +156,46 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, int O, int 
   }
 }
 
+// Batched form: one launch re-packs up to kPackBatch weight tensors (blockIdx.y = tensor): after an optimizer step every
+// conv weight of the network is re-packed at once instead of by ~30 tiny launches inside the next forward.
+static constexpr int kPackBatch = 24;
+struct PackItem {
+  const float* w;
+  bf16* wf;
+  bf16* wt;
+  int O, I, RS, wrows_f, kf, wrows_t, kt;
+  int8_t pos[PDAC_MAX_TAPS];
+};
+struct PackBatch {
+  PackItem it[kPackBatch];
+};
+__global__ void __launch_bounds__(256) pack_conv_weight_batched_kernel(const __grid_constant__ PackBatch b) {
+  const PackItem& d = b.it[blockIdx.y];
+  const long long nf = d.wf ? (long long)d.RS * d.wrows_f * d.kf : 0;
+  const long long nt = d.wt ? (long long)d.RS * d.wrows_t * d.kt : 0;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < nf + nt; e += (long long)gridDim.x * blockDim.x) {
+    if (e < nf) {
+      const int i = (int)(e % d.kf);
+      const long long r = e / d.kf;
+      const int o = (int)(r % d.wrows_f);
+      const int t = (int)(r / d.wrows_f);
+      const float v = (o < d.O && i < d.I) ? d.w[((long long)o * d.I + i) * d.RS + t] : 0.f;
+      d.wf[e] = __float2bfloat16(v);
+    } else {
+      const long long e2 = e - nf;
+      const int o = (int)(e2 % d.kt);
+      const long long r = e2 / d.kt;
+      const int i = (int)(r % d.wrows_t);
+      const int tp = (int)(r / d.wrows_t);
+      int t = 0;
+      for (int k = 0; k < d.RS; ++k)
+        if (d.pos[k] == tp) t = k;
+      const float v = (o < d.O && i < d.I) ? d.w[((long long)o * d.I + i) * d.RS + t] : 0.f;
+      d.wt[e2] = __float2bfloat16(v);
+    }
+  }
+}
+
 // stem: w fp32 [64][3][7][7] -> [16 taps (a,b)][O][16] with channel (p*2+q)*3+c <- w[o][c][2a+p-1][2b+q-1]
 __global__ void pack_stem_weight_kernel(const float* __restrict__ w, int O, bf16* __restrict__ wp) {
   const int total = 16 * O * 16;
@@ -280,6 +321,53 @@ extern "C" int pdac_pack_conv_weight(const float* w, int O, int I, int R, int S,
   pack_conv_weight_kernel<<<ew_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(w, O, I, RS, wrows_f, kf, (bf16*)wp_f,
                                                                                wrows_t, kt, (bf16*)wp_t, perm);
   PDAC_LAUNCH_CHECK("pack_conv_weight");
+  return PDAC_OK;
+}
+
+static void s2_tap_positions(int R, int S, int s2_pad, int8_t* pos) {
+  for (int t = 0; t < PDAC_MAX_TAPS; ++t) pos[t] = (int8_t)t;
+  if (s2_pad < 0) return;
+  int p = 0;
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw)
+      for (int r = 0; r < R; ++r) {
+        if ((r - s2_pad - ph) & 1) continue;
+        for (int s = 0; s < S; ++s) {
+          if ((s - s2_pad - pw) & 1) continue;
+          pos[r * S + s] = (int8_t)p++;
+        }
+      }
+}
+
+extern "C" int pdac_pack_conv_weights_batched(const PdacPackDesc* descs, int n, void* stream) {
+  PDAC_REQUIRE(descs && n >= 0, "pack batch: null argument");
+  for (int base = 0; base < n; base += kPackBatch) {
+    PackBatch b;
+    memset(&b, 0, sizeof(b));
+    const int m = n - base < kPackBatch ? n - base : kPackBatch;
+    for (int j = 0; j < m; ++j) {
+      const PdacPackDesc& d = descs[base + j];
+      PDAC_REQUIRE(d.w && (d.wp_f || d.wp_t), "pack batch %d: null pointer", base + j);
+      const int RS = d.R * d.S;
+      PDAC_REQUIRE(RS >= 1 && RS <= PDAC_MAX_TAPS, "pack batch %d: kernel %dx%d unsupported", base + j, d.R, d.S);
+      PDAC_REQUIRE(!d.wp_f || (d.wrows_f >= d.O && d.kf >= d.I), "pack batch %d: forward wrows/k too small", base + j);
+      PDAC_REQUIRE(!d.wp_t || (d.wrows_t >= d.I && d.kt >= d.O), "pack batch %d: dgrad wrows/k too small", base + j);
+      PackItem& it = b.it[j];
+      it.w = d.w;
+      it.wf = (bf16*)d.wp_f;
+      it.wt = (bf16*)d.wp_t;
+      it.O = d.O;
+      it.I = d.I;
+      it.RS = RS;
+      it.wrows_f = d.wrows_f;
+      it.kf = d.kf;
+      it.wrows_t = d.wrows_t;
+      it.kt = d.kt;
+      s2_tap_positions(d.R, d.S, d.s2_pad, it.pos);
+    }
+    pack_conv_weight_batched_kernel<<<dim3(96, m), 256, 0, (cudaStream_t)stream>>>(b);
+    PDAC_LAUNCH_CHECK("pack_conv_weight_batched");
+  }
   return PDAC_OK;
 }
 

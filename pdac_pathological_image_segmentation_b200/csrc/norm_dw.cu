@@ -52,8 +52,9 @@ static ImgGrid img_grid(int npix, int C, int N) {
 
 // ------------------------------------------------------------------------------------------------ GroupNorm
 // stats[n][grp][0..1] += sum, sum of squares over the group's channels and the image's pixels
-__global__ void __launch_bounds__(256) gn_stats_kernel(ImgView x, int cpg, float* __restrict__ stats, int G, int cg,
-                                                       int ppb) {
+__global__ void __launch_bounds__(256) gn_stats_kernel(ImgView x, int cpg, float* __restrict__ stats,
+                                                       float* __restrict__ rows, int G, int cg, int ppb) {
+  extern __shared__ float s_grp[];  // [G][2] (deterministic path)
   IMG_SETUP(cg, ppb)
   float s[8], q[8];
 #pragma unroll
@@ -69,7 +70,9 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(ImgView x, int cpg, float
       }
     }
     float* st = stats + (long long)n * G * 2;
-    if (cpg >= 8) {
+    if (rows) {
+      // handled below (all threads of the block take part)
+    } else if (cpg >= 8) {
       float ss = 0.f, qq = 0.f;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -91,6 +94,44 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(ImgView x, int cpg, float
         atomicAdd(st + grp * 2 + 1, qq);
       }
     }
+  }
+  if (rows) {
+    // Reproducible form: the block's per-group sums are built in shared memory in a fixed order (one (pixel lane,
+    // thread-within-group) pair adds per round, so no two threads touch a slot in the same round) and stored as this
+    // block's row of the [blocks][N][G][2] table, which rows_sum adds over the blocks in index order.
+    for (int i = threadIdx.x; i < G * 2; i += blockDim.x) s_grp[i] = 0.f;
+    __syncthreads();
+    const int tpg = cpg >= 8 ? cpg / 8 : 1;
+    for (int round = 0; round < ppb * tpg; ++round) {
+      const int qq_ = round / tpg, jj = round - qq_ * tpg;
+      if (active && g < cg && pl == qq_ && (g % tpg) == jj) {
+        if (cpg >= 8) {
+          float ss = 0.f, qq = 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            ss += s[i];
+            qq += q[i];
+          }
+          const int grp = (g * 8) / cpg;
+          s_grp[grp * 2] += ss;
+          s_grp[grp * 2 + 1] += qq;
+        } else {
+          for (int i0 = 0; i0 < 8; i0 += cpg) {
+            float ss = 0.f, qq = 0.f;
+            for (int i = i0; i < i0 + cpg; ++i) {
+              ss += s[i];
+              qq += q[i];
+            }
+            const int grp = (g * 8 + i0) / cpg;
+            s_grp[grp * 2] += ss;
+            s_grp[grp * 2 + 1] += qq;
+          }
+        }
+      }
+      __syncthreads();
+    }
+    float* row = rows + ((size_t)blockIdx.x * gridDim.y + n) * G * 2;
+    for (int i = threadIdx.x; i < G * 2; i += blockDim.x) row[i] = s_grp[i];
   }
 }
 
@@ -137,7 +178,8 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(ImgView dy, ImgView 
                                                             const float* __restrict__ stats, int G,
                                                             const float* __restrict__ gamma, float eps,
                                                             float* __restrict__ gsums, float* __restrict__ dgamma,
-                                                            float* __restrict__ dbeta, int cg, int ppb) {
+                                                            float* __restrict__ dbeta, float* __restrict__ rows, int cg,
+                                                            int ppb) {
   __shared__ float red[256][17];
   IMG_SETUP(cg, ppb)
   float mean[8], rstd[8], a0[8], a1[8];
@@ -175,6 +217,10 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(ImgView dy, ImgView 
     float acc = 0.f;
     for (int q = 0; q < ppb; ++q) acc += red[q * cg + gg][slot];
     const int c = gg * 8 + (slot & 7);
+    if (rows) {  // reproducible form: raw per-channel sums of this block; gn_bwd_finalize adds the blocks in index order
+      rows[((size_t)blockIdx.x * gridDim.y + n) * 2 * dy.C + (slot < 8 ? 0 : dy.C) + c] = acc;
+      continue;
+    }
     const float ga = gamma[c];
     if (slot < 8) {
       atomicAdd(gs + (c / cpg) * 2, acc * ga);
@@ -183,6 +229,39 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(ImgView dy, ImgView 
       atomicAdd(gs + (c / cpg) * 2 + 1, acc * ga);
       if (dgamma) atomicAdd(dgamma + c, acc);
     }
+  }
+}
+
+// rows: [nbx][N][2][C] per-block raw sums (sum dz, sum dz*xhat per channel). One thread per (image, group) builds
+// gsums, one per channel accumulates dgamma / dbeta; blocks, images and channels are walked in index order.
+__global__ void gn_bwd_finalize_kernel(const float* __restrict__ rows, int nbx, int N, int C, int G,
+                                       const float* __restrict__ gamma, float* __restrict__ gsums,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int cpg = C / G;
+  if (t < N * G) {
+    const int n = t / G, grp = t - n * G;
+    float a0 = 0.f, a1 = 0.f;
+    for (int bx = 0; bx < nbx; ++bx) {
+      const float* r = rows + ((size_t)bx * N + n) * 2 * C;
+      for (int c = grp * cpg; c < (grp + 1) * cpg; ++c) {
+        a0 += r[c] * gamma[c];
+        a1 += r[C + c] * gamma[c];
+      }
+    }
+    gsums[(size_t)t * 2] = a0;
+    gsums[(size_t)t * 2 + 1] = a1;
+  } else if (t < N * G + C) {
+    const int c = t - N * G;
+    float b = 0.f, gm = 0.f;
+    for (int n = 0; n < N; ++n)
+      for (int bx = 0; bx < nbx; ++bx) {
+        const float* r = rows + ((size_t)bx * N + n) * 2 * C;
+        b += r[c];
+        gm += r[C + c];
+      }
+    if (dbeta) dbeta[c] += b;
+    if (dgamma) dgamma[c] += gm;
   }
 }
 
@@ -302,10 +381,27 @@ __global__ void __launch_bounds__(256) dw3x3_kernel(ImgView x, int H, int W, con
 // Block-level reduction of the per-thread 9 x 8 partial weight gradients in (dynamic) shared memory, then one global
 // atomic per (channel, tap) and block: the pixel lanes of a block share their channels, and 72 global atomics per
 // THREAD (5 M per call on 2.7 k addresses) were what the 304-channel layer's 3.3 ms consisted of.
-__device__ __forceinline__ void dw_flush(float (&acc)[9][8], bool active, int g, int cg, float* __restrict__ dw) {
+__device__ __forceinline__ void dw_flush(float (&acc)[9][8], bool active, int g, int pl, int ppb, int cg,
+                                         float* __restrict__ dw, float* __restrict__ rows) {
   extern __shared__ float s_dw[];  // [cg * 8 channels][9 taps]
   for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) s_dw[i] = 0.f;
   __syncthreads();
+  if (rows) {
+    // reproducible form: one pixel lane adds per round (distinct channel groups -> distinct slots), the block's row of
+    // the [blocks][C*9] table is added over the blocks in index order by rows_sum
+    for (int q = 0; q < ppb; ++q) {
+      if (active && pl == q) {
+#pragma unroll
+        for (int t = 0; t < 9; ++t)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s_dw[(g * 8 + i) * 9 + t] += acc[t][i];
+      }
+      __syncthreads();
+    }
+    float* row = rows + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * cg * 72;
+    for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) row[i] = s_dw[i];
+    return;
+  }
   if (active) {
 #pragma unroll
     for (int t = 0; t < 9; ++t)
@@ -318,7 +414,8 @@ __device__ __forceinline__ void dw_flush(float (&acc)[9][8], bool active, int g,
 
 // dw[c][r*3+s] += sum_{n,h,w} dy[n,h,w,c] * x[n, h+(r-1)*dil, w+(s-1)*dil, c]
 __global__ void __launch_bounds__(256) dw3x3_wgrad_kernel(ImgView x, ImgView dy, int H, int W, int dil,
-                                                          float* __restrict__ dw, int cg, int ppb) {
+                                                          float* __restrict__ dw, float* __restrict__ rows, int cg,
+                                                          int ppb) {
   IMG_SETUP(cg, ppb)
   float acc[9][8];
 #pragma unroll
@@ -344,7 +441,7 @@ __global__ void __launch_bounds__(256) dw3x3_wgrad_kernel(ImgView x, ImgView dy,
       }
     }
   }
-  dw_flush(acc, active, g, cg, dw);
+  dw_flush(acc, active, g, pl, ppb, cg, dw, rows);
 }
 
 // dilation 1 (DeepLabV3+ decoder: 304 channels at 128x128, the expensive one): a thread owns one image row and slides a
@@ -423,7 +520,8 @@ __global__ void __launch_bounds__(256, 2) dw3x3_d1_kernel(ImgView x, int H, int 
 // Weight gradient, dilation 1: a thread owns (channel group, image row, kernel row r) and slides three packed columns of
 // input row h + r - 1 against dy row h: 24 accumulators per thread (3 blocks / SM) instead of 72 (1 block / SM).
 __global__ void __launch_bounds__(256, 3) dw3x3_d1_wgrad_kernel(ImgView x, ImgView dy, int H, int W,
-                                                                float* __restrict__ dw, int cg, int ppb) {
+                                                                float* __restrict__ dw, float* __restrict__ out_rows,
+                                                                int cg, int ppb) {
   extern __shared__ float s_dw[];  // [cg * 8 channels][9 taps]
   for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) s_dw[i] = 0.f;
   __syncthreads();
@@ -459,6 +557,20 @@ __global__ void __launch_bounds__(256, 3) dw3x3_d1_wgrad_kernel(ImgView x, ImgVi
       c1 = c2;
     }
   }
+  if (out_rows) {  // reproducible form, see dw_flush: one image-row lane adds per round ((g, r) slots are distinct)
+    for (int q = 0; q < rows; ++q) {
+      if (lane_ok && rl == q) {
+#pragma unroll
+        for (int t = 0; t < 3; ++t)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s_dw[(g * 8 + i) * 9 + r * 3 + t] += acc[t][i];
+      }
+      __syncthreads();
+    }
+    float* row = out_rows + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * cg * 72;
+    for (int i = threadIdx.x; i < cg * 72; i += blockDim.x) row[i] = s_dw[i];
+    return;
+  }
   if (lane_ok) {
 #pragma unroll
     for (int t = 0; t < 3; ++t)
@@ -480,14 +592,16 @@ static int gn_check(const PdacView* x, int G, int* cpg) {
   return PDAC_OK;
 }
 
-extern "C" int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, void* stream) {
+extern "C" int pdac_groupnorm_stats(const PdacView* x, int G, float* stats, float* scratch, void* stream) {
   ImgView xv;
   int cpg = 0;
   PDAC_TRY(img_view(x, &xv, "groupnorm x"));
   PDAC_TRY(gn_check(x, G, &cpg));
   const ImgGrid g = img_grid(xv.npix, x->C, x->N);
-  gn_stats_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(xv, cpg, stats, G, g.cg, g.ppb);
+  gn_stats_kernel<<<g.grid, 256, scratch ? (size_t)G * 2 * sizeof(float) : 0, (cudaStream_t)stream>>>(
+      xv, cpg, stats, scratch, G, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("gn_stats_kernel");
+  if (scratch) PDAC_TRY(rows_sum(scratch, (int)g.grid.x, x->N * G * 2, stats, 0, (cudaStream_t)stream));
   return PDAC_OK;
 }
 
@@ -506,7 +620,7 @@ extern "C" int pdac_groupnorm_fwd(const PdacView* x, int G, const float* stats, 
 
 extern "C" int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, const PdacView* x, int G,
                                          const float* stats, const float* gamma, float eps, float* gsums, float* dgamma,
-                                         float* dbeta, void* stream) {
+                                         float* dbeta, float* scratch, void* stream) {
   ImgView dv, yv, xv;
   int cpg = 0;
   PDAC_TRY(img_view(dy, &dv, "groupnorm dy"));
@@ -516,8 +630,14 @@ extern "C" int pdac_groupnorm_bwd_reduce(const PdacView* dy, const PdacView* y, 
   PDAC_TRY(gn_check(x, G, &cpg));
   const ImgGrid g = img_grid(xv.npix, x->C, x->N);
   gn_bwd_reduce_kernel<<<g.grid, 256, 0, (cudaStream_t)stream>>>(dv, yv, xv, cpg, stats, G, gamma, eps, gsums, dgamma,
-                                                                 dbeta, g.cg, g.ppb);
+                                                                 dbeta, scratch, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("gn_bwd_reduce_kernel");
+  if (scratch) {
+    const int work = x->N * G + x->C;
+    gn_bwd_finalize_kernel<<<ceil_div(work, 128), 128, 0, (cudaStream_t)stream>>>(scratch, (int)g.grid.x, x->N, x->C, G,
+                                                                                gamma, gsums, dgamma, dbeta);
+    PDAC_LAUNCH_CHECK("gn_bwd_finalize_kernel");
+  }
   return PDAC_OK;
 }
 
@@ -568,27 +688,32 @@ extern "C" int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int fl
   return PDAC_OK;
 }
 
-extern "C" int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, void* stream) {
+extern "C" int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, float* scratch,
+                                    void* stream) {
   ImgView xv, dv;
   PDAC_TRY(img_view(x, &xv, "dwconv x"));
   PDAC_TRY(img_view(dy, &dv, "dwconv dy"));
   PDAC_REQUIRE(x->H == dy->H && x->W == dy->W && x->C == dy->C && x->N == dy->N && dil >= 1, "dwconv: shape mismatch");
   ImgGrid g = img_grid(xv.npix, x->C, x->N);
-  // fewer, longer-running blocks: every thread ends with 72 atomics
+  // fewer, longer-running blocks: every thread ends with 72 accumulators to hand over
   int cap = (num_sms() * 2 + x->N - 1) / x->N;
   if (cap < 1) cap = 1;
   if ((int)g.grid.x > cap) g.grid.x = cap;
   const size_t smem = (size_t)g.cg * 72 * sizeof(float);
   PDAC_REQUIRE(smem <= 48 * 1024, "dwconv wgrad: too many channels (%d)", x->C);
+  const int ncols = g.cg * 72;  // == C * 9
   if (dil == 1 && x->W >= 16 && g.ppb >= 3) {
     int bands = ceil_div(x->H, g.ppb / 3);
     int per_img = (num_sms() * 6 + x->N - 1) / x->N;  // ~6 blocks per SM in total, each walking whole rows
     if (per_img > bands) per_img = bands;
-    dw3x3_d1_wgrad_kernel<<<dim3(per_img, x->N), 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dw, g.cg, g.ppb);
+    dw3x3_d1_wgrad_kernel<<<dim3(per_img, x->N), 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dw, scratch,
+                                                                                    g.cg, g.ppb);
     PDAC_LAUNCH_CHECK("dw3x3_d1_wgrad_kernel");
+    if (scratch) PDAC_TRY(rows_sum(scratch, per_img * x->N, ncols, dw, 1, (cudaStream_t)stream));
     return PDAC_OK;
   }
-  dw3x3_wgrad_kernel<<<g.grid, 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dil, dw, g.cg, g.ppb);
+  dw3x3_wgrad_kernel<<<g.grid, 256, smem, (cudaStream_t)stream>>>(xv, dv, x->H, x->W, dil, dw, scratch, g.cg, g.ppb);
   PDAC_LAUNCH_CHECK("dw3x3_wgrad_kernel");
+  if (scratch) PDAC_TRY(rows_sum(scratch, (int)g.grid.x * x->N, ncols, dw, 1, (cudaStream_t)stream));
   return PDAC_OK;
 }

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(V4 x, V4 y, uint8_t* _
 
 // One thread produces the 2x2 block (2i+a, 2j+b) of dx for 8 channels: those four pixels are covered by the windows
 // (i,j), (i,j+1), (i+1,j), (i+1,j+1) only, so each window's arg-max bytes and gradient are loaded once for four outputs.
-__global__ void __launch_bounds__(256) maxpool_bwd_kernel(V4 dy, const uint8_t* __restrict__ idx, V4 dx) {
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(V4 dy, const uint8_t* __restrict__ idx, V4 add, V4 dx) {
   const int cg = dx.C / 8;
   const int bh = (dx.H + 1) >> 1, bw = (dx.W + 1) >> 1;
   const long long total = (long long)dx.N * bh * bw * cg;
@@ -136,6 +136,11 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(V4 dy, const uint8_t* 
         F8 o;
 #pragma unroll
         for (int i = 0; i < 8; ++i) o.v[i] = acc[pa * 2 + pb][i];
+        if (add.ptr) {  // gradient already accumulated at this tensor by another consumer (skip connection)
+          const F8 a = unpack8(ld16(add.at(n, hh, ww) + g * 8));
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o.v[i] += a.v[i];
+        }
         st16(dx.at(n, hh, ww) + g * 8, pack8(o));
       }
   }
@@ -497,16 +502,21 @@ extern "C" int pdac_maxpool3x3s2_fwd(const PdacView* x, const PdacView* y, uint8
   PDAC_LAUNCH_CHECK("maxpool_fwd");
   return PDAC_OK;
 }
-extern "C" int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, const PdacView* dx, void* stream) {
-  V4 vdy, vdx;
+extern "C" int pdac_maxpool3x3s2_bwd(const PdacView* dy, const uint8_t* idx, const PdacView* addend, const PdacView* dx,
+                                     void* stream) {
+  V4 vdy, vdx, va = {nullptr, 0, 0, 0, 0, 0, 0, 0};
   PDAC_TRY(to_v4(dy, &vdy, "dy"));
   PDAC_TRY(to_v4(dx, &vdx, "dx"));
+  if (addend) {
+    PDAC_TRY(to_v4(addend, &va, "addend"));
+    PDAC_REQUIRE(va.N == vdx.N && va.H == vdx.H && va.W == vdx.W && va.C == vdx.C, "maxpool bwd: addend shape mismatch");
+  }
   PDAC_REQUIRE(idx, "maxpool bwd: null idx");
   PDAC_REQUIRE(vdy.N == vdx.N && vdy.C == vdx.C && vdy.H == (vdx.H - 1) / 2 + 1 && vdy.W == (vdx.W - 1) / 2 + 1,
                "maxpool bwd: shape mismatch");
   const long long total = (long long)vdx.N * ((vdx.H + 1) / 2) * ((vdx.W + 1) / 2) * (vdx.C / 8);
   if (!total) return PDAC_OK;
-  maxpool_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vdy, idx, vdx);
+  maxpool_bwd_kernel<<<blocks_for(total), 256, 0, (cudaStream_t)stream>>>(vdy, idx, va, vdx);
   PDAC_LAUNCH_CHECK("maxpool_bwd");
   return PDAC_OK;
 }

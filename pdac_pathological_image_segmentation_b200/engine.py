@@ -23,29 +23,51 @@ def pad16(c):
 # ------------------------------------------------------------------------------------------------ packed weights
 class PackCache:
     """bf16 K-major copies of the fp32 state_dict weights in the layouts the tcgen05 kernels read (ops.pack_*),
-    refreshed when a parameter's storage or version counter changes (optimizer.step / load_state_dict / .to())."""
+    refreshed when a parameter's storage or version counter changes (optimizer.step / load_state_dict / .to()).
+    The trainer, which updates parameters through raw pointers, calls refresh() after its optimizer step: every cached
+    copy is re-packed IN PLACE (same buffers, so a captured CUDA graph stays valid), the conv weights by one batched
+    launch."""
 
     def __init__(self):
         self._c = {}
 
     def invalidate(self):
-        """Forget every packed copy (the trainer updates parameters through raw pointers, which bumps no version)."""
+        """Forget every packed copy (parameters changed behind torch's version counters, e.g. a checkpoint load)."""
         self._c.clear()
 
-    def _get(self, key, params, build):
+    def refresh(self):
+        """Re-pack every cached copy from the current parameter values into its existing buffers."""
+        recipes = []
+        for key, (sig, val, redo) in self._c.items():
+            r = redo()
+            if r is not None:
+                recipes.append(r)
+        ops.pack_conv_weights_batched(recipes)
+
+    def _get(self, key, params, build, redo):
         sig = tuple((p.data_ptr(), p._version) for p in params if p is not None)
         hit = self._c.get(key)
-        if hit is not None and hit[0] == sig:
-            return hit[1]
+        if hit is not None:
+            if hit[0] == sig:
+                return hit[1]
+            if tuple(s[0] for s in hit[0]) == tuple(s[0] for s in sig):
+                # same storage, new values (optimizer.step / load_state_dict): re-pack into the existing buffers, which
+                # a captured CUDA graph may have baked in
+                r = hit[2]()
+                if r is not None:
+                    ops.pack_conv_weights_batched([r])
+                self._c[key] = (sig, hit[1], hit[2])
+                return hit[1]
         val = build()
-        self._c[key] = (sig, val)
+        self._c[key] = (sig, val, lambda: redo(val))
         return val
 
     def conv(self, m: Conv2d, want_dgrad=True):
         """-> (wp_f [R*S*wrows][Cin], wp_t [R*S*wrows_t][pad16(Cout)] or None, bias padded to pad16(Cout) or None)."""
+        cpad = pad16(m.cout)
+
         def build():
             w = m.weight.detach()
-            cpad = pad16(m.cout)
             wp_f, wp_t = ops.pack_conv_weight(w.contiguous(), want_fwd=True, want_dgrad=want_dgrad, stride=m.stride,
                                               pad=m.padding, cout_pad=cpad)
             bias = None
@@ -59,16 +81,29 @@ class PackCache:
                     bias = torch.zeros(cpad, dtype=F32, device=w.device)
                     bias[:m.cout].copy_(m.bias.detach())
             return wp_f, wp_t, bias
-        return self._get((id(m), want_dgrad), (m.weight, m.bias), build)
+
+        def redo(val):
+            wp_f, wp_t, bias = val
+            if bias is not None and bias.data_ptr() != m.bias.data_ptr():
+                bias[:m.cout].copy_(m.bias.detach())          # private zero-padded copy (module path only)
+            return ops.conv_pack_recipe(m.weight.detach(), wp_f, wp_t, stride=m.stride, pad=m.padding, cout_pad=cpad)
+        return self._get((id(m), want_dgrad), (m.weight, m.bias), build, redo)
 
     def convt(self, m: ConvTranspose2d):
         def build():
             wp_f, wp_t = ops.pack_convt_weight(m.weight.detach().contiguous())
             return wp_f, wp_t, m.bias.detach()
-        return self._get((id(m), "t"), (m.weight, m.bias), build)
+
+        def redo(val):
+            ops.pack_convt_weight(m.weight.detach(), wp_f=val[0], wp_t=val[1])
+            return None
+        return self._get((id(m), "t"), (m.weight, m.bias), build, redo)
 
     def stem(self, m: Conv2d):
-        return self._get((id(m), "stem"), (m.weight,), lambda: ops.pack_stem_weight(m.weight.detach().contiguous()))
+        def redo(val):
+            ops.pack_stem_weight(m.weight.detach(), wp=val)
+            return None
+        return self._get((id(m), "stem"), (m.weight,), lambda: ops.pack_stem_weight(m.weight.detach().contiguous()), redo)
 
 
 # ------------------------------------------------------------------------------------------------ gradient arena
@@ -289,7 +324,8 @@ def maxpool(tape: Tape, x):
     def bwd():
         dy = tape.pop(y)
         if dy is not None:
-            tape.put(x, ops.maxpool_bwd(dy, idx, (x.shape[1], x.shape[2])))
+            old = tape.pop(x)        # e.g. the decoder's skip-connection gradient: added inside the scatter pass
+            tape.put(x, ops.maxpool_bwd(dy, idx, (x.shape[1], x.shape[2]), addend=old))
     tape.record(bwd)
     return y
 

@@ -277,6 +277,23 @@ def pack_conv_weight(w, want_fwd=True, want_dgrad=True, stride=1, pad=0, cout_pa
     return wp_f, wp_t
 
 
+def conv_pack_recipe(w, wp_f, wp_t, stride=1, pad=0, cout_pad=None):
+    """Descriptor of one pack_conv_weight call (for pack_conv_weights_batched): same arguments, given buffers."""
+    O, I, R, S = w.shape
+    opad = cout_pad or O
+    return _lib.PdacPackDesc(w.data_ptr(), wp_f.data_ptr() if wp_f is not None else None,
+                             wp_t.data_ptr() if wp_t is not None else None, O, I, R, S, wrows_for(opad), I,
+                             wrows_for(I), opad, pad if stride == 2 else -1)
+
+
+def pack_conv_weights_batched(recipes):
+    """Re-packs many conv weights into their existing bf16 buffers with one launch per 24 tensors."""
+    if not recipes:
+        return
+    arr = (_lib.PdacPackDesc * len(recipes))(*recipes)
+    call("pdac_pack_conv_weights_batched", arr, len(recipes), _stream())
+
+
 def pack_convt_weight(w, wp_f=None, wp_t=None):
     """nn.ConvTranspose2d weight fp32 [Cin, Cout, 2, 2] -> (forward matrix [4*wrows(Cout), Cin], dgrad matrix
     [4*wrows(Cin), Cout])."""
@@ -461,9 +478,10 @@ def maxpool_fwd(x, want_idx=True):
     return y, idx
 
 
-def maxpool_bwd(dy, idx, in_hw):
+def maxpool_bwd(dy, idx, in_hw, addend=None):
+    """dx = scatter of dy to the arg-max positions (+ addend, a gradient already accumulated at the same tensor)."""
     dx = empty_act(dy.shape[0], in_hw[0], in_hw[1], dy.shape[3], dy.device)
-    call("pdac_maxpool3x3s2_bwd", _vp(dy), _ptr(idx), _vp(dx), _stream())
+    call("pdac_maxpool3x3s2_bwd", _vp(dy), _ptr(idx), _vp(addend), _vp(dx), _stream())
     return dx
 
 
@@ -529,7 +547,7 @@ def adaptive_avgpool_bwd(dy, in_hw):
 def groupnorm_fwd(x, groups, gamma, beta, eps, relu, out=None):
     """-> (y, stats fp32 [N, G, 2] kept for backward)."""
     stats = torch.zeros((x.shape[0], groups, 2), dtype=torch.float32, device=x.device)
-    call("pdac_groupnorm_stats", _vp(x), groups, _ptr(stats), _stream())
+    call("pdac_groupnorm_stats", _vp(x), groups, _ptr(stats), _scratch_args(x.device)[0], _stream())
     if out is None:
         out = torch.empty_like(x)
     call("pdac_groupnorm_fwd", _vp(x), groups, _ptr(stats), _ptr(gamma), _ptr(beta), eps, int(bool(relu)), _vp(out),
@@ -541,7 +559,7 @@ def groupnorm_bwd(dy, y, x, groups, stats, gamma, eps, dgamma=None, dbeta=None, 
     """dz = dy * (y > 0) when y is given; returns dx, accumulates dgamma / dbeta."""
     gsums = torch.zeros((x.shape[0], groups, 2), dtype=torch.float32, device=x.device)
     call("pdac_groupnorm_bwd_reduce", _vp(dy), _vp(y), _vp(x), groups, _ptr(stats), _ptr(gamma), eps, _ptr(gsums),
-         _ptr(dgamma), _ptr(dbeta), _stream())
+         _ptr(dgamma), _ptr(dbeta), _scratch_args(x.device)[0], _stream())
     if out is None:
         out = torch.empty_like(dy)
     call("pdac_groupnorm_bwd_apply", _vp(dy), _vp(y), _vp(x), groups, _ptr(stats), _ptr(gamma), eps, _ptr(gsums),
@@ -571,7 +589,7 @@ def dwconv3x3(x, w, dil=1, flip=False, out=None):
 
 def dwconv3x3_wgrad(x, dy, dil, out):
     """out: fp32 (C, 1, 3, 3) gradient slot (accumulated into)."""
-    call("pdac_dwconv3x3_wgrad", _vp(x), _vp(dy), int(dil), _ptr(out), _stream())
+    call("pdac_dwconv3x3_wgrad", _vp(x), _vp(dy), int(dil), _ptr(out), _scratch_args(x.device)[0], _stream())
     return out
 
 

@@ -187,7 +187,7 @@ class TrainStep:
 
     def optimizer_step(self):
         ops.adam_step_dev(self.flat_params, self.arena.flat, self.exp_avg, self.exp_avg_sq, self.hyper, self.step_dev)
-        self.model._packs.invalidate()
+        self.model._packs.refresh()     # bf16 GEMM copies of every weight, re-packed in place by one batched launch
 
     def _whole_step(self, img_u8, mask_u8, aug, comm=True):
         out = self.forward_backward(img_u8, mask_u8, aug, reduce=comm)
@@ -225,7 +225,6 @@ class TrainStep:
             self._capture()
         self._g.replay()
         _lib.launches += self._g_launches
-        self.model._packs.invalidate()
         if not self._comm_in_graph:
             self.reducer.allreduce_sum()
             self.optimizer_step()
@@ -261,8 +260,7 @@ class TrainStep:
         was_training = model.training
         model.eval()
         try:
-            model._packs.invalidate()
-            z, mask = ops.stem_prep_u8(img_u8, mask_u8, None)
+            z, mask = ops.stem_prep_u8(img_u8, mask_u8, None)      # the packed weights are current: refreshed by every step
             logits, _ = model._run(Tape(model._packs, False, None), z)
             _, counts = ops.dice_score(logits, mask, pred_is_logits=True)
         finally:
@@ -291,7 +289,7 @@ class TrainStep:
                 raise RuntimeError(f"checkpoint does not match the model: missing {missing[:3]}, unexpected {extra[:3]}")
             for k, t in own.items():
                 t.copy_(sd[k])          # in place: the parameters keep living in the flat arena
-        self.model._packs.invalidate()
+        self.model._packs.refresh()     # in place as well: a captured graph keeps pointing at the same packed buffers
         if "optimizer" in ckpt:
             self.optimizer.load_state_dict(ckpt["optimizer"])
         self._sync_hyper()

@@ -120,6 +120,11 @@ def test_maxpool3x3s2(shape):
     dx = ops.maxpool_bwd(_nhwc(dy), idx, (H, W))
     # ties between equal bf16 values may pick another tap: compare where the window max is unique
     _close(_nchw(dx), xr.grad, "maxpool bwd", rel=2.0 ** -6, abs_=1e-3)
+    # with an addend (the gradient a skip connection left at the same tensor), here a channel slice of a wider tensor
+    wide = _nhwc(_rnd(N, 2 * C, H, W, seed=3))
+    add = wide[..., C:]
+    dx2 = ops.maxpool_bwd(_nhwc(dy), idx, (H, W), addend=add)
+    _close(_nchw(dx2), xr.grad + _nchw(add).float(), "maxpool bwd + addend", rel=2.0 ** -6, abs_=1e-3)
 
 
 def test_nearest2x():
