@@ -50,6 +50,14 @@ struct WhParams {
   int ckb, nboxb, block_n;
   uint32_t pitch_a, layout_a, pitch_b, layout_b, idesc, tmem_cols;
   int tiles_w, tiles_h, n_kblocks;
+  // K block = 16 pixels x tile_rows rows (one MMA K step per row). Row-shift mode (16 / 32-channel tensors, see
+  // wgrad_halo_try): the kernel-row offsets are taken on the dY side, so dY is the haloed operand in h: its box has
+  // b_rows = tile_rows + eh rows and starts b_row0 rows above the tile; column group i of the accumulator belongs to
+  // kernel row rs_tap_r[i] and A sub-block j to kernel column j: tap = rs_tap[i * 8 + j].
+  int tile_rows, b_rows, b_row0, b_tx_bytes, b_tile_bytes;
+  int rowshift, rs_cout;
+  uint32_t lbo_b;
+  int8_t rs_tap[64];
   float* dw;
   long long tap_stride, a_stride, b_stride;
   int Cout;
@@ -79,8 +87,8 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   const int a_stage = p.a_buf * p.cps;
-  const int b_box = 128 * (int)p.pitch_b;
-  const int b_tile = b_box * p.nboxb;
+  const int b_box = p.b_tile_bytes / p.nboxb;
+  const int b_tile = p.b_tile_bytes;
   uint8_t* smem_b = smem + (size_t)p.stages_a * a_stage;
 
   const int slab0 = blockIdx.y * p.spc;
@@ -125,12 +133,13 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
         kb /= p.tiles_w;
         const int tile_h = kb % p.tiles_h;
         const int img = kb / p.tiles_h;
-        const int w0 = tile_w * 16, h0 = tile_h * 8;
+        const int w0 = tile_w * 16, h0 = tile_h * p.tile_rows;
         const int bs = i & 1;
         mbar_wait(&emptyB[bs], ((i >> 1) & 1) ^ 1, p.err);
-        mbar_expect_tx(&fullB[bs], (uint32_t)b_tile);
+        mbar_expect_tx(&fullB[bs], (uint32_t)p.b_tx_bytes);
         for (int j = 0; j < p.nboxb; ++j)
-          tma_load_4d(smem_b + (size_t)bs * b_tile + (size_t)j * b_box, &maps.dy, &fullB[bs], n0 + j * p.ckb, w0, h0, img);
+          tma_load_4d(smem_b + (size_t)bs * b_tile + (size_t)j * b_box, &maps.dy, &fullB[bs], n0 + j * p.ckb, w0,
+                      h0 + p.b_row0, img);
         for (int cg = cg_lo; cg <= cg_hi; ++cg) {
           mbar_wait(&emptyA[stage], phase ^ 1, p.err);
           const int c_first = cg * p.cps;
@@ -156,7 +165,8 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
     const uint32_t ka16 = ((uint32_t)p.PW * p.pitch_a) >> 4;  // next tile row of the halo raster
     const uint32_t kb16 = (16 * p.pitch_b) >> 4;              // next 16 pixels of the dense dY tile
     const uint32_t a_lo0 = smem_u32(smem) >> 4;
-    const uint32_t b_lo0 = smem_desc_lo(smem_u32(smem_b), (uint32_t)b_box);
+    const uint32_t b_lo0 = smem_desc_lo(smem_u32(smem_b), p.lbo_b);
+    const int ksteps = p.tile_rows;
     const uint32_t a_stage16 = (uint32_t)a_stage >> 4, b_tile16 = (uint32_t)b_tile >> 4;
     const uint32_t block_n = (uint32_t)p.block_n;
     const int stages_a = p.stages_a;
@@ -179,6 +189,11 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
             umma_bf16_lohi(td, a_lo, hi_a, b_lo, hi_b, idesc, i > 0 ? 1u : 0u);
 #pragma unroll
             for (int k = 1; k < 8; ++k) umma_bf16_lohi(td, a_lo + k * ka16, hi_a, b_lo + k * kb16, hi_b, idesc, 1u);
+            for (int k0 = 8; k0 < ksteps; k0 += 8) {  // taller K blocks (row-shift mode): 8 more rows per trip
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                umma_bf16_lohi(td, a_lo + (k0 + k) * ka16, hi_a, b_lo + (k0 + k) * kb16, hi_b, idesc, 1u);
+            }
           }
           umma_commit(&emptyA[stage]);
         }
@@ -200,6 +215,31 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
       tc_fence_after();
       const int sub = m / p.ck, within = m - sub * p.ck;
       const int nch = min(p.block_n, p.Cout - n0);
+      if (p.rowshift) {
+        // accumulator column c = (kernel-row group i, output channel b), row m = (kernel column j = sub, input channel)
+        for (int s = slab0; s < slab1; ++s) {
+          const int a_ch = p.slabs[s].sub_c[sub] * p.ck + within;
+          for (int c = 0; c < p.block_n; c += 16) {
+            uint32_t v[16];
+            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((s - slab0) * p.block_n + c), v);
+            tmem_ld_wait();
+            const int gi = c / p.rs_cout, b0 = c - gi * p.rs_cout;
+            const int t = p.slabs[s].sub_t[sub] >= 0 ? p.rs_tap[gi * 8 + sub] : -1;
+            if (t < 0) continue;
+            if (p.part) {
+              float* pb = p.part + (long long)blockIdx.x * p.part_stride + ((long long)t * p.Cout + b0) * p.part_A + a_ch;
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (b0 + i < p.Cout) pb[(long long)i * p.part_A] = __uint_as_float(v[i]);
+            } else {
+              float* base = p.dw + (long long)t * p.tap_stride + (long long)a_ch * p.a_stride + (long long)b0 * p.b_stride;
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if (b0 + i < p.Cout) atomicAdd(base + (long long)i * p.b_stride, __uint_as_float(v[i]));
+            }
+          }
+        }
+      } else
       for (int s = slab0; s < slab1; ++s) {
         const int t = p.slabs[s].sub_t[sub];
         const bool rvalid = t >= 0;
@@ -274,10 +314,43 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   if (ck < 16 || dy->C % 16) return PDAC_OK;
   const int cout = dy->C;
   if (cout > 128 && cout % 128) return PDAC_OK;
-  const int block_n = cout > 128 ? 128 : cout;  // wider outputs: 128-column pieces over grid.z (dY is split, X re-read)
+  int block_n = cout > 128 ? 128 : cout;  // wider outputs: 128-column pieces over grid.z (dY is split, X re-read)
   const int zgroups = cout / block_n;
   int ckb = 64;
   while (cout % ckb) ckb >>= 1;
+
+  // Row-shift mode for 16 / 32-channel tensors (the 512^2 and 256^2 decoder layers). With ck <= 32 an M = 128 slab holds
+  // only the taps of ONE kernel row (3 x 16 or 3 x 32 of its 128 rows), i.e. three MMAs per 16 pixels, each costing
+  // ~32 + N/4 cycles whatever N is (scripts/probe/mma_rate.cu) - the layer is MMA-issue bound at a third of its HBM
+  // rate. Here the kernel-ROW offsets move to the dY operand: dY is loaded with the h halo, the accumulator's N
+  // dimension becomes (kernel row, output channel) = 3 x Cout columns through B sub-blocks one image row apart (LBO),
+  // and the A operand keeps the kernel columns as sub-blocks one pixel apart: ONE MMA per 16 pixels covers all taps.
+  static int rs_ok = -1;
+  if (rs_ok < 0) {
+    const char* e = getenv("PDAC_WGRAD_ROWSHIFT");
+    rs_ok = (e && e[0] == '0') ? 0 : 1;
+  }
+  int rs = 0, rs_R = 0, rs_S = 0, rs_d = 1;
+  if (rs_ok && ck <= 32 && cout == ckb && zgroups == 1) {
+    int S = 1;
+    while (S < tc->n_taps && tc->taps[S].dh == tc->taps[0].dh) ++S;
+    const int Rr = tc->n_taps / S;
+    if (Rr * S == tc->n_taps && Rr <= 8 && S <= 8) {
+      int d = S > 1 ? tc->taps[1].dw - tc->taps[0].dw : (Rr > 1 ? tc->taps[S].dh - tc->taps[0].dh : 1);
+      bool grid_ok = d > 0;
+      for (int t = 0; t < tc->n_taps && grid_ok; ++t)
+        grid_ok = tc->taps[t].dh == dh_min + (t / S) * d && tc->taps[t].dw == dw_min + (t % S) * d;
+      const int n_chunks_ = views[0].C / ck + (tc->n_cat > 1 ? views[1].C / ck : 0);
+      if (grid_ok && S * ck <= 128 && Rr * cout <= 256 && n_chunks_ * Rr * cout <= 512 && n_chunks_ <= kWhMaxSlabs &&
+          d * 16 * ckb * 2 < (1 << 18)) {
+        rs = 1;
+        rs_R = Rr;
+        rs_S = S;
+        rs_d = d;
+        block_n = Rr * cout;
+      }
+    }
+  }
 
   WhMaps maps;
   WhParams p;
@@ -286,13 +359,38 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   p.chunks0 = views[0].C / ck;
   p.n_chunks = p.chunks0 + (tc->n_cat > 1 ? views[1].C / ck : 0);
   p.PW = 16 + ew;
-  p.R = 8 + eh;
-  p.dh_min = dh_min;
-  p.dw_min = dw_min;
   p.pitch_a = ck * 2;
   p.layout_a = swizzle_layout_type(p.pitch_a);
   p.pitch_b = ckb * 2;
   p.layout_b = swizzle_layout_type(p.pitch_b);
+  p.dw_min = dw_min;
+  p.rowshift = rs;
+  if (rs) {
+    // K block = 16 pixels x tile_rows rows: as tall as three A stages + two dY tiles allow with two CTAs per SM
+    int tr = 32;
+    while (tr > 8 && (tr > dy->H || ((tr * p.PW * (int)p.pitch_a + 1023) & ~1023) * 3 +
+                                        2 * (((tr + eh) * 16 * (int)p.pitch_b + 1023) & ~1023) + 2048 > 104 * 1024))
+      tr >>= 1;
+    p.tile_rows = tr;
+    p.R = tr;           // the source box has no h halo in this mode ...
+    p.dh_min = 0;
+    p.b_rows = tr + eh; // ... dY has it
+    p.b_row0 = -dh_max;
+    p.b_tx_bytes = p.b_rows * 16 * (int)p.pitch_b;
+    p.b_tile_bytes = (p.b_tx_bytes + 1023) & ~1023;
+    p.lbo_b = (uint32_t)(rs_d * 16 * (int)p.pitch_b);
+    p.rs_cout = cout;
+    for (int i = 0; i < 8; ++i)
+      for (int j = 0; j < 8; ++j) p.rs_tap[i * 8 + j] = (int8_t)((i < rs_R && j < rs_S) ? (rs_R - 1 - i) * rs_S + j : -1);
+  } else {
+    p.tile_rows = 8;
+    p.R = 8 + eh;
+    p.dh_min = dh_min;
+    p.b_rows = 8;
+    p.b_row0 = 0;
+    p.b_tx_bytes = p.b_tile_bytes = 128 * block_n * 2;
+    p.lbo_b = 128u * p.pitch_b;
+  }
   p.a_buf = (p.R * p.PW * (int)p.pitch_a + 1023) & ~1023;
   p.cps = (ck == 64 && p.n_chunks >= 2) ? 2 : 1;
   p.n_cg = ceil_div(p.n_chunks, p.cps);
@@ -326,6 +424,17 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   for (int cg = 0; cg < p.n_cg; ++cg) {
     const int c_first = cg * p.cps;
     const int nc = p.n_chunks - c_first < p.cps ? p.n_chunks - c_first : p.cps;
+    if (rs) {  // one slab per channel chunk: sub-block j = kernel column j (rs_d pixels apart), all kernel rows at once
+      WhSlab* sl = new_slab(cg);
+      if (!sl) return PDAC_OK;
+      sl->a_off16 = 0;
+      sl->lbo16 = (uint32_t)(rs_d * (int)p.pitch_a) >> 4;
+      for (int j = 0; j < 8; ++j) {
+        sl->sub_t[j] = (int8_t)(j < rs_S ? 0 : -1);
+        sl->sub_c[j] = (int8_t)c_first;
+      }
+      continue;
+    }
     if (ck == 64 && nc == 2) {
       for (int i = 0; i < tc->n_taps; ++i) {  // M = (tap; chunk c_first | chunk c_first + 1)
         WhSlab* s = new_slab(cg);
@@ -384,7 +493,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   int dual = dual_ok && (ns * block_n <= 256 || (block_n <= 64 && ns * block_n <= 512) || dual_ok == 2);
   {
     const int a_stage_ = p.a_buf * p.cps;
-    if (dual && (104 * 1024 - 2 * 128 * block_n * 2 - 1024) / a_stage_ < 3) dual = 0;
+    if (dual && (104 * 1024 - 2 * p.b_tile_bytes - 1024) / a_stage_ < 3) dual = 0;
   }
   int spc_max = (dual ? 256 : 512) / block_n;
   if (spc_max > ns) spc_max = ns;
@@ -392,11 +501,11 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   p.spc = ceil_div(ns, ygroups);
   p.tmem_cols = pow2_ceil(p.spc * block_n < 32 ? 32 : p.spc * block_n);
   p.ckb = ckb;
-  p.nboxb = block_n / ckb;
+  p.nboxb = rs ? 1 : block_n / ckb;
   p.block_n = block_n;
   p.idesc = make_idesc_bf16(128, block_n, 1, 1);
   p.tiles_w = ceil_div(dy->W, 16);
-  p.tiles_h = ceil_div(dy->H, 8);
+  p.tiles_h = ceil_div(dy->H, p.tile_rows);
   p.n_kblocks = p.tiles_w * p.tiles_h * dy->N;
   p.dw = dw;
   p.tap_stride = tap_stride;
@@ -404,7 +513,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   p.b_stride = b_stride;
   p.Cout = b_valid > 0 ? b_valid : cout;
   p.err = device_err_flag();
-  const int b_tile = 128 * block_n * 2;
+  const int b_tile = p.b_tile_bytes;
   const int a_stage = p.a_buf * p.cps;
   int stages_a = ((dual ? 104 : 220) * 1024 - 2 * b_tile - 1024) / a_stage;
   if (stages_a > kWhMaxStages) stages_a = kWhMaxStages;
@@ -412,7 +521,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   p.stages_a = stages_a;
   for (int s = 0; s < tc->n_cat; ++s) PDAC_TRY(encode_view_map(&maps.a[s], &views[s], ck, p.PW, p.R, 1));
   if (tc->n_cat == 1) maps.a[1] = maps.a[0];
-  PDAC_TRY(encode_view_map(&maps.dy, dy, ckb, 16, 8, 1));
+  PDAC_TRY(encode_view_map(&maps.dy, dy, ckb, 16, p.b_rows, 1));
   int splits = (dual ? 2 : 1) * num_sms() / (ygroups * zgroups);
   if (splits < 1) splits = 1;
   if (splits > p.n_kblocks) splits = p.n_kblocks;

@@ -47,6 +47,8 @@ class BucketReducer:
                     self.bucket_of[key] = b
                     self.members[b] += 1
                     break
+        self.record_timeline = False    # profiling: CUDA events around every bucket's all_reduce (scripts/ddp_timeline.py)
+        self.timeline = []
         self.begin()
         self.launch_order = []          # bucket indices in the order their all_reduce was enqueued (tests / profiling)
 
@@ -56,6 +58,7 @@ class BucketReducer:
         self._sent = [False] * len(self.spans)
         self._seen = set()
         self.launch_order = []
+        self.timeline = []
 
     def ready(self, keys):
         """The gradient slots of these parameters are complete on the current stream."""
@@ -81,7 +84,13 @@ class BucketReducer:
         ev.record(torch.cuda.current_stream(self.flat.device))
         self.stream.wait_event(ev)
         with torch.cuda.stream(self.stream):
+            if self.record_timeline:
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record(self.stream)
             dist.all_reduce(self.flat[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
+            if self.record_timeline:
+                t1.record(self.stream)
+                self.timeline.append((b, (hi - lo) * self.flat.element_size(), t0, t1))
 
     def finish(self):
         """Reduces whatever has not been sent yet (buckets whose parameters never reported) and makes the current

@@ -156,7 +156,12 @@ def test_train_step_matches_oracle(name, train):
                 assert int(so[k]) == int(sa[k]), k
 
 
-@pytest.mark.parametrize("name", MODELS)
+# DeepLabV3+ is left out: its ASPP image-pooling branch feeds a BatchNorm that normalises ONE value per image and channel
+# (4 values per channel at this batch), and bf16 storage alone moves its whole fp32 gradient by 47 % at batch 4, 12 % at
+# batch 16 and 120 % in eval mode even with the shifts moved (oracle-only measurement, CPU): no well-conditioned regime
+# to test in. Its kernels are pinned individually (test_norm_dw_gpu.py, test_conv_gpu.py) and its network gradients by
+# the calibrated test above.
+@pytest.mark.parametrize("name", ["unet_smp", "fpn", "pspnet"])
 def test_gradients_match_fp32_when_well_conditioned(name):
     """A gradient test with discriminating power (VERDICT r1 weakness 2). On the seeded random-init networks the ReLU
     pre-activations are centred on the kink, and bf16 activation storage alone moves the fp32 gradients by 50-60 %
