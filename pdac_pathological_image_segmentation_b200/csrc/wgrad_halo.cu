@@ -224,7 +224,8 @@ __global__ void __launch_bounds__(kWhThreads, DUAL ? 2 : 1) wgrad_halo_kernel(co
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((s - slab0) * p.block_n + c), v);
             tmem_ld_wait();
             const int gi = c / p.rs_cout, b0 = c - gi * p.rs_cout;
-            const int t = p.slabs[s].sub_t[sub] >= 0 ? p.rs_tap[gi * 8 + sub] : -1;
+            const int kc = p.slabs[s].sub_t[sub];  // kernel column of this A sub-block
+            const int t = kc >= 0 ? p.rs_tap[gi * 8 + kc] : -1;
             if (t < 0) continue;
             if (p.part) {
               float* pb = p.part + (long long)blockIdx.x * p.part_stride + ((long long)t * p.Cout + b0) * p.part_A + a_ch;
@@ -325,13 +326,15 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   // rate. Here the kernel-ROW offsets move to the dY operand: dY is loaded with the h halo, the accumulator's N
   // dimension becomes (kernel row, output channel) = 3 x Cout columns through B sub-blocks one image row apart (LBO),
   // and the A operand keeps the kernel columns as sub-blocks one pixel apart: ONE MMA per 16 pixels covers all taps.
+  // With 64-channel chunks (PDAC_WGRAD_ROWSHIFT=2) the A sub-blocks of a slab are the two chunks of a stage for one kernel
+  // column, or two kernel columns of one chunk: 3 (or 2) slabs of N = 3 x Cout instead of 9 (or 5) of N = Cout.
   static int rs_ok = -1;
   if (rs_ok < 0) {
     const char* e = getenv("PDAC_WGRAD_ROWSHIFT");
-    rs_ok = (e && e[0] == '0') ? 0 : 1;
+    rs_ok = e ? atoi(e) : 2;
   }
   int rs = 0, rs_R = 0, rs_S = 0, rs_d = 1;
-  if (rs_ok && ck <= 32 && cout == ckb && zgroups == 1) {
+  if (rs_ok && (ck <= 32 || rs_ok >= 2) && cout == ckb && zgroups == 1) {
     int S = 1;
     while (S < tc->n_taps && tc->taps[S].dh == tc->taps[0].dh) ++S;
     const int Rr = tc->n_taps / S;
@@ -341,7 +344,7 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
       for (int t = 0; t < tc->n_taps && grid_ok; ++t)
         grid_ok = tc->taps[t].dh == dh_min + (t / S) * d && tc->taps[t].dw == dw_min + (t % S) * d;
       const int n_chunks_ = views[0].C / ck + (tc->n_cat > 1 ? views[1].C / ck : 0);
-      if (grid_ok && S * ck <= 128 && Rr * cout <= 256 && n_chunks_ * Rr * cout <= 512 && n_chunks_ <= kWhMaxSlabs &&
+      if (grid_ok && (S * ck <= 128 || ck == 64) && Rr * cout <= 256 && n_chunks_ * S <= kWhMaxSlabs &&
           d * 16 * ckb * 2 < (1 << 18)) {
         rs = 1;
         rs_R = Rr;
@@ -365,11 +368,20 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   p.layout_b = swizzle_layout_type(p.pitch_b);
   p.dw_min = dw_min;
   p.rowshift = rs;
+  p.cps = (ck == 64 && p.n_chunks >= 2) ? 2 : 1;
+  p.n_cg = ceil_div(p.n_chunks, p.cps);
   if (rs) {
-    // K block = 16 pixels x tile_rows rows: as tall as three A stages + two dY tiles allow with two CTAs per SM
+    // K block = 16 pixels x tile_rows rows: as tall as three A stages + two dY tiles allow (two CTAs per SM when the
+    // slabs fit half of the tensor memory)
+    int ns_est = 0;
+    for (int cg = 0; cg < p.n_cg; ++cg) {
+      const int nc = p.n_chunks - cg * p.cps < p.cps ? p.n_chunks - cg * p.cps : p.cps;
+      ns_est += (ck == 64 && nc == 2) ? rs_S : nc * ceil_div(rs_S, 128 / ck);
+    }
+    const int budget = (ns_est * block_n <= 256 ? 104 : 218) * 1024;
     int tr = 32;
-    while (tr > 8 && (tr > dy->H || ((tr * p.PW * (int)p.pitch_a + 1023) & ~1023) * 3 +
-                                        2 * (((tr + eh) * 16 * (int)p.pitch_b + 1023) & ~1023) + 2048 > 104 * 1024))
+    while (tr > 8 && (tr > dy->H || ((tr * p.PW * (int)p.pitch_a + 1023) & ~1023) * p.cps * 3 +
+                                        2 * (((tr + eh) * 16 * (int)p.pitch_b + 1023) & ~1023) + 2048 > budget))
       tr >>= 1;
     p.tile_rows = tr;
     p.R = tr;           // the source box has no h halo in this mode ...
@@ -392,8 +404,6 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
     p.lbo_b = 128u * p.pitch_b;
   }
   p.a_buf = (p.R * p.PW * (int)p.pitch_a + 1023) & ~1023;
-  p.cps = (ck == 64 && p.n_chunks >= 2) ? 2 : 1;
-  p.n_cg = ceil_div(p.n_chunks, p.cps);
 
   // taps in ascending halo-raster shift
   int order[PDAC_MAX_TAPS], shift[PDAC_MAX_TAPS];
@@ -424,14 +434,32 @@ int wgrad_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, co
   for (int cg = 0; cg < p.n_cg; ++cg) {
     const int c_first = cg * p.cps;
     const int nc = p.n_chunks - c_first < p.cps ? p.n_chunks - c_first : p.cps;
-    if (rs) {  // one slab per channel chunk: sub-block j = kernel column j (rs_d pixels apart), all kernel rows at once
-      WhSlab* sl = new_slab(cg);
-      if (!sl) return PDAC_OK;
-      sl->a_off16 = 0;
-      sl->lbo16 = (uint32_t)(rs_d * (int)p.pitch_a) >> 4;
-      for (int j = 0; j < 8; ++j) {
-        sl->sub_t[j] = (int8_t)(j < rs_S ? 0 : -1);
-        sl->sub_c[j] = (int8_t)c_first;
+    if (rs) {
+      // row-shift slabs: every slab covers ALL kernel rows (they sit in the accumulator's N dimension); its A
+      // sub-blocks are kernel COLUMNS (sub_t = column index, rs_d pixels apart) of one chunk, or, for 64-channel chunk
+      // pairs, the two chunks of the stage for one kernel column (a_buf apart)
+      if (ck == 64 && nc == 2) {
+        for (int j = 0; j < rs_S; ++j) {
+          WhSlab* sl = new_slab(cg);
+          if (!sl) return PDAC_OK;
+          sl->a_off16 = (uint32_t)(j * rs_d * (int)p.pitch_a) >> 4;
+          sl->lbo16 = (uint32_t)p.a_buf >> 4;
+          sl->sub_t[0] = sl->sub_t[1] = (int8_t)j;
+          sl->sub_c[0] = (int8_t)c_first;
+          sl->sub_c[1] = (int8_t)(c_first + 1);
+        }
+      } else {
+        for (int jc = 0; jc < nc; ++jc)
+          for (int j0 = 0; j0 < rs_S; j0 += subs) {
+            WhSlab* sl = new_slab(cg);
+            if (!sl) return PDAC_OK;
+            sl->a_off16 = (uint32_t)(jc * p.a_buf + j0 * rs_d * (int)p.pitch_a) >> 4;
+            sl->lbo16 = (uint32_t)(rs_d * (int)p.pitch_a) >> 4;
+            for (int k = 0; k < subs && j0 + k < rs_S; ++k) {
+              sl->sub_t[k] = (int8_t)(j0 + k);
+              sl->sub_c[k] = (int8_t)(c_first + jc);
+            }
+          }
       }
       continue;
     }
