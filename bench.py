@@ -482,9 +482,20 @@ def run_ours(args):
     h2d = B * S * S * 3 + B * S * S
     d2h = 4
 
-    if rank != 0:
+    def shutdown():
+        """NCCL's communicator teardown waits for every CUDA graph holding its collectives: drop the graph first, and
+        never let a teardown problem keep the process (and the launcher) alive."""
         if world > 1:
+            ts.release_graph()
+            guard = threading.Timer(60.0, lambda: os._exit(0))
+            guard.daemon = True
+            guard.start()
+            dist.barrier()
             dist.destroy_process_group()
+            guard.cancel()
+
+    if rank != 0:
+        shutdown()
         return
 
     # ---- roofline of the dominant kernel group (CUDA events recorded on the launching stream, timed region 1) ----
@@ -569,8 +580,7 @@ def run_ours(args):
             others["wsi"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
         line["other_configs"] = others
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    shutdown()
 
 
 # ------------------------------------------------------------------------------------------------ WSI inference

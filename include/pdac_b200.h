@@ -274,6 +274,10 @@ int pdac_dice_fwd(const float* logits, const void* targets, int tgt_dtype, long 
                   float* loss, void* stream);
 int pdac_dice_bwd(const float* logits, const void* targets, int tgt_dtype, long long n, const double* sums, float smooth,
                   const float* grad_out, float* grad_logits, void* stream);
+/* The 1-class case of pdac_dice_bwd with grad_out = 1, written as the bf16 NHWC tensor [n][cpad] (class in channel 0, the
+ * other cpad - 1 channels zero) that the head convolution's backward kernels read. */
+int pdac_dice_bwd_nhwc(const float* logits, const void* targets, int tgt_dtype, long long n, const double* sums,
+                       float smooth, void* grad_nhwc, int cpad, void* stream);
 /* mask = ge(sigmoid(x), 0.5) as fp32 {0,1} and/or uint8. */
 int pdac_sigmoid_mask(const float* logits, long long n, float* mask_f32, uint8_t* mask_u8, void* stream);
 /* pred_kind: 0 = fp32 hard mask, 1 = fp32 logits (mask rule applied on the fly), 2 = uint8 mask. counts: 3 uint64

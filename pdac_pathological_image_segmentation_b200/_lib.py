@@ -95,6 +95,7 @@ SIGNATURES = {
     "pdac_dwconv3x3_wgrad": [_VP, _VP, _i, _p, _p, _p],
     "pdac_dice_fwd": [_p, _p, _i, _ll, _p, _f, _p, _p],
     "pdac_dice_bwd": [_p, _p, _i, _ll, _p, _f, _p, _p, _p],
+    "pdac_dice_bwd_nhwc": [_p, _p, _i, _ll, _p, _f, _p, _i, _p],
     "pdac_sigmoid_mask": [_p, _ll, _p, _p, _p],
     "pdac_dice_score": [_p, _i, _p, _i, _ll, _p, _f, _p, _p],
     "pdac_argmax_nchw": [_p, _i, _i, _ll, _p, _p],

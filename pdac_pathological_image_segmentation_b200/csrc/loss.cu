@@ -97,6 +97,27 @@ __global__ void __launch_bounds__(256) dice_bwd_kernel(const float* __restrict__
   }
 }
 
+// The same gradient written straight into the layout the head convolution's backward reads: bf16 NHWC with the single
+// class in channel 0 of `cpad` (a multiple of 8) zero-padded channels — saves the fp32 round trip through HBM and the
+// separate layout pass of the 1-class training step (train_worker.py:150-182 all use classes = 1).
+template <typename T>
+__global__ void __launch_bounds__(256) dice_bwd_nhwc_kernel(const float* __restrict__ x, const T* __restrict__ t,
+                                                            long long n, const double* __restrict__ sums, float smooth,
+                                                            __nv_bfloat16* __restrict__ gx, int cpad) {
+  const double D = sums[1] + sums[2] + (double)smooth;
+  const double num = 2.0 * sums[0] + (double)smooth;
+  const float k1 = (float)(-2.0 / D), k0 = (float)(num / (D * D));
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float p = sigmoid_ref(__ldg(x + i));
+    const float tv = tgt_val(t, i);
+    const float g = (k1 * tv + k0) * p * (1.f - p);
+    uint4 v = make_uint4((uint32_t)__bfloat16_as_ushort(__float2bfloat16(g)), 0u, 0u, 0u);
+    uint4* o = reinterpret_cast<uint4*>(gx + i * cpad);
+    o[0] = v;
+    for (int k = 1; k < cpad / 8; ++k) o[k] = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
 // mask = ge(sigmoid(x), 0.5)
 __global__ void __launch_bounds__(256) sigmoid_mask_kernel(const float* __restrict__ x, long long n,
                                                            float* __restrict__ mf, uint8_t* __restrict__ mu) {
@@ -320,6 +341,21 @@ extern "C" int pdac_dice_bwd(const float* logits, const void* targets, int tgt_d
     dice_bwd_kernel<uint8_t><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const uint8_t*)targets, n, sums,
                                                                             smooth, grad_out, grad_logits);
   PDAC_LAUNCH_CHECK("dice_bwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_dice_bwd_nhwc(const float* logits, const void* targets, int tgt_dtype, long long n, const double* sums,
+                                  float smooth, void* grad_nhwc, int cpad, void* stream) {
+  PDAC_REQUIRE(logits && targets && sums && grad_nhwc, "dice_bwd_nhwc: null argument");
+  PDAC_REQUIRE(cpad >= 8 && cpad % 8 == 0 && ((uintptr_t)grad_nhwc & 15) == 0, "dice_bwd_nhwc: cpad must be a multiple of 8, output 16-byte aligned");
+  if (n <= 0) return PDAC_OK;
+  if (tgt_dtype == 0)
+    dice_bwd_nhwc_kernel<float><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const float*)targets, n, sums, smooth,
+                                                                               (__nv_bfloat16*)grad_nhwc, cpad);
+  else
+    dice_bwd_nhwc_kernel<uint8_t><<<rblocks(n), 256, 0, (cudaStream_t)stream>>>(logits, (const uint8_t*)targets, n, sums,
+                                                                                 smooth, (__nv_bfloat16*)grad_nhwc, cpad);
+  PDAC_LAUNCH_CHECK("dice_bwd_nhwc");
   return PDAC_OK;
 }
 

@@ -492,11 +492,15 @@ def logits_head(tape: Tape, x, n_classes, out_hw, align_corners):
         out = ops.bilinear_head_fwd(x, n_classes, out_hw, align_corners)
 
     def feed(g):
-        if same:
+        if g.dtype == torch.bfloat16:      # already the bf16 NHWC (N, h, w, cpad) gradient (ops.dice_bwd_nhwc)
+            assert same and tuple(g.shape) == tuple(x.shape)
+            dx = g
+        elif same:
             dx = ops.nchw_to_nhwc(g.contiguous(), c_pad=cpad)
         else:
             dx = ops.bilinear_head_bwd(g, (h, w, cpad), align_corners)
         tape.put(x, dx)
+    feed.nhwc_cpad = cpad if same else None     # callers may hand feed() a bf16 NHWC gradient with this channel padding
     return out, feed
 
 

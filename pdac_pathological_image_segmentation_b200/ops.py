@@ -625,6 +625,17 @@ def dice_bwd(logits, targets, sums, grad_out, smooth=1e-6):
     return g
 
 
+def dice_bwd_nhwc(logits, targets, sums, cpad, smooth=1e-6):
+    """1-class Dice gradient (grad_out = 1) as the bf16 NHWC (N, H, W, cpad) tensor the head's backward reads."""
+    logits = logits.contiguous()
+    n, c, h, w = logits.shape
+    assert c == 1 and logits.dtype == torch.float32
+    t, kind = _tgt(targets)
+    g = torch.empty((n, h, w, cpad), dtype=BF16, device=logits.device)
+    call("pdac_dice_bwd_nhwc", _ptr(logits), _ptr(t), kind, logits.numel(), _ptr(sums), smooth, _ptr(g), cpad, _stream())
+    return g
+
+
 def sigmoid_mask(logits, as_uint8=False):
     _need_cuda(logits, "logits")
     logits = logits.contiguous()

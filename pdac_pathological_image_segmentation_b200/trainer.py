@@ -173,7 +173,8 @@ class TrainStep:
             raise RuntimeError("TrainStep implements the reference's 1-class sigmoid/Dice step (train_worker.py:150-182)")
         score, _ = ops.dice_score(logits, mask, pred_is_logits=True)
         loss, sums = ops.dice_fwd(logits, mask)
-        g = ops.dice_bwd(logits, mask, sums, None)
+        cpad = getattr(feed, "nhwc_cpad", None)
+        g = ops.dice_bwd_nhwc(logits, mask, sums, cpad) if cpad else ops.dice_bwd(logits, mask, sums, None)
         self.arena.zero()
         feed(g)
         if reduce and self.world > 1:
@@ -250,6 +251,15 @@ class TrainStep:
         self._g_launches = _lib.launches - l0
         _lib.launches = l0
         self._g = g
+
+    def release_graph(self):
+        """Drops the captured CUDA graph (the next step re-captures). REQUIRED before torch.distributed's
+        destroy_process_group() when the graph holds the NCCL all_reduces: NCCL's communicator teardown waits for every
+        CUDA graph that captured collectives on it to be destroyed."""
+        self._g = None
+        self._g_out = None
+        self._g_key = None
+        torch.cuda.synchronize(self.device)
 
     # ------------------------------------------------------------------------------------------------ validation
     @torch.no_grad()

@@ -33,6 +33,20 @@ def test_dice_loss_fwd_bwd(n, tdtype):
     assert torch.allclose(gx2, gx * 0.5, rtol=1e-6, atol=0)
 
 
+def test_dice_bwd_nhwc_equals_dice_bwd_then_layout():
+    """The fused 1-class gradient (bf16 NHWC, class in channel 0 of 16) is bit-identical to dice_bwd followed by the
+    fp32 NCHW -> bf16 NHWC layout pass it replaces in the train step."""
+    from pdac_pathological_image_segmentation_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    x = (torch.randn(3, 1, 40, 56, generator=g) * 2).to(DEV)
+    t = (torch.rand(3, 40, 56, generator=g) < 0.4).to(torch.uint8).to(DEV)
+    _, sums = ops.dice_fwd(x, t)
+    want = ops.nchw_to_nhwc(ops.dice_bwd(x, t, sums, None), c_pad=16)
+    got = ops.dice_bwd_nhwc(x, t, sums, 16)
+    assert got.shape == (3, 40, 56, 16) and torch.equal(got, want)
+    assert got[..., 0].float().abs().max().item() > 0 and got[..., 1:].abs().max().item() == 0
+
+
 def test_dice_closed_forms():
     """SURVEY 8c KATs: zero logits vs all-ones target; empty prediction vs empty target."""
     from pdac_pathological_image_segmentation_b200 import ops

@@ -152,6 +152,7 @@ def _ddp_worker(rank, world, port, out):
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    tg = None
     try:
         from pdac_pathological_image_segmentation_b200.synthetic import synthetic_batch
         img, mask = (t.to(dev) for t in synthetic_batch(2, 128, seed=50 + rank))
@@ -189,8 +190,8 @@ def _ddp_worker(rank, world, port, out):
         opt = torch.optim.Adam(ddp.parameters(), lr=1e-3)
         from pdac_pathological_image_segmentation_b200 import ops
         x = torch.empty(2, 3, 128, 128, device=dev).normal_()
-        out = ddp(x)
-        DiceLoss()(torch.squeeze(out), mask.float()).backward()
+        logits = ddp(x)
+        DiceLoss()(torch.squeeze(logits), mask.float()).backward()
         g = getattr(m2.segmentation_head, "0").weight.grad
         gs = [torch.empty_like(g) for _ in range(world)]
         dist.all_gather(gs, g.contiguous())
@@ -198,13 +199,15 @@ def _ddp_worker(rank, world, port, out):
         opt.step()
         res["ddp_finite"] = bool(all(torch.isfinite(p).all() for p in m2.parameters()))
         ops.check_device_flag()
-        out_d = dict(res)
-        out[rank] = out_d
+        out[rank] = dict(res)
     finally:
+        if tg is not None:
+            tg.release_graph()      # also on failure: a live graph with captured collectives blocks the teardown
+        torch.cuda.synchronize()
         dist.destroy_process_group()
 
 
-@pytest.mark.timeout(600)
+@pytest.mark.timeout(240)
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (NCCL)")
 def test_two_gpu_allreduce_overlap_graph_and_ddp_wrap():
     import torch.multiprocessing as mp
