@@ -16,13 +16,16 @@ import torch
 import torch.distributed as dist
 
 
-def make_buckets(param_offsets, total, bucket_mb=25.0, elem_bytes=4):
+def make_buckets(param_offsets, total, bucket_mb=25.0, elem_bytes=4, tail_mb=0.0):
     """param_offsets: arena offset of every parameter in REGISTRATION order (ascending). -> [(lo, hi)] spans in
-    reduction order (last parameters first) that tile [0, total)."""
+    reduction order (last parameters first) that tile [0, total). tail_mb > 0 caps the LAST span (the first registered
+    parameters, whose gradients complete at the very end of backward and whose all_reduce nothing can hide) at that
+    size by splitting it at a parameter boundary — the mirror image of torch DDP's small first bucket."""
+    offs = list(param_offsets)
     cap = max(int(bucket_mb * 1024 * 1024 / elem_bytes), 1)
     spans, hi = [], total
     lo = total
-    for off in reversed(list(param_offsets)):
+    for off in reversed(offs):
         if hi - off > cap and lo < hi:
             spans.append((lo, hi))
             hi = lo
@@ -31,6 +34,12 @@ def make_buckets(param_offsets, total, bucket_mb=25.0, elem_bytes=4):
         lo = 0
     if lo < hi:
         spans.append((lo, hi))
+    if tail_mb > 0 and spans:
+        tail = max(int(tail_mb * 1024 * 1024 / elem_bytes), 1)
+        lo, hi = spans[-1]
+        cut = [o for o in offs if lo < o < hi and o - lo <= tail]
+        if hi - lo > tail and cut:
+            spans[-1:] = [(max(cut), hi), (lo, max(cut))]
     return spans
 
 

@@ -112,7 +112,10 @@ class TrainStep:
         self.exp_avg = torch.zeros_like(self.arena.flat)
         self.exp_avg_sq = torch.zeros_like(self.arena.flat)
         offsets = {id(p): self.arena.offsets[id(p)][0] for p in self.params}
-        self.reducer = BucketReducer(self.arena.flat, make_buckets(sorted(offsets.values()), self.arena.size, bucket_mb),
+        # 25 MB buckets as torch DDP, plus a small last bucket: the stem / layer1 gradients are complete only when
+        # backward ends, so their all_reduce is the one piece of communication nothing can overlap
+        self.reducer = BucketReducer(self.arena.flat,
+                                     make_buckets(sorted(offsets.values()), self.arena.size, bucket_mb, tail_mb=1.0),
                                      process_group, offsets)
         self.world = self.reducer.world
         self.optimizer = ArenaAdam(self, model.parameters(), lr, betas, eps)

@@ -30,6 +30,11 @@ def test_buckets_tile_arena_in_reverse_registration_order():
             assert inside and (hi - lo <= cap or len(inside) == 1)   # only a single oversized tensor may exceed the cap
     assert len(make_buckets(offs, arena.size, 25.0)) == 1
     assert make_buckets([], 0) == []
+    # a capped tail: the last span (first registered parameters, complete only when backward ends) is split off small
+    spans = make_buckets(offs, arena.size, 25.0, tail_mb=0.5)
+    assert len(spans) == 2 and spans[0][1] == arena.size and spans[0][0] == spans[1][1] and spans[1][0] == 0
+    assert 0 < (spans[1][1] - spans[1][0]) * 4 <= 0.5 * 1024 * 1024 and spans[1][1] in offs
+    assert make_buckets(offs, arena.size, 25.0, tail_mb=1000.0) == make_buckets(offs, arena.size, 25.0)
 
 
 def _free_port():
