@@ -196,7 +196,9 @@ int pdac_unpack_stem_wgrad(const float* dwp, int O, float* dw, void* stream);
 int pdac_bn_prepare(const float* stats, int n_rows, double count, const float* gamma, const float* beta, float eps,
                     float momentum, int train, float* running_mean, float* running_var,
                     long long* num_batches_tracked, float* scale_shift, float* mean_invstd, int C, void* stream);
-/* y = [relu](x*scale[c] + shift[c] + residual); scale_shift / residual may be NULL. */
+/* y = [relu](x*scale[c] + shift[c] + residual); scale_shift / residual may be NULL. When y is 2H x 2W the result is
+ * stored nearest-neighbour upsampled (each pixel four times): smp UnetDecoder's F.interpolate(scale_factor=2) fused into
+ * the normalise pass of the layer that produces its input. */
 int pdac_scale_shift_act(const PdacView* x, const float* scale_shift, const PdacView* residual, int relu,
                          const PdacView* y, void* stream);
 /* BN backward pass 1: dz = dy * (y > 0); sums[c] = sum dz, sums[C+c] = sum dz*xhat. sums: fp32

@@ -160,8 +160,11 @@ int rows_sum(const float* rows, int n_rows, int ncols, float* out, int accumulat
 }
 
 // ------------------------------------------------------------------------------------------------ y = act(x*s + b + r)
+// UP2: y is the nearest-neighbour x2 upsampling of the result (smp UnetDecoder's F.interpolate(scale_factor=2) fused
+// into the producer's normalise pass: every output pixel is stored four times, the low-resolution tensor never exists)
+template <bool UP2>
 __global__ void __launch_bounds__(256) scale_shift_act_kernel(Flat x, const float* __restrict__ ss, Flat res, int relu,
-                                                              Flat y, int cg, int ppb) {
+                                                              Flat y, int cg, int ppb, int H, int W) {
   EW_SETUP(cg, ppb)
   if (!active) return;
   float sc[8], sh[8];
@@ -195,7 +198,21 @@ __global__ void __launch_bounds__(256) scale_shift_act_kernel(Flat x, const floa
 #pragma unroll
         for (int i = 0; i < 8; ++i) a.v[i] = fmaxf(a.v[i], 0.f);
       }
-      st16(y.ptr + (u ? p2 : p) * y.ps + g * 8, pack8(a));
+      const long long pp = u ? p2 : p;
+      if (UP2) {
+        const long long hw = (long long)H * W;
+        const long long n = pp / hw;
+        const int rem = (int)(pp - n * hw);
+        const int h = rem / W, w = rem - h * W;
+        const uint4 v = pack8(a);
+        bf16* o = y.ptr + ((n * 2 * H + 2 * h) * (2LL * W) + 2 * w) * y.ps + g * 8;
+        st16(o, v);
+        st16(o + y.ps, v);
+        st16(o + 2LL * W * y.ps, v);
+        st16(o + (2LL * W + 1) * y.ps, v);
+      } else {
+        st16(y.ptr + pp * y.ps + g * 8, pack8(a));
+      }
     }
   }
 }
@@ -422,13 +439,24 @@ extern "C" int pdac_scale_shift_act(const PdacView* x, const float* scale_shift,
   PDAC_TRY(flatten(x, &fx, "x"));
   PDAC_TRY(flatten(y, &fy, "y"));
   if (residual) PDAC_TRY(flatten(residual, &fr, "residual"));
-  PDAC_REQUIRE(fy.npix == fx.npix && fy.C == fx.C && (!residual || (fr.npix == fx.npix && fr.C == fx.C)),
+  // y either has x's shape or is its nearest-neighbour x2 upsampling (2H x 2W)
+  const bool up2 = y->H == 2 * x->H && y->W == 2 * x->W && y->N == x->N && x->H > 0;
+  PDAC_REQUIRE((up2 ? fy.npix == 4 * fx.npix : fy.npix == fx.npix) && fy.C == fx.C &&
+                   (!residual || (fr.npix == fx.npix && fr.C == fx.C)),
                "scale_shift_act: shape mismatch");
   PDAC_REQUIRE(fx.C <= 2048, "scale_shift_act: too many channels");
   if (fx.npix == 0) return PDAC_OK;
-  static const int resident = resident_blocks(scale_shift_act_kernel);
-  const EwGrid g = ew_grid(fx.npix, fx.C, resident);
-  scale_shift_act_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fx, scale_shift, fr, relu, fy, g.cg, g.ppb);
+  if (up2) {
+    static const int resident = resident_blocks(scale_shift_act_kernel<true>);
+    const EwGrid g = ew_grid(fx.npix, fx.C, resident);
+    scale_shift_act_kernel<true><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fx, scale_shift, fr, relu, fy, g.cg, g.ppb,
+                                                                            x->H, x->W);
+  } else {
+    static const int resident = resident_blocks(scale_shift_act_kernel<false>);
+    const EwGrid g = ew_grid(fx.npix, fx.C, resident);
+    scale_shift_act_kernel<false><<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fx, scale_shift, fr, relu, fy, g.cg,
+                                                                             g.ppb, x->H, x->W);
+  }
   PDAC_LAUNCH_CHECK("scale_shift_act");
   return PDAC_OK;
 }

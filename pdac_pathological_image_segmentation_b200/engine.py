@@ -249,23 +249,29 @@ def _bn_prepare(tape, bn: BatchNorm2d, stats, count, device):
     return st
 
 
-def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residual=None, out=None):
+def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residual=None, out=None, up2=False):
     """[relu](BN(conv(cat(srcs))) + residual): conv with per-channel sum / sum-of-squares in its epilogue, a finalize
-    kernel, then one fused normalise(+residual)(+ReLU) pass (torchvision resnet.py:92-103; smp Conv2dReLU)."""
+    kernel, then one fused normalise(+residual)(+ReLU) pass (torchvision resnet.py:92-103; smp Conv2dReLU).
+    up2 (training path): returns the nearest-neighbour x2 upsampling of the result, written by the normalise pass itself
+    (smp UnetDecoder: F.interpolate(x, scale_factor=2, mode="nearest") in front of the next block)."""
     wp_f, wp_t, _ = tape.packs.conv(m)
     k = m.k
     dev = srcs[0].device
     if not tape.training and not tape.enabled:
         # inference: BatchNorm is a per-channel affine map -> folded (with the residual and the ReLU) into the conv epilogue
         st = _bn_prepare(tape, bn, None, 1, dev)
-        return ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, relu=relu, bias=st.ss[1],
-                              addend=residual, scale=st.ss[0], out=out)
+        y = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, relu=relu, bias=st.ss[1],
+                           addend=residual, scale=st.ss[0], out=out)
+        return ops.upsample_nearest2x_fwd(y) if up2 else y
     stats = ops.new_stats(m.cout, dev) if tape.training else None
     x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
     keep_x = tape.enabled
     if out is not None:        # write the activation straight into a channel slice of a concat buffer
+        assert not up2
         y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=out)
+    elif up2:
+        y = ops.scale_shift_act(x, st.ss, residual, relu=relu, up2=True)
     else:
         y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=None if keep_x else x)
     training = tape.training
@@ -274,8 +280,11 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         dy = tape.pop(y)
         if dy is None:
             return
+        if up2:                # gradient of the fused upsampling: sum of the four replicas
+            dy = ops.upsample_nearest2x_bwd(dy)
         sums = ops.new_bwd_sums(m.cout, dev)
         # without a residual the ReLU mask is recomputed from x and the forward's scale / shift: y is not re-read
+        assert not (up2 and residual is not None), "up2 is fused for residual-free layers only (mask recomputed from x)"
         ymask = y if (relu and residual is not None) else None
         ssm = st.ss if (relu and residual is None) else None
         ops.bn_bwd_reduce(dy, ymask, x, st.mi, sums, scale_shift=ssm)

@@ -424,9 +424,10 @@ def bn_prepare(stats, count, gamma, beta, eps, momentum, train, running_mean, ru
          _stream())
 
 
-def scale_shift_act(x, scale_shift=None, residual=None, relu=False, out=None):
+def scale_shift_act(x, scale_shift=None, residual=None, relu=False, out=None, up2=False):
+    """up2: the result is stored nearest-neighbour x2 upsampled ((N, 2H, 2W, C); the low-resolution tensor is not)."""
     if out is None:
-        out = torch.empty_like(x)
+        out = empty_act(x.shape[0], 2 * x.shape[1], 2 * x.shape[2], x.shape[3], x.device) if up2 else torch.empty_like(x)
     call("pdac_scale_shift_act", _vp(x), _ptr(scale_shift), _vp(residual), int(bool(relu)), _vp(out), _stream())
     return out
 

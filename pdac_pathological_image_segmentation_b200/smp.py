@@ -56,12 +56,14 @@ def conv2d_relu(cin, cout, k, padding=0, use_batchnorm=True):
                BatchNorm2d(cout) if use_batchnorm else None)
 
 
-def run_conv2d_relu(tape, block, srcs):
+def run_conv2d_relu(tape, block, srcs, up2=False):
+    """up2: also apply the next decoder block's nearest x2 upsampling (fused into the BatchNorm pass when there is one)."""
     conv = getattr(block, "0")
     bn = getattr(block, "1", None)
     if bn is not None:
-        return E.conv_bn_act(tape, conv, bn, srcs, relu=True)
-    return E.conv_bias_act(tape, conv, srcs, relu=True)
+        return E.conv_bn_act(tape, conv, bn, srcs, relu=True, up2=up2)
+    y = E.conv_bias_act(tape, conv, srcs, relu=True)
+    return E.nearest2x(tape, y) if up2 else y
 
 
 class _SmpBase(SegModule):
@@ -109,13 +111,13 @@ class Unet(_SmpBase):
     def _run(self, tape, x):
         stem, l1, l2, l3, l4 = E.resnet18_features(tape, self.encoder, x)
         skips = [l3, l2, l1, stem, None]
-        y = l4
+        y = E.nearest2x(tape, l4)                                      # F.interpolate(scale_factor=2, nearest)
         for i, skip in enumerate(skips):
             blk = getattr(self.decoder.blocks, str(i))
-            y = E.nearest2x(tape, y)                                   # F.interpolate(scale_factor=2, nearest)
             srcs = [y, skip] if skip is not None else [y]              # torch.cat([x, skip], 1) = two K ranges
             y = run_conv2d_relu(tape, blk.conv1, srcs)
-            y = run_conv2d_relu(tape, blk.conv2, [y])
+            # the NEXT block's upsampling is written by this block's last normalise pass
+            y = run_conv2d_relu(tape, blk.conv2, [y], up2=i + 1 < len(skips))
         return self._head(tape, y, 1)
 
 

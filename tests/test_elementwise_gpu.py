@@ -127,6 +127,19 @@ def test_maxpool3x3s2(shape):
     _close(_nchw(dx2), xr.grad + _nchw(add).float(), "maxpool bwd + addend", rel=2.0 ** -6, abs_=1e-3)
 
 
+@pytest.mark.parametrize("shape", [(2, 32, 8, 8), (3, 16, 5, 7), (1, 256, 4, 4)])
+def test_scale_shift_act_with_fused_nearest2x(shape):
+    """The normalise pass that stores its result nearest-neighbour x2 upsampled (smp UnetDecoder's F.interpolate fused
+    into the producing layer): bit-identical to the plain pass followed by the upsampling kernel."""
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, C, H, W = shape
+    x = _nhwc(_rnd(N, C, H, W, seed=1))
+    ss = torch.stack([torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV) * 0.3])
+    want = ops.upsample_nearest2x_fwd(ops.scale_shift_act(x, ss, None, relu=True))
+    got = ops.scale_shift_act(x, ss, None, relu=True, up2=True)
+    assert got.shape == (N, 2 * H, 2 * W, C) and torch.equal(got, want)
+
+
 def test_nearest2x():
     from pdac_pathological_image_segmentation_b200 import ops
     x = _rnd(2, 32, 8, 8, seed=1)
