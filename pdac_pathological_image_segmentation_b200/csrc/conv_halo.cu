@@ -403,16 +403,8 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
     const int e = (threadIdx.x - 64) & 127;
     const int sc = p.block_n < 64 ? p.block_n : 64;  // staging columns per pass
     const int spitch = sc * 2 + 16;
-    // DUAL: two staging buffers (and row-offset tables) per warpgroup, used alternately: the barrier in the middle of
-    // an accumulator pass then also protects the buffer written two passes later, the barrier at the top of the pass
-    // disappears, and a warp can start the TMEM loads of the next accumulator while slower warps of its warpgroup are
-    // still in the store loop of this one (the 16 / 32-channel layers are bound by this latency chain)
-    const uint32_t stg0 = smem_u32(smem_stg) + (uint32_t)(wg * 128 * spitch);
-    const uint32_t stg_alt = (uint32_t)(p.n_wg * 128 * spitch);  // distance to the second buffer
-    uint32_t stg = stg0;
-    uint32_t my_row = stg + (uint32_t)(m * spitch);
-    int rslot = wg;  // s_rowoff table in use
-    int acc_it = 0;
+    const uint32_t stg = smem_u32(smem_stg) + (uint32_t)(wg * 128 * spitch);
+    const uint32_t my_row = stg + (uint32_t)(m * spitch);
     const uint32_t bar_id = 1 + wg;
     const int nch = min(p.block_n, p.Cout - n0);
     const bool vec = (p.Cout & 7) == 0;
@@ -456,15 +448,8 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
           const bool valid = (tw < p.TW) && (th < p.TH) && (w0 + tw < p.W) && (h0 + th < p.H);
           const long long ooff = obase + (long long)th * p.osH + (long long)tw * p.osW;
           const bf16* arow = p.addend + abase + (long long)th * p.asH + (long long)tw * p.asW + n0;
-          if (DUAL) {
-            stg = stg0 + ((acc_it & 1) ? stg_alt : 0u);
-            my_row = stg + (uint32_t)(m * spitch);
-            rslot = wg + 2 * (acc_it & 1);
-            ++acc_it;
-          } else {
-            asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // previous staging fully consumed
-          }
-          s_rowoff[rslot][m] = valid ? ooff : -1;
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // previous staging fully consumed
+          s_rowoff[wg][m] = valid ? ooff : -1;
           const uint32_t tacc =
               tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
 #pragma unroll
@@ -556,7 +541,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                 int row = e >> cpr_log2;
 #pragma unroll 2
                 for (int it = 0; it < (1 << cpr_log2); ++it, row += step, saddr += sstep) {
-                  const long long off = s_rowoff[rslot][row];
+                  const long long off = s_rowoff[wg][row];
                   const uint4 val = lds128(saddr);
                   if (off >= 0 && ch_ok && !DBG(0)) *reinterpret_cast<uint4*>(gcol + off) = val;
                   if (p.stats && !DBG(3)) {
@@ -576,7 +561,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                 const int nv = min(cols, nch - c0);
                 for (int id = e; id < 128 * nv; id += 128) {
                   const int row = id / nv, chn = id - row * nv;
-                  const long long off = s_rowoff[rslot][row];
+                  const long long off = s_rowoff[wg][row];
                   if (off < 0) continue;
                   p.out[off + n0 + c0 + chn] = __ushort_as_bfloat16(lds16(stg + (uint32_t)(row * spitch + chn * 2)));
                 }
@@ -597,7 +582,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
     // slots in index order and stores the CTA's row of the [rows][2][Cout] partial table (no atomics anywhere).
     if (p.stats && vec) {
       asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // the last tile's staging has been consumed
-      float* wslot = reinterpret_cast<float*>(smem_stg + (size_t)wg * 128 * spitch) + q * 256;  // buffer 0 of this warpgroup
+      float* wslot = reinterpret_cast<float*>(smem_stg + (size_t)wg * 128 * spitch) + q * 256;
 #pragma unroll
       for (int pass = 0; pass < NPASS; ++pass) {
         const int c0 = pass * 64;
@@ -675,7 +660,7 @@ static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int
   const int max_nacc = tmem_half / N < 4 ? tmem_half / N : 4;
   if (max_nacc < 1) return false;
   const long long w_bytes = (long long)n_taps * n_chunks * N * pitch;
-  const int stg_wg = (dual ? 2 : 1) * 128 * ((N < 64 ? N : 64) * 2 + 16);  // staging bytes per epilogue warpgroup (two buffers when dual)
+  const int stg_wg = 128 * ((N < 64 ? N : 64) * 2 + 16);  // staging bytes per epilogue warpgroup
   best->cost = 1e30;
   // tuning overrides (debug): PDAC_HALO_TW / PDAC_HALO_NACC / PDAC_HALO_SA / PDAC_HALO_WG
   static int f_tw = -1, f_nacc = -1, f_sa = -1, f_wg = -1;
@@ -902,8 +887,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     PDAC_TRY(encode_tiled_bf16(&maps.w, w_packed, 2, dims, strides, box, p.pitch));
   }
   const size_t b_bytes = (size_t)(p.b_resident ? p.n_taps * p.n_chunks : p.sb * p.tap_S) * p.b_sub;
-  const size_t smem = (size_t)p.sa * p.a_buf + b_bytes +
-                      (size_t)(dual ? 2 : 1) * p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16) + 1024;
+  const size_t smem = (size_t)p.sa * p.a_buf + b_bytes + (size_t)p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16) + 1024;
   PDAC_REQUIRE(smem <= (size_t)(dual ? 105 : 221) * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
   int per_n = (dual ? 2 : 1) * num_sms() / p.tiles_c;
   if (per_n < 1) per_n = 1;
