@@ -269,6 +269,19 @@ int pdac_dwconv3x3(const PdacView* x, const float* w, int dil, int flip, const P
  * floats): reproducible fixed-order sum over the blocks; NULL: fp32 atomics. */
 int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* dw, float* scratch, void* stream);
 
+/* ---- full-resolution segmentation head (head.cu) -----------------------------------------------------------
+ * smp SegmentationHead of Unet: Conv2d(C, classes, 3, padding=1) + bias with C = 16 or 32 and 1 or 2 classes, as direct
+ * HBM-bound kernels (a tensor-core GEMM with N = 1 would write and re-read 16-channel padded tensors).
+ * weight: the fp32 state_dict tensor [classes][C][3][3], bias fp32 [classes] or NULL; logits / grad_logits: fp32 NCHW
+ * (N, classes, H, W) — what the reference's callers see (train_worker.py:70-79). dw / dbias are accumulated into (state_dict
+ * layouts); scratch: fp32, >= 296 * classes * (9*C + 1) floats (fixed-order partial rows: reproducible). */
+int pdac_head3x3_supported(int channels, int classes); /* 1 / 0, no status code */
+int pdac_head3x3_fwd(const PdacView* x, const float* weight, const float* bias, int classes, float* logits,
+                     void* stream);
+int pdac_head3x3_dgrad(const float* grad_logits, const float* weight, int classes, const PdacView* dx, void* stream);
+int pdac_head3x3_wgrad(const PdacView* x, const float* grad_logits, int classes, float* dw, float* dbias, float* scratch,
+                       long long scratch_bytes, void* stream);
+
 /* ---- loss / metric / mask / stitch / optimiser (loss.cu) ---------------------------------------------------- */
 /* tgt_dtype: 0 = fp32, 1 = uint8. sums: 3 * (1 + PDAC_STAT_ROWS) doubles: [0..2] = (sum p*t, sum p, sum t), kept for
  * backward; the rest takes the blocks' partial rows, added in a fixed order (no zeroing needed). loss: 1 float. */

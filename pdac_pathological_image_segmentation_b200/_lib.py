@@ -93,6 +93,10 @@ SIGNATURES = {
     "pdac_dropout": [_VP, _VP, _f, C.c_ulonglong, _p, _i, _p],
     "pdac_dwconv3x3": [_VP, _p, _i, _i, _VP, _p],
     "pdac_dwconv3x3_wgrad": [_VP, _VP, _i, _p, _p, _p],
+    "pdac_head3x3_supported": [_i, _i],
+    "pdac_head3x3_fwd": [_VP, _p, _p, _i, _p, _p],
+    "pdac_head3x3_dgrad": [_p, _p, _i, _VP, _p],
+    "pdac_head3x3_wgrad": [_VP, _p, _i, _p, _p, _p, _ll, _p],
     "pdac_dice_fwd": [_p, _p, _i, _ll, _p, _f, _p, _p],
     "pdac_dice_bwd": [_p, _p, _i, _ll, _p, _f, _p, _p, _p],
     "pdac_dice_bwd_nhwc": [_p, _p, _i, _ll, _p, _f, _p, _i, _p],

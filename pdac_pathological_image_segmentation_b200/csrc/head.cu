@@ -1,0 +1,307 @@
+// The segmentation head at full resolution: Conv2d(C, classes, 3, padding=1) with C = 16 / 32 input channels and 1 or 2
+// classes (smp SegmentationHead of Unet, train_worker.py / BASELINE configs 2 and 5: classes = 1 at 512 x 512).
+// As a tensor-core GEMM this layer has N = 1: the implicit-GEMM kernels pad it to 16 output channels, write a 16-channel
+// bf16 tensor of which one channel is real (537 MB per step at batch 64), convert it to fp32 NCHW in another pass, and do
+// the same on the way back (a 16-channel dY, its own bias-gradient pass). It is 144 MACs per pixel — CUDA-core work that is
+// purely HBM-bound — so it gets three direct kernels that touch each tensor once:
+//   forward   x (bf16 NHWC) -> logits fp32 NCHW (what the callers see; NHWC == NCHW for one class), bias added
+//   dgrad     dL/dlogits fp32 NCHW -> dx bf16 NHWC
+//   wgrad     dw [classes][C][3][3] and dbias [classes] in the state_dict layout, per-block partial rows added in a
+//             fixed order by rows_sum (reproducible, no atomics)
+// fp32 master weights are used directly (no bf16 copy): the arithmetic is fp32 on bf16 activations.
+#include "common.h"
+#include "vec.cuh"
+
+namespace pdac {
+
+static constexpr int kHTW = 32, kHTH = 8;  // output tile (one pixel per thread)
+
+struct HeadView {
+  const bf16* ptr;
+  long long sN, sH, sW;
+  int N, H, W;
+};
+
+// shared-memory tile of the bf16 NHWC source with a one-pixel halo, zero-filled outside the image
+template <int CIN>
+__device__ __forceinline__ void load_x_tile(const HeadView& x, int n, int h0, int w0, uint4* tile) {
+  constexpr int CG = CIN / 8;
+  const int total = (kHTH + 2) * (kHTW + 2) * CG;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int g = i % CG;
+    const int px = i / CG;
+    const int ty = px / (kHTW + 2), tx = px - ty * (kHTW + 2);
+    const int h = h0 + ty - 1, w = w0 + tx - 1;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (h >= 0 && h < x.H && w >= 0 && w < x.W) v = ld16(x.ptr + n * x.sN + h * x.sH + w * x.sW + g * 8);
+    tile[i] = v;
+  }
+}
+
+// tile of the fp32 NCHW gradient (one class) with a one-pixel halo, zero outside the image
+__device__ __forceinline__ void load_g_tile(const float* __restrict__ g, int H, int W, int h0, int w0, float* tile) {
+  const int total = (kHTH + 2) * (kHTW + 2);
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int ty = i / (kHTW + 2), tx = i - ty * (kHTW + 2);
+    const int h = h0 + ty - 1, w = w0 + tx - 1;
+    tile[i] = (h >= 0 && h < H && w >= 0 && w < W) ? __ldg(g + (long long)h * W + w) : 0.f;
+  }
+}
+
+template <int CIN, int COUT>
+__global__ void __launch_bounds__(256) head3x3_fwd_kernel(HeadView x, const float* __restrict__ wgt,
+                                                          const float* __restrict__ bias, float* __restrict__ out,
+                                                          int tiles_w, int tiles_h) {
+  constexpr int CG = CIN / 8;
+  __shared__ uint4 tile[(kHTH + 2) * (kHTW + 2) * CG];
+  __shared__ float w_s[COUT][9][CIN];
+  int b = blockIdx.x;
+  const int tw = b % tiles_w;
+  b /= tiles_w;
+  const int th = b % tiles_h;
+  const int n = b / tiles_h;
+  const int h0 = th * kHTH, w0 = tw * kHTW;
+  for (int i = threadIdx.x; i < COUT * 9 * CIN; i += blockDim.x) {
+    const int ci = i % CIN, t = (i / CIN) % 9, co = i / (9 * CIN);
+    w_s[co][t][ci] = wgt[((long long)co * CIN + ci) * 9 + t];  // state_dict [co][ci][r][s]
+  }
+  load_x_tile<CIN>(x, n, h0, w0, tile);
+  __syncthreads();
+  const int tx = threadIdx.x % kHTW, ty = threadIdx.x / kHTW;
+  const int h = h0 + ty, w = w0 + tx;
+  float acc[COUT];
+#pragma unroll
+  for (int co = 0; co < COUT; ++co) acc[co] = bias ? bias[co] : 0.f;
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const uint4* px = tile + ((ty + r) * (kHTW + 2) + tx + s) * CG;
+#pragma unroll
+      for (int g = 0; g < CG; ++g) {
+        const F8 v = unpack8(px[g]);
+#pragma unroll
+        for (int co = 0; co < COUT; ++co)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[co] = fmaf(v.v[i], w_s[co][r * 3 + s][g * 8 + i], acc[co]);
+      }
+    }
+  if (h < x.H && w < x.W) {
+#pragma unroll
+    for (int co = 0; co < COUT; ++co) out[(((long long)n * COUT + co) * x.H + h) * x.W + w] = acc[co];
+  }
+}
+
+// dx[q][ci] = sum_co sum_{r,s} g[co][q - (r-1, s-1)] * w[co][ci][r][s]
+template <int CIN, int COUT>
+__global__ void __launch_bounds__(256) head3x3_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ wgt,
+                                                            bf16* __restrict__ dx, long long dsN, long long dsH,
+                                                            long long dsW, int N, int H, int W, int tiles_w,
+                                                            int tiles_h) {
+  __shared__ float gt[COUT][(kHTH + 2) * (kHTW + 2)];
+  __shared__ float w_s[COUT][9][CIN];
+  int b = blockIdx.x;
+  const int tw = b % tiles_w;
+  b /= tiles_w;
+  const int th = b % tiles_h;
+  const int n = b / tiles_h;
+  const int h0 = th * kHTH, w0 = tw * kHTW;
+  for (int i = threadIdx.x; i < COUT * 9 * CIN; i += blockDim.x) {
+    const int ci = i % CIN, t = (i / CIN) % 9, co = i / (9 * CIN);
+    w_s[co][t][ci] = wgt[((long long)co * CIN + ci) * 9 + t];
+  }
+#pragma unroll
+  for (int co = 0; co < COUT; ++co) load_g_tile(g + ((long long)n * COUT + co) * H * W, H, W, h0, w0, gt[co]);
+  __syncthreads();
+  const int tx = threadIdx.x % kHTW, ty = threadIdx.x / kHTW;
+  const int h = h0 + ty, w = w0 + tx;
+  if (h >= H || w >= W) return;
+  float acc[CIN];
+#pragma unroll
+  for (int i = 0; i < CIN; ++i) acc[i] = 0.f;
+#pragma unroll
+  for (int co = 0; co < COUT; ++co)
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        // the output pixel q - (r-1, s-1) sits at tile offset (ty + 1 - (r-1), tx + 1 - (s-1))
+        const float gv = gt[co][(ty + 2 - r) * (kHTW + 2) + tx + 2 - s];
+#pragma unroll
+        for (int i = 0; i < CIN; ++i) acc[i] = fmaf(gv, w_s[co][r * 3 + s][i], acc[i]);
+      }
+  bf16* o = dx + n * dsN + h * dsH + w * dsW;
+#pragma unroll
+  for (int g8 = 0; g8 < CIN / 8; ++g8) {
+    F8 f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f.v[i] = acc[g8 * 8 + i];
+    st16(o + g8 * 8, pack8(f));
+  }
+}
+
+// dw[co][ci][r][s] += sum_q x[q + (r-1, s-1)][ci] * g[co][q] = sum_u x[u][ci] * g[co][u - (r-1, s-1)];  dbias[co] += sum g.
+// A thread owns 8 channels of one source pixel u per tile and keeps 9 x 8 partial products per class across ALL the
+// tiles of its (persistent) block; the block then adds its threads in a fixed order and stores one row
+// [COUT][CIN*9 + 1] of the partial table.
+template <int CIN, int COUT>
+__global__ void __launch_bounds__(256) head3x3_wgrad_kernel(HeadView x, const float* __restrict__ g,
+                                                            float* __restrict__ rows, int tiles_w, int tiles_h,
+                                                            int n_tiles) {
+  constexpr int CG = CIN / 8;
+  constexpr int PPT = 256 / CG;          // source pixels per pass of the block
+  constexpr int TPX = kHTW * kHTH;       // pixels per tile
+  __shared__ float gt[(kHTH + 2) * (kHTW + 2)];
+  __shared__ float s_dw[CIN * 9 + 1];
+  const int cgi = threadIdx.x % CG, pl = threadIdx.x / CG;
+  for (int co = 0; co < COUT; ++co) {
+    float acc[9][8];
+    float gsum = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[t][i] = 0.f;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int b = tile;
+      const int tw = b % tiles_w;
+      b /= tiles_w;
+      const int th = b % tiles_h;
+      const int n = b / tiles_h;
+      const int h0 = th * kHTH, w0 = tw * kHTW;
+      __syncthreads();  // previous tile's gradient values fully consumed
+      load_g_tile(g + ((long long)n * COUT + co) * x.H * x.W, x.H, x.W, h0, w0, gt);
+      __syncthreads();
+      for (int p = pl; p < TPX; p += PPT) {
+        const int ty = p / kHTW, tx = p - ty * kHTW;
+        const int h = h0 + ty, w = w0 + tx;
+        if (h >= x.H || w >= x.W) continue;
+        const F8 v = unpack8(ld16(x.ptr + n * x.sN + h * x.sH + w * x.sW + cgi * 8));
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s = 0; s < 3; ++s) {
+            const float gv = gt[(ty + 2 - r) * (kHTW + 2) + tx + 2 - s];  // g[u - (r-1, s-1)], zero outside the image
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[r * 3 + s][i] = fmaf(v.v[i], gv, acc[r * 3 + s][i]);
+          }
+        if (cgi == 0) gsum += gt[(ty + 1) * (kHTW + 2) + tx + 1];
+      }
+    }
+    // fixed-order block reduction: one pixel lane adds per round (distinct channel groups -> distinct slots)
+    __syncthreads();
+    for (int i = threadIdx.x; i < CIN * 9 + 1; i += blockDim.x) s_dw[i] = 0.f;
+    __syncthreads();
+    for (int q = 0; q < PPT; ++q) {
+      if (pl == q) {
+#pragma unroll
+        for (int t = 0; t < 9; ++t)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s_dw[(cgi * 8 + i) * 9 + t] += acc[t][i];
+        if (cgi == 0) s_dw[CIN * 9] += gsum;
+      }
+      __syncthreads();
+    }
+    float* row = rows + ((size_t)blockIdx.x * COUT + co) * (CIN * 9 + 1);
+    for (int i = threadIdx.x; i < CIN * 9 + 1; i += blockDim.x) row[i] = s_dw[i];
+  }
+}
+
+// rows [nrows][COUT][CIN*9 + 1] -> dw[(co*CIN + ci)*9 + t] += ..., dbias[co] += ... (rows added in index order)
+__global__ void head3x3_wgrad_finalize_kernel(const float* __restrict__ rows, int nrows, int cout, int cin9,
+                                              float* __restrict__ dw, float* __restrict__ dbias) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = cin9 + 1;
+  if (i >= cout * per) return;
+  const int co = i / per, k = i - co * per;
+  float a = 0.f;
+  for (int r = 0; r < nrows; ++r) a += rows[(size_t)r * cout * per + i];
+  if (k < cin9)
+    dw[(size_t)co * cin9 + k] += a;
+  else if (dbias)
+    dbias[co] += a;
+}
+
+static int head_view(const PdacView* v, HeadView* o, const char* what) {
+  PDAC_REQUIRE(v && v->ptr, "%s: null view", what);
+  PDAC_REQUIRE(((uintptr_t)v->ptr & 15) == 0 && v->sW % 8 == 0 && v->sH % 8 == 0 && v->sN % 8 == 0,
+               "%s: view must be 16-byte aligned", what);
+  o->ptr = (const bf16*)v->ptr;
+  o->sN = v->sN;
+  o->sH = v->sH;
+  o->sW = v->sW;
+  o->N = v->N;
+  o->H = v->H;
+  o->W = v->W;
+  return PDAC_OK;
+}
+
+}  // namespace pdac
+
+using namespace pdac;
+
+#define HEAD_DISPATCH(CALL)                                             \
+  if (x->C == 16 && classes == 1) { CALL(16, 1); }                      \
+  else if (x->C == 16 && classes == 2) { CALL(16, 2); }                 \
+  else if (x->C == 32 && classes == 1) { CALL(32, 1); }                 \
+  else if (x->C == 32 && classes == 2) { CALL(32, 2); }                 \
+  else return fail(PDAC_E_INVALID, "head3x3: %d channels / %d classes unsupported (16 or 32 channels, 1 or 2 classes)", x->C, classes)
+
+extern "C" int pdac_head3x3_supported(int channels, int classes) {
+  return (channels == 16 || channels == 32) && (classes == 1 || classes == 2);
+}
+
+extern "C" int pdac_head3x3_fwd(const PdacView* x, const float* weight, const float* bias, int classes, float* logits,
+                                void* stream) {
+  PDAC_REQUIRE(x && weight && logits, "head3x3_fwd: null argument");
+  HeadView xv;
+  PDAC_TRY(head_view(x, &xv, "head x"));
+  if ((long long)x->N * x->H * x->W == 0) return PDAC_OK;
+  const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
+  const int blocks = tiles_w * tiles_h * x->N;
+#define CALL(CI, CO) head3x3_fwd_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h)
+  HEAD_DISPATCH(CALL);
+#undef CALL
+  PDAC_LAUNCH_CHECK("head3x3_fwd");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_head3x3_dgrad(const float* grad_logits, const float* weight, int classes, const PdacView* dx,
+                                  void* stream) {
+  PDAC_REQUIRE(grad_logits && weight && dx, "head3x3_dgrad: null argument");
+  const PdacView* x = dx;
+  HeadView dv;
+  PDAC_TRY(head_view(dx, &dv, "head dx"));
+  if ((long long)x->N * x->H * x->W == 0) return PDAC_OK;
+  const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
+  const int blocks = tiles_w * tiles_h * x->N;
+#define CALL(CI, CO)                                                                                                  \
+  head3x3_dgrad_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(grad_logits, weight, (bf16*)dx->ptr, dx->sN, \
+                                                                         dx->sH, dx->sW, x->N, x->H, x->W, tiles_w, tiles_h)
+  HEAD_DISPATCH(CALL);
+#undef CALL
+  PDAC_LAUNCH_CHECK("head3x3_dgrad");
+  return PDAC_OK;
+}
+
+extern "C" int pdac_head3x3_wgrad(const PdacView* x, const float* grad_logits, int classes, float* dw, float* dbias,
+                                  float* scratch, long long scratch_bytes, void* stream) {
+  PDAC_REQUIRE(x && grad_logits && dw && scratch, "head3x3_wgrad: null argument (the scratch buffer is required)");
+  HeadView xv;
+  PDAC_TRY(head_view(x, &xv, "head x"));
+  if ((long long)x->N * x->H * x->W == 0) return PDAC_OK;
+  const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
+  const int n_tiles = tiles_w * tiles_h * x->N;
+  const int per = x->C * 9 + 1;
+  int blocks = 2 * num_sms();
+  if (blocks > n_tiles) blocks = n_tiles;
+  PDAC_REQUIRE((long long)blocks * classes * per * (long long)sizeof(float) <= scratch_bytes,
+               "head3x3_wgrad: scratch too small (%lld bytes needed)", (long long)blocks * classes * per * 4);
+#define CALL(CI, CO) head3x3_wgrad_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, grad_logits, scratch, tiles_w, tiles_h, n_tiles)
+  HEAD_DISPATCH(CALL);
+#undef CALL
+  PDAC_LAUNCH_CHECK("head3x3_wgrad");
+  head3x3_wgrad_finalize_kernel<<<ceil_div(classes * per, 128), 128, 0, (cudaStream_t)stream>>>(scratch, blocks, classes,
+                                                                                                x->C * 9, dw, dbias);
+  PDAC_LAUNCH_CHECK("head3x3_wgrad_finalize");
+  return PDAC_OK;
+}

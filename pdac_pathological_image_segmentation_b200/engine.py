@@ -513,6 +513,29 @@ def logits_head(tape: Tape, x, n_classes, out_hw, align_corners):
     return out, feed
 
 
+def head_conv3x3(tape: Tape, m: Conv2d, x):
+    """smp SegmentationHead at full resolution, Conv2d(C, classes, 3, padding=1) + bias -> fp32 NCHW logits, on the
+    direct kernels of head.cu (fp32 master weights; no 16-channel padded tensors). -> (logits, feed_grad(g))."""
+    w = m.weight.detach()
+    bias = m.bias.detach() if m.bias is not None else None
+    out = ops.head3x3_fwd(x, w, bias)
+
+    def feed(g):
+        g = g.contiguous()
+        ops.head3x3_wgrad(x, g, tape.arena.slot(m.weight), tape.arena.slot(m.bias) if m.bias is not None else None)
+        if tape.wants(x):
+            old = tape.pop(x)
+            dx = ops.head3x3_dgrad(g, w, tuple(x.shape))
+            if old is not None:
+                ops.add(old, dx, out=dx)
+            tape.put(x, dx)
+    feed.nhwc_cpad = None
+    # feed() runs before the tape's backward steps: this (first executed) step only reports the head's parameters as
+    # complete to the data-parallel reducer
+    tape.record(lambda: None, (m.weight, m.bias))
+    return out, feed
+
+
 # ------------------------------------------------------------------------------------------------ ResNet18 encoder
 def basic_block(tape: Tape, blk, x):
     """torchvision BasicBlock.forward (resnet.py:89-106): relu(bn2(conv2(relu(bn1(conv1 x)))) + shortcut(x))."""

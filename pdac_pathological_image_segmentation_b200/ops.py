@@ -594,6 +594,45 @@ def dwconv3x3_wgrad(x, dy, dil, out):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ segmentation head
+def head3x3_supported(channels, classes):
+    return bool(_lib.load().pdac_head3x3_supported(int(channels), int(classes)))
+
+
+def head3x3_fwd(x, weight, bias, out=None):
+    """Conv2d(C, classes, 3, padding=1) + bias on bf16 NHWC x with the fp32 state_dict weight -> fp32 NCHW logits."""
+    classes = weight.shape[0]
+    assert weight.dtype == torch.float32 and weight.is_contiguous() and tuple(weight.shape[1:]) == (x.shape[3], 3, 3)
+    if out is None:
+        out = torch.empty((x.shape[0], classes, x.shape[1], x.shape[2]), dtype=torch.float32, device=x.device)
+    call("pdac_head3x3_fwd", _vp(x), _ptr(weight), _ptr(bias), classes, _ptr(out), _stream(),
+         flops=2 * x.shape[0] * x.shape[1] * x.shape[2] * classes * x.shape[3] * 9, nbytes=_act_bytes(x, out),
+         tag=f"head fwd {tuple(x.shape)} -> {classes}")
+    return out
+
+
+def head3x3_dgrad(g, weight, in_shape):
+    """g fp32 NCHW (N, classes, H, W) -> dx bf16 NHWC (N, H, W, C)."""
+    _need_cuda(g, "gradient")
+    g = g.contiguous()
+    assert g.dtype == torch.float32
+    n, h, w, c = in_shape
+    dx = empty_act(n, h, w, c, g.device)
+    call("pdac_head3x3_dgrad", _ptr(g), _ptr(weight), weight.shape[0], _vp(dx), _stream(),
+         flops=2 * n * h * w * weight.shape[0] * c * 9, nbytes=_act_bytes(g, dx), tag=f"head dgrad {tuple(dx.shape)}")
+    return dx
+
+
+def head3x3_wgrad(x, g, dw, dbias=None):
+    """Accumulates dw fp32 [classes, C, 3, 3] and dbias fp32 [classes] (state_dict layouts); fixed-order reduction."""
+    g = g.contiguous()
+    sc = scratch(x.device)
+    call("pdac_head3x3_wgrad", _vp(x), _ptr(g), g.shape[1], _ptr(dw), _ptr(dbias), C.c_void_p(sc.data_ptr()),
+         sc.numel() * 4, _stream(), flops=2 * x.numel() * g.shape[1] * 9, nbytes=_act_bytes(x, g),
+         tag=f"head wgrad {tuple(x.shape)}")
+    return dw
+
+
 # ------------------------------------------------------------------------------------------------ loss / metric
 def _tgt(t):
     _need_cuda(t, "target")

@@ -71,6 +71,9 @@ class _SmpBase(SegModule):
 
     def _head(self, tape, x, upsampling):
         conv = getattr(self.segmentation_head, "0")
+        if (upsampling == 1 and conv.k == 3 and conv.padding == 1 and conv.stride == 1 and conv.dilation == 1
+                and E.ops.head3x3_supported(x.shape[3], self.classes)):
+            return E.head_conv3x3(tape, conv, x)        # Unet: full-resolution head, direct kernels (head.cu)
         y = E.conv_bias_act(tape, conv, [x], relu=False)
         out_hw = (x.shape[1] * upsampling, x.shape[2] * upsampling)
         return E.logits_head(tape, y, self.classes, out_hw, True)      # UpsamplingBilinear2d: align_corners=True
