@@ -11,10 +11,13 @@
 // fp32 master weights are used directly (no bf16 copy): the arithmetic is fp32 on bf16 activations.
 #include "common.h"
 #include "vec.cuh"
+#include <stdlib.h>
 
 namespace pdac {
 
 static constexpr int kHTW = 32, kHTH = 8;  // output tile (one pixel per thread)
+
+__device__ __forceinline__ uint32_t smem_u32_h(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 struct HeadView {
   const bf16* ptr;
@@ -45,6 +48,193 @@ __device__ __forceinline__ void load_g_tile(const float* __restrict__ g, int H, 
     const int ty = i / (kHTW + 2), tx = i - ty * (kHTW + 2);
     const int h = h0 + ty - 1, w = w0 + tx - 1;
     tile[i] = (h >= 0 && h < H && w >= 0 && w < W) ? __ldg(g + (long long)h * W + w) : 0.f;
+  }
+}
+
+// ---- warp-level tensor-core helpers (mma.sync m16n8k16, bf16 x bf16 -> fp32): the head is far too small for a
+// tcgen05 pipeline (N = 1 or 2) but at 144 MACs per pixel the scalar version above is instruction-bound at ~1.1 TB/s;
+// with the pixels as the M (forward) or K (weight gradient) dimension of warp MMAs it is HBM-bound.
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// Forward on warp MMAs: a warp owns one row of the 32 x 8 tile = two segments of 16 pixels (M); K = the CIN channels of
+// one tap (ldmatrix straight from the haloed shared-memory tile, shifted by the tap); N = 8 with the classes in the
+// first columns (weights rounded to bf16, as the tensor-core convolutions have them). fp32 accumulation over the 9 taps.
+template <int CIN, int COUT>
+__global__ void __launch_bounds__(256) head3x3_fwd_mma_kernel(HeadView x, const float* __restrict__ wgt,
+                                                              const float* __restrict__ bias, float* __restrict__ out,
+                                                              int tiles_w, int tiles_h) {
+  constexpr int CG = CIN / 8, KS = CIN / 16;
+  __shared__ __align__(16) uint4 tile[(kHTH + 2) * (kHTW + 2) * CG];
+  int b = blockIdx.x;
+  const int tw = b % tiles_w;
+  b /= tiles_w;
+  const int th = b % tiles_h;
+  const int n = b / tiles_h;
+  const int h0 = th * kHTH, w0 = tw * kHTW;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int gid = lane >> 2, tid = lane & 3;
+  // B fragments: B[k = ci][n = class]; this lane holds k = tid*2, tid*2+1 (b0) and +8 (b1) of column n = gid
+  uint32_t bw[9][KS][2];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+      for (int hlf = 0; hlf < 2; ++hlf) {
+        float v0 = 0.f, v1 = 0.f;
+        if (gid < COUT) {
+          const int ci = ks * 16 + hlf * 8 + tid * 2;
+          v0 = wgt[((long long)gid * CIN + ci) * 9 + t];
+          v1 = wgt[((long long)gid * CIN + ci + 1) * 9 + t];
+        }
+        bw[t][ks][hlf] = pack2(v0, v1);
+      }
+  load_x_tile<CIN>(x, n, h0, w0, tile);
+  __syncthreads();
+  const uint32_t tbase = smem_u32_h(tile);
+  constexpr int PITCH = CIN * 2;  // bytes per pixel
+  const int ty = warp;            // tile row of this warp
+#pragma unroll
+  for (int seg = 0; seg < 2; ++seg) {
+    float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        // ldmatrix lane address: matrix j = lane / 8: pixels (j & 1) * 8 + lane % 8, channels (j >> 1) * 8 ..
+        const int px = seg * 16 + s + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const uint32_t addr = tbase + (uint32_t)(((ty + r) * (kHTW + 2) + px) * PITCH + (lane >> 4) * 16);
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          uint32_t a[4];
+          ldsm_x4(addr + ks * 32, a);
+          mma_bf16_16816(d, a, bw[r * 3 + s][ks][0], bw[r * 3 + s][ks][1]);
+        }
+      }
+    // d[0], d[1] = classes tid*2, tid*2+1 of pixel gid; d[2], d[3] of pixel gid + 8: the classes sit in columns 0..1
+    if (tid == 0) {
+      const int h = h0 + ty;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int w = w0 + seg * 16 + gid + half * 8;
+        if (h < x.H && w < x.W) {
+#pragma unroll
+          for (int co = 0; co < COUT; ++co)
+            out[(((long long)n * COUT + co) * x.H + h) * x.W + w] = d[half * 2 + co] + (bias ? bias[co] : 0.f);
+        }
+      }
+    }
+  }
+}
+
+// Weight gradient on warp MMAs, one class per pass: D[m = tap][n = ci] += sum_k A[m][k] B[k][n] with k = the 16 pixels u
+// of a segment, A[tap][k] = bf16(g[u_k - off_tap]) built from the haloed fp32 gradient tile and B[k][ci] = x[u_k][ci]
+// (ldmatrix.trans from the pixel-major tile). The 16 x CIN accumulators stay in registers over all tiles of the
+// (persistent) block; warps and blocks are then added in index order (reproducible).
+template <int CIN, int COUT>
+__global__ void __launch_bounds__(256) head3x3_wgrad_mma_kernel(HeadView x, const float* __restrict__ g,
+                                                                float* __restrict__ rows, int tiles_w, int tiles_h,
+                                                                int n_tiles) {
+  constexpr int CG = CIN / 8, NT = CIN / 8;  // NT n-tiles of 8 input channels
+  __shared__ __align__(16) uint4 tile[kHTH * kHTW * CG];  // source pixels of the tile (no halo), pixel-major
+  __shared__ float gt[(kHTH + 2) * (kHTW + 2)];
+  __shared__ float red[8][16 * CIN + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int gid = lane >> 2, tid = lane & 3;
+  const uint32_t tbase = smem_u32_h(tile);
+  constexpr int PITCH = CIN * 2;
+  for (int co = 0; co < COUT; ++co) {
+    float d[NT][4];
+#pragma unroll
+    for (int i = 0; i < NT; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) d[i][j] = 0.f;
+    float gsum = 0.f;
+    for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+      int b = tl;
+      const int tw = b % tiles_w;
+      b /= tiles_w;
+      const int th = b % tiles_h;
+      const int n = b / tiles_h;
+      const int h0 = th * kHTH, w0 = tw * kHTW;
+      __syncthreads();  // previous tile fully consumed
+      load_g_tile(g + ((long long)n * COUT + co) * x.H * x.W, x.H, x.W, h0, w0, gt);
+      for (int i = threadIdx.x; i < kHTH * kHTW * CG; i += blockDim.x) {
+        const int cgi = i % CG, px = i / CG;
+        const int ty = px / kHTW, tx = px - ty * kHTW;
+        const int h = h0 + ty, w = w0 + tx;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (h < x.H && w < x.W) v = ld16(x.ptr + n * x.sN + h * x.sH + w * x.sW + cgi * 8);
+        tile[i] = v;
+      }
+      __syncthreads();
+      const int ty = warp;
+#pragma unroll
+      for (int seg = 0; seg < 2; ++seg) {
+        // A fragment: rows gid (tap gid) and gid + 8 (tap 8 for gid == 0, else zero), k = tid*2, tid*2+1, +8, +9
+        uint32_t a[4];
+        const int r0 = gid / 3, s0 = gid - r0 * 3;
+        const float* grow = gt + (ty + 2 - r0) * (kHTW + 2) + seg * 16 + 2 - s0;   // g[u - (r-1, s-1)]
+        const float g0 = grow[tid * 2], g1 = grow[tid * 2 + 1], g2 = grow[tid * 2 + 8], g3 = grow[tid * 2 + 9];
+        a[0] = pack2(g0, g1);
+        a[2] = pack2(g2, g3);
+        a[1] = a[3] = 0u;
+        if (gid == 0) {  // tap 8 = (r, s) = (2, 2)
+          const float* g8 = gt + (ty + 0) * (kHTW + 2) + seg * 16 + 0;
+          a[1] = pack2(g8[tid * 2], g8[tid * 2 + 1]);
+          a[3] = pack2(g8[tid * 2 + 8], g8[tid * 2 + 9]);
+        }
+        if (gid == 4) gsum += (g0 + g1) + (g2 + g3);  // tap 4 is the centre: every pixel of the segment exactly once
+        // B fragments of all n-tiles: matrix j of an x4 load = pixels (j & 1) * 8 .., channels (j >> 1) * 8 ..
+        const int px = seg * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+#pragma unroll
+        for (int np = 0; np < NT / 2; ++np) {
+          uint32_t bb[4];
+          ldsm_x4_trans(tbase + (uint32_t)((ty * kHTW + px) * PITCH + np * 32 + (lane >> 4) * 16), bb);
+          mma_bf16_16816(d[np * 2], a, bb[0], bb[1]);
+          mma_bf16_16816(d[np * 2 + 1], a, bb[2], bb[3]);
+        }
+      }
+    }
+    // warp -> shared -> fixed-order sum over the 8 warps -> this block's row [CIN*9 + 1]
+    __syncthreads();
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      // d[nt][0], [1]: tap gid, channels nt*8 + tid*2, +1; d[nt][2], [3]: tap gid + 8
+      red[warp][gid * CIN + nt * 8 + tid * 2] = d[nt][0];
+      red[warp][gid * CIN + nt * 8 + tid * 2 + 1] = d[nt][1];
+      red[warp][(gid + 8) * CIN + nt * 8 + tid * 2] = d[nt][2];
+      red[warp][(gid + 8) * CIN + nt * 8 + tid * 2 + 1] = d[nt][3];
+    }
+    // bias gradient: the four tid lanes of gid == 4 hold partial sums: add them in lane order
+    float gs = gsum;
+    gs += __shfl_down_sync(0xffffffffu, gs, 2, 4);
+    gs += __shfl_down_sync(0xffffffffu, gs, 1, 4);
+    if (lane == 16) red[warp][16 * CIN] = gs;
+    __syncthreads();
+    float* row = rows + ((size_t)blockIdx.x * COUT + co) * (CIN * 9 + 1);
+    for (int i = threadIdx.x; i < CIN * 9 + 1; i += blockDim.x) {
+      float v = 0.f;
+      if (i < CIN * 9) {
+        const int ci = i / 9, t = i - ci * 9;  // state_dict order within a class: [ci][tap]
+        for (int w8 = 0; w8 < 8; ++w8) v += red[w8][t * CIN + ci];
+      } else {
+        for (int w8 = 0; w8 < 8; ++w8) v += red[w8][16 * CIN];
+      }
+      row[i] = v;
+    }
   }
 }
 
@@ -239,6 +429,16 @@ static int head_view(const PdacView* v, HeadView* o, const char* what) {
 
 using namespace pdac;
 
+// PDAC_HEAD_SCALAR=1: the CUDA-core versions of forward / weight gradient (A-B timing, debugging)
+static int head_scalar() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PDAC_HEAD_SCALAR");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v;
+}
+
 #define HEAD_DISPATCH(CALL)                                             \
   if (x->C == 16 && classes == 1) { CALL(16, 1); }                      \
   else if (x->C == 16 && classes == 2) { CALL(16, 2); }                 \
@@ -258,7 +458,11 @@ extern "C" int pdac_head3x3_fwd(const PdacView* x, const float* weight, const fl
   if ((long long)x->N * x->H * x->W == 0) return PDAC_OK;
   const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
   const int blocks = tiles_w * tiles_h * x->N;
-#define CALL(CI, CO) head3x3_fwd_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h)
+#define CALL(CI, CO)                                                                                              \
+  if (head_scalar())                                                                                              \
+    head3x3_fwd_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h); \
+  else                                                                                                            \
+    head3x3_fwd_mma_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h)
   HEAD_DISPATCH(CALL);
 #undef CALL
   PDAC_LAUNCH_CHECK("head3x3_fwd");
@@ -296,7 +500,11 @@ extern "C" int pdac_head3x3_wgrad(const PdacView* x, const float* grad_logits, i
   if (blocks > n_tiles) blocks = n_tiles;
   PDAC_REQUIRE((long long)blocks * classes * per * (long long)sizeof(float) <= scratch_bytes,
                "head3x3_wgrad: scratch too small (%lld bytes needed)", (long long)blocks * classes * per * 4);
-#define CALL(CI, CO) head3x3_wgrad_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, grad_logits, scratch, tiles_w, tiles_h, n_tiles)
+#define CALL(CI, CO)                                                                                                   \
+  if (head_scalar())                                                                                                   \
+    head3x3_wgrad_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, grad_logits, scratch, tiles_w, tiles_h, n_tiles); \
+  else                                                                                                                 \
+    head3x3_wgrad_mma_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, grad_logits, scratch, tiles_w, tiles_h, n_tiles)
   HEAD_DISPATCH(CALL);
 #undef CALL
   PDAC_LAUNCH_CHECK("head3x3_wgrad");

@@ -16,9 +16,11 @@ def test_head3x3_fwd_dgrad_wgrad(shape, classes):
     N, C, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(7)
     x = torch.randn(N, C, H, W, device=DEV, generator=g).to(torch.bfloat16)
-    w = torch.randn(classes, C, 3, 3, device=DEV, generator=g) * 0.2
+    # bf16-representable weights and gradient: the warp-MMA forward rounds the weights, the weight gradient rounds
+    # dL/dlogits to bf16 (as the tensor-core convolutions do); products and the fp32 accumulation are then exact
+    w = (torch.randn(classes, C, 3, 3, device=DEV, generator=g) * 0.2).to(torch.bfloat16).float()
     b = torch.randn(classes, device=DEV, generator=g)
-    go = torch.randn(N, classes, H, W, device=DEV, generator=g)
+    go = torch.randn(N, classes, H, W, device=DEV, generator=g).to(torch.bfloat16).float()
     assert ops.head3x3_supported(C, classes)
     xr = x.float().requires_grad_(True)
     wr = w.clone().requires_grad_(True)
