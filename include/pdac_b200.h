@@ -274,7 +274,7 @@ int pdac_dwconv3x3_wgrad(const PdacView* x, const PdacView* dy, int dil, float* 
  * HBM-bound kernels (a tensor-core GEMM with N = 1 would write and re-read 16-channel padded tensors).
  * weight: the fp32 state_dict tensor [classes][C][3][3], bias fp32 [classes] or NULL; logits / grad_logits: fp32 NCHW
  * (N, classes, H, W) — what the reference's callers see (train_worker.py:70-79). dw / dbias are accumulated into (state_dict
- * layouts); scratch: fp32, >= 296 * classes * (9*C + 1) floats (fixed-order partial rows: reproducible). */
+ * layouts); scratch: fp32, >= 592 * classes * (9*C + 1) floats (fixed-order partial rows: reproducible). */
 int pdac_head3x3_supported(int channels, int classes); /* 1 / 0, no status code */
 int pdac_head3x3_fwd(const PdacView* x, const float* weight, const float* bias, int classes, float* logits,
                      void* stream);

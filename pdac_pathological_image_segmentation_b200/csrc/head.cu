@@ -51,6 +51,72 @@ __device__ __forceinline__ void load_g_tile(const float* __restrict__ g, int H, 
   }
 }
 
+// Register prefetch of the NEXT tile while the current one is computed from shared memory (the blocks are persistent:
+// with one small tile per block the kernels were bound by the load -> barrier -> compute latency chain at ~1 TB/s).
+__device__ __forceinline__ void decode_tile(int tile, int tiles_w, int tiles_h, int& n, int& h0, int& w0) {
+  const int tw = tile % tiles_w;
+  tile /= tiles_w;
+  const int th = tile % tiles_h;
+  n = tile / tiles_h;
+  h0 = th * kHTH;
+  w0 = tw * kHTW;
+}
+// HALO = 1: (kHTH+2) x (kHTW+2) pixels starting one pixel up-left of the tile; HALO = 0: the tile's own pixels
+template <int CIN, int HALO>
+struct XPrefetch {
+  static constexpr int CG = CIN / 8;
+  static constexpr int TWP = kHTW + 2 * HALO, THP = kHTH + 2 * HALO;
+  static constexpr int TOTAL = TWP * THP * CG;
+  static constexpr int NL = (TOTAL + 255) / 256;
+  uint4 buf[NL];
+  __device__ __forceinline__ void issue(const HeadView& x, int n, int h0, int w0) {
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      const int i = threadIdx.x + j * 256;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (i < TOTAL) {
+        const int g = i % CG, px = i / CG;
+        const int ty = px / TWP, tx = px - ty * TWP;
+        const int h = h0 + ty - HALO, w = w0 + tx - HALO;
+        if (h >= 0 && h < x.H && w >= 0 && w < x.W) v = ld16(x.ptr + n * x.sN + h * x.sH + w * x.sW + g * 8);
+      }
+      buf[j] = v;
+    }
+  }
+  __device__ __forceinline__ void store(uint4* tile) const {
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      const int i = threadIdx.x + j * 256;
+      if (i < TOTAL) tile[i] = buf[j];
+    }
+  }
+};
+struct GPrefetch {  // haloed fp32 gradient tile of one class
+  static constexpr int TOTAL = (kHTH + 2) * (kHTW + 2);
+  static constexpr int NL = (TOTAL + 255) / 256;
+  float buf[NL];
+  __device__ __forceinline__ void issue(const float* __restrict__ g, int H, int W, int h0, int w0) {
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      const int i = threadIdx.x + j * 256;
+      float v = 0.f;
+      if (i < TOTAL) {
+        const int ty = i / (kHTW + 2), tx = i - ty * (kHTW + 2);
+        const int h = h0 + ty - 1, w = w0 + tx - 1;
+        if (h >= 0 && h < H && w >= 0 && w < W) v = __ldg(g + (long long)h * W + w);
+      }
+      buf[j] = v;
+    }
+  }
+  __device__ __forceinline__ void store(float* tile) const {
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      const int i = threadIdx.x + j * 256;
+      if (i < TOTAL) tile[i] = buf[j];
+    }
+  }
+};
+
 // ---- warp-level tensor-core helpers (mma.sync m16n8k16, bf16 x bf16 -> fp32): the head is far too small for a
 // tcgen05 pipeline (N = 1 or 2) but at 144 MACs per pixel the scalar version above is instruction-bound at ~1.1 TB/s;
 // with the pixels as the M (forward) or K (weight gradient) dimension of warp MMAs it is HBM-bound.
@@ -74,15 +140,9 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 template <int CIN, int COUT>
 __global__ void __launch_bounds__(256) head3x3_fwd_mma_kernel(HeadView x, const float* __restrict__ wgt,
                                                               const float* __restrict__ bias, float* __restrict__ out,
-                                                              int tiles_w, int tiles_h) {
+                                                              int tiles_w, int tiles_h, int n_tiles) {
   constexpr int CG = CIN / 8, KS = CIN / 16;
   __shared__ __align__(16) uint4 tile[(kHTH + 2) * (kHTW + 2) * CG];
-  int b = blockIdx.x;
-  const int tw = b % tiles_w;
-  b /= tiles_w;
-  const int th = b % tiles_h;
-  const int n = b / tiles_h;
-  const int h0 = th * kHTH, w0 = tw * kHTW;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int gid = lane >> 2, tid = lane & 3;
   // B fragments: B[k = ci][n = class]; this lane holds k = tid*2, tid*2+1 (b0) and +8 (b1) of column n = gid
@@ -101,38 +161,56 @@ __global__ void __launch_bounds__(256) head3x3_fwd_mma_kernel(HeadView x, const 
         }
         bw[t][ks][hlf] = pack2(v0, v1);
       }
-  load_x_tile<CIN>(x, n, h0, w0, tile);
-  __syncthreads();
+  float bv[COUT];
+#pragma unroll
+  for (int co = 0; co < COUT; ++co) bv[co] = bias ? bias[co] : 0.f;
   const uint32_t tbase = smem_u32_h(tile);
   constexpr int PITCH = CIN * 2;  // bytes per pixel
   const int ty = warp;            // tile row of this warp
+  XPrefetch<CIN, 1> pf;
+  int n, h0, w0;
+  if ((int)blockIdx.x < n_tiles) {
+    decode_tile(blockIdx.x, tiles_w, tiles_h, n, h0, w0);
+    pf.issue(x, n, h0, w0);
+  }
+  for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+    decode_tile(tl, tiles_w, tiles_h, n, h0, w0);
+    __syncthreads();  // the previous tile has been consumed
+    pf.store(tile);
+    __syncthreads();
+    if (tl + (int)gridDim.x < n_tiles) {  // next tile's loads fly while this one is computed
+      int n2, h2, w2;
+      decode_tile(tl + gridDim.x, tiles_w, tiles_h, n2, h2, w2);
+      pf.issue(x, n2, h2, w2);
+    }
 #pragma unroll
-  for (int seg = 0; seg < 2; ++seg) {
-    float d[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int seg = 0; seg < 2; ++seg) {
+      float d[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
+      for (int r = 0; r < 3; ++r)
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
-        // ldmatrix lane address: matrix j = lane / 8: pixels (j & 1) * 8 + lane % 8, channels (j >> 1) * 8 ..
-        const int px = seg * 16 + s + (lane & 7) + ((lane >> 3) & 1) * 8;
-        const uint32_t addr = tbase + (uint32_t)(((ty + r) * (kHTW + 2) + px) * PITCH + (lane >> 4) * 16);
+        for (int s = 0; s < 3; ++s) {
+          // ldmatrix lane address: matrix j = lane / 8: pixels (j & 1) * 8 + lane % 8, channels (j >> 1) * 8 ..
+          const int px = seg * 16 + s + (lane & 7) + ((lane >> 3) & 1) * 8;
+          const uint32_t addr = tbase + (uint32_t)(((ty + r) * (kHTW + 2) + px) * PITCH + (lane >> 4) * 16);
 #pragma unroll
-        for (int ks = 0; ks < KS; ++ks) {
-          uint32_t a[4];
-          ldsm_x4(addr + ks * 32, a);
-          mma_bf16_16816(d, a, bw[r * 3 + s][ks][0], bw[r * 3 + s][ks][1]);
+          for (int ks = 0; ks < KS; ++ks) {
+            uint32_t a[4];
+            ldsm_x4(addr + ks * 32, a);
+            mma_bf16_16816(d, a, bw[r * 3 + s][ks][0], bw[r * 3 + s][ks][1]);
+          }
         }
-      }
-    // d[0], d[1] = classes tid*2, tid*2+1 of pixel gid; d[2], d[3] of pixel gid + 8: the classes sit in columns 0..1
-    if (tid == 0) {
-      const int h = h0 + ty;
+      // d[0], d[1] = classes tid*2, tid*2+1 of pixel gid; d[2], d[3] of pixel gid + 8: the classes sit in columns 0..1
+      if (tid == 0) {
+        const int h = h0 + ty;
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int w = w0 + seg * 16 + gid + half * 8;
-        if (h < x.H && w < x.W) {
+        for (int half = 0; half < 2; ++half) {
+          const int w = w0 + seg * 16 + gid + half * 8;
+          if (h < x.H && w < x.W) {
 #pragma unroll
-          for (int co = 0; co < COUT; ++co)
-            out[(((long long)n * COUT + co) * x.H + h) * x.W + w] = d[half * 2 + co] + (bias ? bias[co] : 0.f);
+            for (int co = 0; co < COUT; ++co)
+              out[(((long long)n * COUT + co) * x.H + h) * x.W + w] = d[half * 2 + co] + bv[co];
+          }
         }
       }
     }
@@ -148,7 +226,8 @@ __global__ void __launch_bounds__(256) head3x3_wgrad_mma_kernel(HeadView x, cons
                                                                 float* __restrict__ rows, int tiles_w, int tiles_h,
                                                                 int n_tiles) {
   constexpr int CG = CIN / 8, NT = CIN / 8;  // NT n-tiles of 8 input channels
-  __shared__ __align__(16) uint4 tile[kHTH * kHTW * CG];  // source pixels of the tile (no halo), pixel-major
+  (void)CG;
+  __shared__ __align__(16) uint4 tile[kHTH * kHTW * (CIN / 8)];  // source pixels of the tile (no halo), pixel-major
   __shared__ float gt[(kHTH + 2) * (kHTW + 2)];
   __shared__ float red[8][16 * CIN + 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -162,24 +241,25 @@ __global__ void __launch_bounds__(256) head3x3_wgrad_mma_kernel(HeadView x, cons
 #pragma unroll
       for (int j = 0; j < 4; ++j) d[i][j] = 0.f;
     float gsum = 0.f;
+    XPrefetch<CIN, 0> pfx;
+    GPrefetch pfg;
+    {
+      int n, h0, w0;
+      decode_tile(blockIdx.x, tiles_w, tiles_h, n, h0, w0);  // gridDim.x <= n_tiles
+      pfx.issue(x, n, h0, w0);
+      pfg.issue(g + ((long long)n * COUT + co) * x.H * x.W, x.H, x.W, h0, w0);
+    }
     for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
-      int b = tl;
-      const int tw = b % tiles_w;
-      b /= tiles_w;
-      const int th = b % tiles_h;
-      const int n = b / tiles_h;
-      const int h0 = th * kHTH, w0 = tw * kHTW;
       __syncthreads();  // previous tile fully consumed
-      load_g_tile(g + ((long long)n * COUT + co) * x.H * x.W, x.H, x.W, h0, w0, gt);
-      for (int i = threadIdx.x; i < kHTH * kHTW * CG; i += blockDim.x) {
-        const int cgi = i % CG, px = i / CG;
-        const int ty = px / kHTW, tx = px - ty * kHTW;
-        const int h = h0 + ty, w = w0 + tx;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (h < x.H && w < x.W) v = ld16(x.ptr + n * x.sN + h * x.sH + w * x.sW + cgi * 8);
-        tile[i] = v;
-      }
+      pfx.store(tile);
+      pfg.store(gt);
       __syncthreads();
+      if (tl + (int)gridDim.x < n_tiles) {  // next tile's loads fly while this one is computed
+        int n2, h2, w2;
+        decode_tile(tl + gridDim.x, tiles_w, tiles_h, n2, h2, w2);
+        pfx.issue(x, n2, h2, w2);
+        pfg.issue(g + ((long long)n2 * COUT + co) * x.H * x.W, x.H, x.W, h2, w2);
+      }
       const int ty = warp;
 #pragma unroll
       for (int seg = 0; seg < 2; ++seg) {
@@ -282,51 +362,62 @@ __global__ void __launch_bounds__(256) head3x3_fwd_kernel(HeadView x, const floa
   }
 }
 
-// dx[q][ci] = sum_co sum_{r,s} g[co][q - (r-1, s-1)] * w[co][ci][r][s]
+// dx[q][ci] = sum_co sum_{r,s} g[co][q - (r-1, s-1)] * w[co][ci][r][s]   (persistent blocks, next tile prefetched)
 template <int CIN, int COUT>
 __global__ void __launch_bounds__(256) head3x3_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ wgt,
                                                             bf16* __restrict__ dx, long long dsN, long long dsH,
                                                             long long dsW, int N, int H, int W, int tiles_w,
-                                                            int tiles_h) {
+                                                            int tiles_h, int n_tiles) {
   __shared__ float gt[COUT][(kHTH + 2) * (kHTW + 2)];
   __shared__ float w_s[COUT][9][CIN];
-  int b = blockIdx.x;
-  const int tw = b % tiles_w;
-  b /= tiles_w;
-  const int th = b % tiles_h;
-  const int n = b / tiles_h;
-  const int h0 = th * kHTH, w0 = tw * kHTW;
   for (int i = threadIdx.x; i < COUT * 9 * CIN; i += blockDim.x) {
     const int ci = i % CIN, t = (i / CIN) % 9, co = i / (9 * CIN);
     w_s[co][t][ci] = wgt[((long long)co * CIN + ci) * 9 + t];
   }
+  GPrefetch pf[COUT];
+  int n, h0, w0;
+  if ((int)blockIdx.x < n_tiles) {
+    decode_tile(blockIdx.x, tiles_w, tiles_h, n, h0, w0);
 #pragma unroll
-  for (int co = 0; co < COUT; ++co) load_g_tile(g + ((long long)n * COUT + co) * H * W, H, W, h0, w0, gt[co]);
-  __syncthreads();
+    for (int co = 0; co < COUT; ++co) pf[co].issue(g + ((long long)n * COUT + co) * H * W, H, W, h0, w0);
+  }
   const int tx = threadIdx.x % kHTW, ty = threadIdx.x / kHTW;
-  const int h = h0 + ty, w = w0 + tx;
-  if (h >= H || w >= W) return;
-  float acc[CIN];
+  for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
+    decode_tile(tl, tiles_w, tiles_h, n, h0, w0);
+    __syncthreads();
 #pragma unroll
-  for (int i = 0; i < CIN; ++i) acc[i] = 0.f;
+    for (int co = 0; co < COUT; ++co) pf[co].store(gt[co]);
+    __syncthreads();
+    if (tl + (int)gridDim.x < n_tiles) {
+      int n2, h2, w2;
+      decode_tile(tl + gridDim.x, tiles_w, tiles_h, n2, h2, w2);
 #pragma unroll
-  for (int co = 0; co < COUT; ++co)
+      for (int co = 0; co < COUT; ++co) pf[co].issue(g + ((long long)n2 * COUT + co) * H * W, H, W, h2, w2);
+    }
+    const int h = h0 + ty, w = w0 + tx;
+    if (h >= H || w >= W) continue;
+    float acc[CIN];
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
+    for (int i = 0; i < CIN; ++i) acc[i] = 0.f;
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
-        // the output pixel q - (r-1, s-1) sits at tile offset (ty + 1 - (r-1), tx + 1 - (s-1))
-        const float gv = gt[co][(ty + 2 - r) * (kHTW + 2) + tx + 2 - s];
+    for (int co = 0; co < COUT; ++co)
 #pragma unroll
-        for (int i = 0; i < CIN; ++i) acc[i] = fmaf(gv, w_s[co][r * 3 + s][i], acc[i]);
-      }
-  bf16* o = dx + n * dsN + h * dsH + w * dsW;
+      for (int r = 0; r < 3; ++r)
 #pragma unroll
-  for (int g8 = 0; g8 < CIN / 8; ++g8) {
-    F8 f;
+        for (int s = 0; s < 3; ++s) {
+          // the output pixel q - (r-1, s-1) sits at tile offset (ty + 1 - (r-1), tx + 1 - (s-1))
+          const float gv = gt[co][(ty + 2 - r) * (kHTW + 2) + tx + 2 - s];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) f.v[i] = acc[g8 * 8 + i];
-    st16(o + g8 * 8, pack8(f));
+          for (int i = 0; i < CIN; ++i) acc[i] = fmaf(gv, w_s[co][r * 3 + s][i], acc[i]);
+        }
+    bf16* o = dx + n * dsN + h * dsH + w * dsW;
+#pragma unroll
+    for (int g8 = 0; g8 < CIN / 8; ++g8) {
+      F8 f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f.v[i] = acc[g8 * 8 + i];
+      st16(o + g8 * 8, pack8(f));
+    }
   }
 }
 
@@ -457,12 +548,15 @@ extern "C" int pdac_head3x3_fwd(const PdacView* x, const float* weight, const fl
   PDAC_TRY(head_view(x, &xv, "head x"));
   if ((long long)x->N * x->H * x->W == 0) return PDAC_OK;
   const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
-  const int blocks = tiles_w * tiles_h * x->N;
+  const int n_tiles = tiles_w * tiles_h * x->N;
+  const int blocks = n_tiles;                                   // scalar version: one tile per block
+  int pblocks = 6 * num_sms();                                  // warp-MMA version: persistent blocks
+  if (pblocks > n_tiles) pblocks = n_tiles;
 #define CALL(CI, CO)                                                                                              \
   if (head_scalar())                                                                                              \
     head3x3_fwd_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h); \
   else                                                                                                            \
-    head3x3_fwd_mma_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h)
+    head3x3_fwd_mma_kernel<CI, CO><<<pblocks, 256, 0, (cudaStream_t)stream>>>(xv, weight, bias, logits, tiles_w, tiles_h, n_tiles)
   HEAD_DISPATCH(CALL);
 #undef CALL
   PDAC_LAUNCH_CHECK("head3x3_fwd");
@@ -477,10 +571,12 @@ extern "C" int pdac_head3x3_dgrad(const float* grad_logits, const float* weight,
   PDAC_TRY(head_view(dx, &dv, "head dx"));
   if ((long long)x->N * x->H * x->W == 0) return PDAC_OK;
   const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
-  const int blocks = tiles_w * tiles_h * x->N;
+  const int n_tiles = tiles_w * tiles_h * x->N;
+  int blocks = 8 * num_sms();
+  if (blocks > n_tiles) blocks = n_tiles;
 #define CALL(CI, CO)                                                                                                  \
   head3x3_dgrad_kernel<CI, CO><<<blocks, 256, 0, (cudaStream_t)stream>>>(grad_logits, weight, (bf16*)dx->ptr, dx->sN, \
-                                                                         dx->sH, dx->sW, x->N, x->H, x->W, tiles_w, tiles_h)
+                                                                         dx->sH, dx->sW, x->N, x->H, x->W, tiles_w, tiles_h, n_tiles)
   HEAD_DISPATCH(CALL);
 #undef CALL
   PDAC_LAUNCH_CHECK("head3x3_dgrad");
@@ -496,7 +592,7 @@ extern "C" int pdac_head3x3_wgrad(const PdacView* x, const float* grad_logits, i
   const int tiles_w = ceil_div(x->W, kHTW), tiles_h = ceil_div(x->H, kHTH);
   const int n_tiles = tiles_w * tiles_h * x->N;
   const int per = x->C * 9 + 1;
-  int blocks = 2 * num_sms();
+  int blocks = 4 * num_sms();
   if (blocks > n_tiles) blocks = n_tiles;
   PDAC_REQUIRE((long long)blocks * classes * per * (long long)sizeof(float) <= scratch_bytes,
                "head3x3_wgrad: scratch too small (%lld bytes needed)", (long long)blocks * classes * per * 4);
