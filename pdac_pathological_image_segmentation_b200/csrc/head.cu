@@ -53,15 +53,40 @@ __device__ __forceinline__ void load_g_tile(const float* __restrict__ g, int H, 
 
 // Register prefetch of the NEXT tile while the current one is computed from shared memory (the blocks are persistent:
 // with one small tile per block the kernels were bound by the load -> barrier -> compute latency chain at ~1 TB/s).
-__device__ __forceinline__ void decode_tile(int tile, int tiles_w, int tiles_h, int& n, int& h0, int& w0) {
-  const int tw = tile % tiles_w;
-  tile /= tiles_w;
-  const int th = tile % tiles_h;
-  n = tile / tiles_h;
-  h0 = th * kHTH;
-  w0 = tw * kHTW;
-}
-// HALO = 1: (kHTH+2) x (kHTW+2) pixels starting one pixel up-left of the tile; HALO = 0: the tile's own pixels
+// Tile index -> (image, tile row, tile column), advanced by gridDim.x tiles per step without divisions (the ncu source
+// page showed the per-tile index arithmetic — divisions, 64-bit address products, bounds tests — costing more warp
+// instructions than the MMAs: r02 profiles).
+struct TileWalk {
+  int tw, th, n, dw, dh, dn, tiles_w, tiles_h;
+  __device__ __forceinline__ TileWalk(int first, int step, int tiles_w_, int tiles_h_) : tiles_w(tiles_w_), tiles_h(tiles_h_) {
+    tw = first % tiles_w;
+    first /= tiles_w;
+    th = first % tiles_h;
+    n = first / tiles_h;
+    dw = step % tiles_w;
+    step /= tiles_w;
+    dh = step % tiles_h;
+    dn = step / tiles_h;
+  }
+  __device__ __forceinline__ void advance() {
+    tw += dw;
+    if (tw >= tiles_w) {
+      tw -= tiles_w;
+      ++th;
+    }
+    th += dh;
+    if (th >= tiles_h) {
+      th -= tiles_h;
+      ++n;
+    }
+    n += dn;
+  }
+  __device__ __forceinline__ int h0() const { return th * kHTH; }
+  __device__ __forceinline__ int w0() const { return tw * kHTW; }
+};
+
+// HALO = 1: (kHTH+2) x (kHTW+2) pixels starting one pixel up-left of the tile; HALO = 0: the tile's own pixels.
+// The position of each of this thread's chunks inside the tile is loop-invariant: computed once (init).
 template <int CIN, int HALO>
 struct XPrefetch {
   static constexpr int CG = CIN / 8;
@@ -69,25 +94,46 @@ struct XPrefetch {
   static constexpr int TOTAL = TWP * THP * CG;
   static constexpr int NL = (TOTAL + 255) / 256;
   uint4 buf[NL];
-  __device__ __forceinline__ void issue(const HeadView& x, int n, int h0, int w0) {
+  long long off[NL];  // element offset of the chunk from the tile origin pixel (h0, w0)
+  int dyx[NL];        // (dy << 16) | (dx & 0xffff), dy / dx relative to (h0, w0); dy = 0x4000 marks an unused slot
+  __device__ __forceinline__ void init(const HeadView& x) {
 #pragma unroll
     for (int j = 0; j < NL; ++j) {
       const int i = threadIdx.x + j * 256;
-      uint4 v = make_uint4(0u, 0u, 0u, 0u);
-      if (i < TOTAL) {
-        const int g = i % CG, px = i / CG;
-        const int ty = px / TWP, tx = px - ty * TWP;
-        const int h = h0 + ty - HALO, w = w0 + tx - HALO;
-        if (h >= 0 && h < x.H && w >= 0 && w < x.W) v = ld16(x.ptr + n * x.sN + h * x.sH + w * x.sW + g * 8);
-      }
-      buf[j] = v;
+      const int g = i % CG, px = i / CG;
+      const int ty = px / TWP, tx = px - ty * TWP;
+      const int dy = i < TOTAL ? ty - HALO : 0x4000, dx = tx - HALO;
+      off[j] = (long long)dy * x.sH + (long long)dx * x.sW + g * 8;
+      dyx[j] = (dy << 16) | (dx & 0xffff);
     }
+  }
+  __device__ __forceinline__ void issue(const HeadView& x, int n, int h0, int w0) {
+    const bf16* base = x.ptr + n * x.sN + h0 * x.sH + w0 * x.sW;
+    const bool interior = h0 >= HALO && w0 >= HALO && h0 + kHTH + HALO <= x.H && w0 + kHTW + HALO <= x.W;
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      const int dy = dyx[j] >> 16, dx = (int)(short)(dyx[j] & 0xffff);
+      bool ok = dy != 0x4000;
+      if (!interior) {
+        const int h = h0 + dy, w = w0 + dx;
+        ok = ok && h >= 0 && h < x.H && w >= 0 && w < x.W;
+      }
+      buf[j] = ok ? ld16(base + off[j]) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+  // 16-byte chunk g of tile pixel p lives at chunk slot g ^ swz(p): the 8 row addresses of an ldmatrix 8x8 block
+  // (8 consecutive pixels, one chunk column) then fall into 8 different 16-byte bank groups. With the plain layout
+  // (pitch 32 or 64 bytes) ncu counted an 8-way bank conflict per shared load and the L1 pipe at 96 %.
+  static __device__ __forceinline__ int swz(int p) { return CG == 2 ? (p >> 2) & 1 : (CG == 4 ? (p >> 1) & 3 : 0); }
+  static __device__ __forceinline__ uint32_t chunk_addr(uint32_t base, int p, int g) {
+    return base + (uint32_t)((p * CG + (g ^ swz(p))) * 16);
   }
   __device__ __forceinline__ void store(uint4* tile) const {
 #pragma unroll
     for (int j = 0; j < NL; ++j) {
       const int i = threadIdx.x + j * 256;
-      if (i < TOTAL) tile[i] = buf[j];
+      const int g = i % CG, px = i / CG;
+      if (i < TOTAL) tile[px * CG + (g ^ swz(px))] = buf[j];
     }
   }
 };
@@ -95,17 +141,30 @@ struct GPrefetch {  // haloed fp32 gradient tile of one class
   static constexpr int TOTAL = (kHTH + 2) * (kHTW + 2);
   static constexpr int NL = (TOTAL + 255) / 256;
   float buf[NL];
-  __device__ __forceinline__ void issue(const float* __restrict__ g, int H, int W, int h0, int w0) {
+  int off[NL], dyx[NL];
+  __device__ __forceinline__ void init(int W) {
 #pragma unroll
     for (int j = 0; j < NL; ++j) {
       const int i = threadIdx.x + j * 256;
-      float v = 0.f;
-      if (i < TOTAL) {
-        const int ty = i / (kHTW + 2), tx = i - ty * (kHTW + 2);
-        const int h = h0 + ty - 1, w = w0 + tx - 1;
-        if (h >= 0 && h < H && w >= 0 && w < W) v = __ldg(g + (long long)h * W + w);
+      const int ty = i / (kHTW + 2), tx = i - ty * (kHTW + 2);
+      const int dy = i < TOTAL ? ty - 1 : 0x4000, dx = tx - 1;
+      off[j] = dy * W + dx;
+      dyx[j] = (dy << 16) | (dx & 0xffff);
+    }
+  }
+  // g: the (image, class) plane
+  __device__ __forceinline__ void issue(const float* __restrict__ g, int H, int W, int h0, int w0) {
+    const float* base = g + (long long)h0 * W + w0;
+    const bool interior = h0 >= 1 && w0 >= 1 && h0 + kHTH + 1 <= H && w0 + kHTW + 1 <= W;
+#pragma unroll
+    for (int j = 0; j < NL; ++j) {
+      const int dy = dyx[j] >> 16, dx = (int)(short)(dyx[j] & 0xffff);
+      bool ok = dy != 0x4000;
+      if (!interior) {
+        const int h = h0 + dy, w = w0 + dx;
+        ok = ok && h >= 0 && h < H && w >= 0 && w < W;
       }
-      buf[j] = v;
+      buf[j] = ok ? __ldg(base + off[j]) : 0.f;
     }
   }
   __device__ __forceinline__ void store(float* tile) const {
@@ -165,24 +224,18 @@ __global__ void __launch_bounds__(256) head3x3_fwd_mma_kernel(HeadView x, const 
 #pragma unroll
   for (int co = 0; co < COUT; ++co) bv[co] = bias ? bias[co] : 0.f;
   const uint32_t tbase = smem_u32_h(tile);
-  constexpr int PITCH = CIN * 2;  // bytes per pixel
   const int ty = warp;            // tile row of this warp
   XPrefetch<CIN, 1> pf;
-  int n, h0, w0;
-  if ((int)blockIdx.x < n_tiles) {
-    decode_tile(blockIdx.x, tiles_w, tiles_h, n, h0, w0);
-    pf.issue(x, n, h0, w0);
-  }
+  pf.init(x);
+  TileWalk wk(blockIdx.x, gridDim.x, tiles_w, tiles_h);
+  if ((int)blockIdx.x < n_tiles) pf.issue(x, wk.n, wk.h0(), wk.w0());
   for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
-    decode_tile(tl, tiles_w, tiles_h, n, h0, w0);
+    const int n = wk.n, h0 = wk.h0(), w0 = wk.w0();
     __syncthreads();  // the previous tile has been consumed
     pf.store(tile);
     __syncthreads();
-    if (tl + (int)gridDim.x < n_tiles) {  // next tile's loads fly while this one is computed
-      int n2, h2, w2;
-      decode_tile(tl + gridDim.x, tiles_w, tiles_h, n2, h2, w2);
-      pf.issue(x, n2, h2, w2);
-    }
+    wk.advance();
+    if (tl + (int)gridDim.x < n_tiles) pf.issue(x, wk.n, wk.h0(), wk.w0());  // flies while this tile is computed
 #pragma unroll
     for (int seg = 0; seg < 2; ++seg) {
       float d[4] = {0.f, 0.f, 0.f, 0.f};
@@ -192,11 +245,11 @@ __global__ void __launch_bounds__(256) head3x3_fwd_mma_kernel(HeadView x, const 
         for (int s = 0; s < 3; ++s) {
           // ldmatrix lane address: matrix j = lane / 8: pixels (j & 1) * 8 + lane % 8, channels (j >> 1) * 8 ..
           const int px = seg * 16 + s + (lane & 7) + ((lane >> 3) & 1) * 8;
-          const uint32_t addr = tbase + (uint32_t)(((ty + r) * (kHTW + 2) + px) * PITCH + (lane >> 4) * 16);
+          const int plin = (ty + r) * (kHTW + 2) + px;
 #pragma unroll
           for (int ks = 0; ks < KS; ++ks) {
             uint32_t a[4];
-            ldsm_x4(addr + ks * 32, a);
+            ldsm_x4(XPrefetch<CIN, 1>::chunk_addr(tbase, plin, ks * 2 + (lane >> 4)), a);
             mma_bf16_16816(d, a, bw[r * 3 + s][ks][0], bw[r * 3 + s][ks][1]);
           }
         }
@@ -233,7 +286,6 @@ __global__ void __launch_bounds__(256) head3x3_wgrad_mma_kernel(HeadView x, cons
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int gid = lane >> 2, tid = lane & 3;
   const uint32_t tbase = smem_u32_h(tile);
-  constexpr int PITCH = CIN * 2;
   for (int co = 0; co < COUT; ++co) {
     float d[NT][4];
 #pragma unroll
@@ -243,22 +295,21 @@ __global__ void __launch_bounds__(256) head3x3_wgrad_mma_kernel(HeadView x, cons
     float gsum = 0.f;
     XPrefetch<CIN, 0> pfx;
     GPrefetch pfg;
-    {
-      int n, h0, w0;
-      decode_tile(blockIdx.x, tiles_w, tiles_h, n, h0, w0);  // gridDim.x <= n_tiles
-      pfx.issue(x, n, h0, w0);
-      pfg.issue(g + ((long long)n * COUT + co) * x.H * x.W, x.H, x.W, h0, w0);
-    }
+    pfx.init(x);
+    pfg.init(x.W);
+    TileWalk wk(blockIdx.x, gridDim.x, tiles_w, tiles_h);  // gridDim.x <= n_tiles
+    const long long plane = (long long)x.H * x.W;
+    pfx.issue(x, wk.n, wk.h0(), wk.w0());
+    pfg.issue(g + ((long long)wk.n * COUT + co) * plane, x.H, x.W, wk.h0(), wk.w0());
     for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
       __syncthreads();  // previous tile fully consumed
       pfx.store(tile);
       pfg.store(gt);
       __syncthreads();
+      wk.advance();
       if (tl + (int)gridDim.x < n_tiles) {  // next tile's loads fly while this one is computed
-        int n2, h2, w2;
-        decode_tile(tl + gridDim.x, tiles_w, tiles_h, n2, h2, w2);
-        pfx.issue(x, n2, h2, w2);
-        pfg.issue(g + ((long long)n2 * COUT + co) * x.H * x.W, x.H, x.W, h2, w2);
+        pfx.issue(x, wk.n, wk.h0(), wk.w0());
+        pfg.issue(g + ((long long)wk.n * COUT + co) * plane, x.H, x.W, wk.h0(), wk.w0());
       }
       const int ty = warp;
 #pragma unroll
@@ -282,7 +333,7 @@ __global__ void __launch_bounds__(256) head3x3_wgrad_mma_kernel(HeadView x, cons
 #pragma unroll
         for (int np = 0; np < NT / 2; ++np) {
           uint32_t bb[4];
-          ldsm_x4_trans(tbase + (uint32_t)((ty * kHTW + px) * PITCH + np * 32 + (lane >> 4) * 16), bb);
+          ldsm_x4_trans(XPrefetch<CIN, 0>::chunk_addr(tbase, ty * kHTW + px, np * 2 + (lane >> 4)), bb);
           mma_bf16_16816(d[np * 2], a, bb[0], bb[1]);
           mma_bf16_16816(d[np * 2 + 1], a, bb[2], bb[3]);
         }
@@ -369,30 +420,31 @@ __global__ void __launch_bounds__(256) head3x3_dgrad_kernel(const float* __restr
                                                             long long dsW, int N, int H, int W, int tiles_w,
                                                             int tiles_h, int n_tiles) {
   __shared__ float gt[COUT][(kHTH + 2) * (kHTW + 2)];
-  __shared__ float w_s[COUT][9][CIN];
+  __shared__ __align__(16) float w_s[COUT][9][CIN];
   for (int i = threadIdx.x; i < COUT * 9 * CIN; i += blockDim.x) {
     const int ci = i % CIN, t = (i / CIN) % 9, co = i / (9 * CIN);
     w_s[co][t][ci] = wgt[((long long)co * CIN + ci) * 9 + t];
   }
   GPrefetch pf[COUT];
-  int n, h0, w0;
-  if ((int)blockIdx.x < n_tiles) {
-    decode_tile(blockIdx.x, tiles_w, tiles_h, n, h0, w0);
 #pragma unroll
-    for (int co = 0; co < COUT; ++co) pf[co].issue(g + ((long long)n * COUT + co) * H * W, H, W, h0, w0);
+  for (int co = 0; co < COUT; ++co) pf[co].init(W);
+  TileWalk wk(blockIdx.x, gridDim.x, tiles_w, tiles_h);
+  const long long plane = (long long)H * W;
+  if ((int)blockIdx.x < n_tiles) {
+#pragma unroll
+    for (int co = 0; co < COUT; ++co) pf[co].issue(g + ((long long)wk.n * COUT + co) * plane, H, W, wk.h0(), wk.w0());
   }
   const int tx = threadIdx.x % kHTW, ty = threadIdx.x / kHTW;
   for (int tl = blockIdx.x; tl < n_tiles; tl += gridDim.x) {
-    decode_tile(tl, tiles_w, tiles_h, n, h0, w0);
+    const int n = wk.n, h0 = wk.h0(), w0 = wk.w0();
     __syncthreads();
 #pragma unroll
     for (int co = 0; co < COUT; ++co) pf[co].store(gt[co]);
     __syncthreads();
+    wk.advance();
     if (tl + (int)gridDim.x < n_tiles) {
-      int n2, h2, w2;
-      decode_tile(tl + gridDim.x, tiles_w, tiles_h, n2, h2, w2);
 #pragma unroll
-      for (int co = 0; co < COUT; ++co) pf[co].issue(g + ((long long)n2 * COUT + co) * H * W, H, W, h2, w2);
+      for (int co = 0; co < COUT; ++co) pf[co].issue(g + ((long long)wk.n * COUT + co) * plane, H, W, wk.h0(), wk.w0());
     }
     const int h = h0 + ty, w = w0 + tx;
     if (h >= H || w >= W) continue;
@@ -407,8 +459,15 @@ __global__ void __launch_bounds__(256) head3x3_dgrad_kernel(const float* __restr
         for (int s = 0; s < 3; ++s) {
           // the output pixel q - (r-1, s-1) sits at tile offset (ty + 1 - (r-1), tx + 1 - (s-1))
           const float gv = gt[co][(ty + 2 - r) * (kHTW + 2) + tx + 2 - s];
+          const float4* wv = reinterpret_cast<const float4*>(w_s[co][r * 3 + s]);
 #pragma unroll
-          for (int i = 0; i < CIN; ++i) acc[i] = fmaf(gv, w_s[co][r * 3 + s][i], acc[i]);
+          for (int i = 0; i < CIN / 4; ++i) {
+            const float4 q = wv[i];
+            acc[4 * i] = fmaf(gv, q.x, acc[4 * i]);
+            acc[4 * i + 1] = fmaf(gv, q.y, acc[4 * i + 1]);
+            acc[4 * i + 2] = fmaf(gv, q.z, acc[4 * i + 2]);
+            acc[4 * i + 3] = fmaf(gv, q.w, acc[4 * i + 3]);
+          }
         }
     bf16* o = dx + n * dsN + h * dsH + w * dsW;
 #pragma unroll
