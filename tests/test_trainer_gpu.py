@@ -133,6 +133,47 @@ def test_validate_is_the_eval_mode_dice():
     assert abs(score.item() - want.item()) <= 1e-6
 
 
+def test_loss_curve_tracks_the_fp32_oracle():
+    """Loss-curve parity: 60 Adam steps of the reference loop (train_worker.py:68-80) on one fixed batch,
+    the fp32 torch oracle of the smp Unet with torch.optim.Adam on one side and the captured-graph TrainStep on the other,
+    from the same weights. Individual steps diverge (bf16 activations, a chaotic random-init network: see
+    test_gradients_match_fp32_when_well_conditioned), so the test compares what a user of the loop sees: the first loss,
+    that both runs learn, the level of the curve half way and at the end, and the eval-mode Dice afterwards."""
+    from oracle import resunet_oracle as R
+    from oracle import smp_oracle as S
+    from oracle import util_oracle as U
+    from pdac_pathological_image_segmentation_b200 import smp as P
+    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
+    torch.manual_seed(17)
+    ref = S.build("unet_smp", classes=1, dropout=0.0)
+    ours = P.Unet(encoder_name="resnet18", encoder_weights=None, in_channels=3, classes=1, activation=None)
+    ours.load_state_dict(ref.state_dict(), strict=True)
+    ref, ours = ref.to(DEV).train(), ours.to(DEV).train()
+    img, mask = R.synthetic_batch(8, 64, seed=11)
+    img = torch.where(mask[..., None].bool(), img // 2 + 128, img // 2).to(torch.uint8)   # a learnable signal: bright = tumour
+    x = R.normalize(img).to(DEV)
+    img_d, mask_d = img.to(DEV), mask.to(DEV)
+    opt = torch.optim.Adam(ref.parameters(), lr=1e-3)
+    ts = TrainStep(ours, lr=1e-3, graph=True)
+    la, lb = [], []
+    for _ in range(60):
+        _, loss, _ = U.train_step(ref, opt, x, mask_d)
+        la.append(loss.item())
+        loss_o, _ = ts.step(img_d, mask_d)
+        lb.append(loss_o.item())
+    mean = lambda v: sum(v) / len(v)
+    assert abs(la[0] - lb[0]) <= 5e-3, (la[0], lb[0])
+    assert mean(la[-10:]) <= 0.6 * la[0] and mean(lb[-10:]) <= 0.6 * lb[0], (la[0], la[-10:], lb[0], lb[-10:])
+    assert abs(mean(la[20:30]) - mean(lb[20:30])) <= 0.08, (la[20:30], lb[20:30])
+    assert abs(mean(la[-10:]) - mean(lb[-10:])) <= 0.05, (la[-10:], lb[-10:])
+    ref.eval()
+    with torch.no_grad():
+        want = U.dice_score(U.sigmoid_mask(torch.squeeze(ref(x))), mask_d.float()).item()
+    got = ts.validate(img_d, mask_d).item()
+    assert abs(want - got) <= 0.1, (want, got)
+    ts.release_graph()
+
+
 # ------------------------------------------------------------------------------------------------ 2 GPUs (NCCL)
 def _free_port():
     s = socket.socket()
