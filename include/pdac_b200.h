@@ -216,6 +216,16 @@ int pdac_bn_bwd_apply(const PdacView* dy, const PdacView* y, const PdacView* x, 
  * [PDAC_STAT_ROWS][C] for the reproducible fixed-order sum, or NULL (fp32 atomics). */
 int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias, float* scratch,
                        void* stream);
+/* Allocation-free variant of pdac_relu_bwd_bias (reproducible mode). NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, serving loops,
+ * harnesses that forbid it). Same arithmetic and result as pdac_relu_bwd_bias with caller scratch; the
+ * [PDAC_STAT_ROWS][C] partial-row table lives in a static device array inside the library instead (1.2 MB per GPU that
+ * loads the library, held until exit), and the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limit: dy->C <= PDAC_NOALLOC_MAX_C, otherwise PDAC_E_INVALID with a message naming the limit. dy and dbias are
+ * required (dbias[c] += sum, caller zeroes); y and dz may be NULL. Every call on a GPU shares the one array: calls that
+ * overlap on the GPU (different streams, no ordering between them) race; calls ordered on one stream do not. */
+#define PDAC_NOALLOC_MAX_C 512
+int pdac_relu_bwd_bias_noalloc(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias, void* stream);
 
 /* ---- pooling / resampling (pool.cu) ------------------------------------------------------------------------- */
 /* idx: uint8 [N][Ho][Wo][C] arg-max tap (r*3+s), saved for backward (may be NULL in inference). */

@@ -75,6 +75,7 @@ SIGNATURES = {
     "pdac_bn_bwd_reduce": [_VP, _VP, _VP, _p, _p, _p, _p],
     "pdac_bn_bwd_apply": [_VP, _VP, _VP, _p, _p, _p, _p, _d, _i, _VP, _VP, _p, _p, _p],
     "pdac_relu_bwd_bias": [_VP, _VP, _VP, _p, _p, _p],
+    "pdac_relu_bwd_bias_noalloc": [_VP, _VP, _VP, _p, _p],
     "pdac_maxpool3x3s2_fwd": [_VP, _VP, _p, _p],
     "pdac_maxpool3x3s2_bwd": [_VP, _p, _VP, _VP, _p],
     "pdac_upsample_nearest2x_fwd": [_VP, _VP, _p],

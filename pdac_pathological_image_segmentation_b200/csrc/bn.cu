@@ -535,3 +535,51 @@ extern "C" int pdac_relu_bwd_bias(const PdacView* dy, const PdacView* y, const P
   if (det) PDAC_TRY(rows_sum(scratch, g.blocks, fd.C, dbias, 1, (cudaStream_t)stream));
   return PDAC_OK;
 }
+
+// ---- allocation-free variant (no counterpart in the reference) -----------
+// pdac_relu_bwd_bias with its [PDAC_STAT_ROWS][C] partial-row table in a file-scope device array instead of caller
+// scratch, for callers that cannot cudaMalloc (graph capture, serving loops). Limit: C <= PDAC_NOALLOC_MAX_C (512), i.e.
+// 592 * 512 * 4 = 1.2 MB held by every GPU that loads the library, until exit. All calls share the array: calls that
+// overlap on one GPU (different streams) race. Nothing has to start at zero — every launched block overwrites its whole
+// row and rows_sum reads exactly the rows of this launch — so the previous call's contents never leak into the next.
+static __device__ __align__(256) float g_noalloc_rows[PDAC_STAT_ROWS * PDAC_NOALLOC_MAX_C];
+
+// The array's name is only a host-side stand-in here: the device address comes from cudaGetSymbolAddress, looked up once
+// per device with that device current.
+static int noalloc_rows_ptr(float** out) {
+  static float* ptr[64] = {};
+  int dev = 0;
+  PDAC_CUDA(cudaGetDevice(&dev));
+  PDAC_REQUIRE(dev >= 0 && dev < 64, "relu_bwd_bias_noalloc: device ordinal %d out of range", dev);
+  float* p = __atomic_load_n(&ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    PDAC_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_rows));
+    PDAC_REQUIRE(p != nullptr, "relu_bwd_bias_noalloc: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&ptr[dev], p, __ATOMIC_RELEASE);  // racing threads look up the same address
+  }
+  *out = p;
+  return PDAC_OK;
+}
+
+extern "C" int pdac_relu_bwd_bias_noalloc(const PdacView* dy, const PdacView* y, const PdacView* dz, float* dbias,
+                                          void* stream) {
+  PDAC_REQUIRE(dy && dbias, "relu_bwd_bias_noalloc: dy and dbias are required");
+  Flat fd, fy = {nullptr, 0, 0, 0}, fdz = {nullptr, 0, 0, 0};
+  PDAC_TRY(flatten(dy, &fd, "dy"));
+  if (y) PDAC_TRY(flatten(y, &fy, "y"));
+  if (dz) PDAC_TRY(flatten(dz, &fdz, "dz"));
+  PDAC_REQUIRE((!y || (fy.npix == fd.npix && fy.C == fd.C)) && (!dz || (fdz.npix == fd.npix && fdz.C == fd.C)),
+               "relu_bwd_bias_noalloc: y / dz must have dy's shape");
+  PDAC_REQUIRE(fd.C <= PDAC_NOALLOC_MAX_C,
+               "relu_bwd_bias_noalloc: C = %d exceeds the static scratch limit of %d channels (use pdac_relu_bwd_bias "
+               "with caller scratch)",
+               fd.C, PDAC_NOALLOC_MAX_C);
+  float* rows = nullptr;
+  PDAC_TRY(noalloc_rows_ptr(&rows));
+  static const int resident = resident_blocks(relu_bwd_bias_kernel);
+  const EwGrid g = ew_grid(fd.npix, fd.C, resident > PDAC_STAT_ROWS ? PDAC_STAT_ROWS : resident);
+  relu_bwd_bias_kernel<<<g.blocks, 256, 0, (cudaStream_t)stream>>>(fd, fy, fdz, dbias, rows, g.cg, g.ppb);
+  PDAC_LAUNCH_CHECK("relu_bwd_bias_noalloc");
+  PDAC_TRY(rows_sum(rows, g.blocks, fd.C, dbias, 1, (cudaStream_t)stream));
+  return PDAC_OK;
+}
