@@ -126,6 +126,15 @@ int pdac_conv2d_fwd_affine(const PdacConv* cv, int n_src, const PdacView* src, c
  * stride 2 the four output parity classes are separate launches; classes no tap reaches get addend or zero. */
 int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const void* w_packed_t, const PdacView* addend,
                       const PdacView* dx, void* stream);
+/* The same data gradient when the conv's first dx_pooled->C input channels were F.interpolate(x, scale_factor=2,
+ * mode="nearest") (smp UnetDecoder / DecoderBlock.forward: interpolate -> torch.cat([x, skip]) -> conv1): those channels'
+ * gradient is returned at half resolution, summed over each 2x2 block (the interpolation's backward), in dx_pooled
+ * (N, H/2, W/2, C0); the remaining channels (the skip connection's gradient) go to dx_rest (N, H, W, C1; NULL when there
+ * is no skip). Stride 1, spatial-size-preserving convolutions only. Bit-identical to pdac_conv2d_dgrad followed by
+ * pdac_upsample_nearest2x_bwd. *handled = 0 (and PDAC_OK): the geometry is not eligible for the fused kernel, nothing was
+ * launched; run the two calls instead. */
+int pdac_conv2d_dgrad_pool2(const PdacConv* cv, const PdacView* dy, const void* w_packed_t, const PdacView* dx_pooled,
+                            const PdacView* dx_rest, int* handled, void* stream);
 /* dw += sum_pixels dy[p,cout] * cat(src)[p*stride + off, cin]. dw_layout 0: fp32 [R*S][Cout][Ctot];
  * dw_layout 1: the nn.Conv2d state_dict layout [cout_valid][Ctot][R][S] (gradients land where autograd wants them). */
 int pdac_conv2d_wgrad(const PdacConv* cv, int n_src, const PdacView* src, const PdacView* dy, float* dw,

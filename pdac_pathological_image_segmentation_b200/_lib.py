@@ -56,6 +56,7 @@ SIGNATURES = {
     "pdac_conv2d_fwd_affine": [C.POINTER(PdacConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
     "pdac_tapconv_fwd_affine": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
     "pdac_conv2d_dgrad": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, _p],
+    "pdac_conv2d_dgrad_pool2": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, C.POINTER(C.c_int), _p],
     "pdac_conv2d_wgrad": [C.POINTER(PdacConv), _i, _VP, _VP, _p, _i, _p, _ll, _p],
     "pdac_convt2x2_fwd": [_VP, _p, _i, _p, _i, _VP, _p],
     "pdac_convt2x2_dgrad": [_VP, _p, _i, _VP, _p],

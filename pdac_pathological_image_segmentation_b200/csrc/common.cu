@@ -24,6 +24,9 @@ int cuda_fail(cudaError_t e, const char* what) {
 static thread_local const float* g_epi_scale = nullptr;
 void set_epi_scale(const float* scale) { g_epi_scale = scale; }
 const float* epi_scale() { return g_epi_scale; }
+static thread_local const PdacView* g_epi_pool = nullptr;
+void set_epi_pool(const PdacView* pooled) { g_epi_pool = pooled; }
+const PdacView* epi_pool() { return g_epi_pool; }
 
 static thread_local int g_last_kernel = 0;
 void note_kernel(int id) { g_last_kernel = id; }

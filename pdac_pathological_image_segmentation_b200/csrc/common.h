@@ -50,6 +50,10 @@ void note_kernel(int id);
 // eval-mode BatchNorm folded into the GEMM epilogue as y = act(acc * scale + shift + addend)).
 void set_epi_scale(const float* scale);
 const float* epi_scale();
+// Half-resolution destination of the next tap convolution's leading output channels (set by pdac_conv2d_dgrad_pool2:
+// the 2x2 sum of a nearest-neighbour x2 upsampling's gradient, formed in the halo kernel's epilogue).
+void set_epi_pool(const PdacView* pooled);
+const PdacView* epi_pool();
 
 // Deterministic cross-block reductions (no floating-point atomics): out[c] (+)= sum over rows 0..n_rows-1 of
 // rows[r][c], added in a fixed order (bn.cu).

@@ -52,6 +52,13 @@ struct HaloParams {
   float* stats;
   int relu;
   int* err;
+  // POOL mode (data gradient in front of a nearest-neighbour x2 upsampling): output channels [0, pool_c) are summed
+  // over 2x2 pixel blocks in the epilogue and stored to the half-resolution tensor pout; the remaining channels go
+  // to `out` (whose pointer the host has moved back by pool_c channels). PW is a power of two (pw_log2) that divides
+  // 128 with an even quotient, so every accumulator holds whole pixel-row pairs.
+  int pool_c, pw_log2;
+  bf16* pout;
+  long long psN, psH, psW;
 };
 
 // -DPDAC_HALO_PROF (make prof): per-CTA cycle counters of where each role waits, read back with pdac_halo_prof_read
@@ -118,9 +125,10 @@ __device__ __forceinline__ void halo_issue(uint32_t tacc, uint32_t acc_step, uin
   }
 }
 
-// AFF: folded-BatchNorm inference epilogue (per-channel scale and shift); a separate instantiation because the epilogue
-// sits at the register limit and the training kernels must not pay for it
-template <int NACC, int KS, int DUAL, int AFF>
+// MODE 1 (AFF): folded-BatchNorm inference epilogue (per-channel scale and shift); MODE 2 (POOL): 2x2 sum-pooled stores
+// (see HaloParams::pool_c). Separate instantiations because the epilogue sits at the register limit and the training
+// kernels must not pay for either.
+template <int NACC, int KS, int DUAL, int MODE>
 __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ? 2 : 1)
     conv_halo_kernel(const __grid_constant__ HaloMaps maps, const __grid_constant__ HaloParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -132,6 +140,9 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_slot;
   __shared__ long long s_rowoff[4][128];
+  __shared__ long long s_pooloff[MODE == 2 ? (DUAL ? 2 : 4) : 1][32];
+  constexpr int AFF = MODE == 1;
+  constexpr int POOL = MODE == 2;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -450,6 +461,15 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
           const bf16* arow = p.addend + abase + (long long)th * p.asH + (long long)tw * p.asW + n0;
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // previous staging fully consumed
           s_rowoff[wg][m] = valid ? ooff : -1;
+          if (POOL && m < 32) {  // the 32 pooled pixels of this accumulator: (128 / PW) / 2 row pairs x PW / 2 column pairs
+            const int hw = p.pw_log2 - 1;
+            const int pr = m >> hw, pc = m & ((1 << hw) - 1);
+            const int th2 = j * (128 >> p.pw_log2) + 2 * pr, tw2 = 2 * pc;
+            const bool ok = (tw2 < p.TW) && (th2 < p.TH) && (w0 + tw2 < p.W) && (h0 + th2 < p.H);
+            s_pooloff[wg][m] = ok ? (long long)img * p.psN + (long long)((h0 + th2) >> 1) * p.psH +
+                                        (long long)((w0 >> 1) + pc) * p.psW
+                                  : -1;
+          }
           const uint32_t tacc =
               tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
 #pragma unroll
@@ -539,6 +559,29 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                 uint32_t saddr = stg + (uint32_t)((e >> cpr_log2) * spitch + ch * 16);
                 const uint32_t sstep = (uint32_t)(step * spitch);
                 int row = e >> cpr_log2;
+                if (POOL && n0 + c0 + ch * 8 < p.pool_c) {
+                  // this 8-channel column is pooled: rows < 32 index pooled pixels; (a + b) + (c + d) in fp32 of the
+                  // bf16-rounded values, the order of up2_bwd_kernel (pool.cu) -> bit-identical to the unfused pair
+                  const int hw = p.pw_log2 - 1;
+                  const uint32_t colb = stg + (uint32_t)(ch * 16);
+                  for (; row < 32; row += step) {
+                    const int pr = row >> hw, pc = row & ((1 << hw) - 1);
+                    const uint32_t a00 = colb + (uint32_t)((((2 * pr) << p.pw_log2) + 2 * pc) * spitch);
+                    const uint4 va = lds128(a00), vb = lds128(a00 + (uint32_t)spitch);
+                    const uint4 vc = lds128(a00 + (uint32_t)(spitch << p.pw_log2));
+                    const uint4 vd = lds128(a00 + (uint32_t)(spitch << p.pw_log2) + (uint32_t)spitch);
+                    const uint32_t ua[4] = {va.x, va.y, va.z, va.w}, ub[4] = {vb.x, vb.y, vb.z, vb.w};
+                    const uint32_t uc[4] = {vc.x, vc.y, vc.z, vc.w}, ud[4] = {vd.x, vd.y, vd.z, vd.w};
+                    uint32_t r[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                      r[i] = h_pack((h_bf16lo(ua[i]) + h_bf16lo(ub[i])) + (h_bf16lo(uc[i]) + h_bf16lo(ud[i])),
+                                    (h_bf16hi(ua[i]) + h_bf16hi(ub[i])) + (h_bf16hi(uc[i]) + h_bf16hi(ud[i])));
+                    const long long off = s_pooloff[wg][row];
+                    if (off >= 0 && ch_ok && !DBG(0))
+                      *reinterpret_cast<uint4*>(p.pout + n0 + c0 + ch * 8 + off) = make_uint4(r[0], r[1], r[2], r[3]);
+                  }
+                } else {
 #pragma unroll 2
                 for (int it = 0; it < (1 << cpr_log2); ++it, row += step, saddr += sstep) {
                   const long long off = s_rowoff[wg][row];
@@ -555,6 +598,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                       acc[pass][8 + 2 * i + 1] = fmaf(x1, x1, acc[pass][8 + 2 * i + 1]);
                     }
                   }
+                }
                 }
               } else {
                 // channel count not a multiple of 8 (1-class logit heads): scalar stores, no statistics
@@ -651,7 +695,7 @@ struct HaloPlan {
 // Picks the tile. Cost model (cycles per image, per SM share): MMA issue = tiles * nacc * taps * K16-steps * max(N/2, 10)
 // against bytes moved (halo in + tile out) at ~40 B/cycle/SM; the larger of the two plus a per-tile overhead.
 static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int ck, int eh, int ew, int has_addend,
-                      int dual, HaloPlan* best) {
+                      int dual, int pool, HaloPlan* best) {
   const int pitch = ck * 2;
   // dual: two CTAs per SM, each with half of the shared memory (228 KB per SM, 1 KB reserved + ~6.5 KB static per CTA)
   // and half of the tensor memory
@@ -671,20 +715,30 @@ static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int
     f_sa = (e = getenv("PDAC_HALO_SA")) ? atoi(e) : 0;
     f_wg = (e = getenv("PDAC_HALO_WG")) ? atoi(e) : 0;
   }
-  const int tws[5] = {16, 32, 64, 128, W};
+  // pool: the halo pitch is a power of two that divides 128 into an even number of pixel rows per accumulator (every
+  // 2x2 block then lies inside one accumulator's staging tile); the tile is nacc * 128 / PW rows high
+  const int tws[5] = {pool ? 16 - ew : 16, pool ? 32 - ew : 32, pool ? 64 - ew : 64, pool ? 0 : 128, pool ? 0 : W};
   for (int ti = 0; ti < 5; ++ti) {
     int TW = tws[ti];
-    if (TW > W) TW = W;
+    if (TW <= 0) continue;
+    if (TW > W && !pool) TW = W;
     if (TW + ew > 256) continue;
-    if (f_tw && TW != f_tw) continue;
+    if (f_tw && TW != f_tw && !pool) continue;
     const int PW = TW + ew;
     for (int nacc = 1; nacc <= max_nacc; ++nacc) {
-      int TH = (128 * nacc - TW) / PW + 1;
-      if (128 * nacc < TW) continue;
-      if (TH > H) TH = H;
-      if (TH + eh > 256) TH = 256 - eh;
-      const int nacc_eff = ((TH - 1) * PW + TW + 127) / 128;
-      if (nacc_eff != nacc) continue;  // the same tile is reachable with fewer accumulators
+      int TH;
+      if (pool) {
+        TH = nacc * (128 / PW);
+        if (nacc > 1 && TH - 128 / PW >= H) continue;  // fewer accumulators already cover the image height
+        if (TH + eh > 256) continue;
+      } else {
+        TH = (128 * nacc - TW) / PW + 1;
+        if (128 * nacc < TW) continue;
+        if (TH > H) TH = H;
+        if (TH + eh > 256) TH = 256 - eh;
+        const int nacc_eff = ((TH - 1) * PW + TW + 127) / 128;
+        if (nacc_eff != nacc) continue;  // the same tile is reachable with fewer accumulators
+      }
       if (f_nacc && nacc != f_nacc) continue;
       const int R = TH + eh;
       const int a_buf = ((nacc * 128 + eh * PW + ew) * pitch + 1023) & ~1023;
@@ -786,10 +840,20 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     const char* e = getenv("PDAC_HALO_DUAL");
     dual_ok = (e && e[0] == '0') ? 0 : 1;
   }
+  // POOL mode (pdac_conv2d_dgrad_pool2): the leading pool->C output channels are stored 2x2-summed at half resolution
+  const PdacView* pool = epi_pool();
+  if (pool) {
+    if ((cout & 7) || (pool->C & 7) || pool->C <= 0 || pool->C > cout || (out->H & 1) || (out->W & 1) || (ew & 1) ||
+        pool->N != out->N || 2 * pool->H != out->H || 2 * pool->W != out->W || addend || stats || bias || epi_scale() ||
+        tc->relu)
+      return PDAC_OK;
+  }
   int dual = dual_ok && ck <= 32 && block_n <= 32;
-  if (dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1, &pl))
+  if (dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1,
+                         pool != nullptr, &pl))
     dual = 0;
-  if (!dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 0, &pl))
+  if (!dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 0,
+                          pool != nullptr, &pl))
     return PDAC_OK;
 
   {
@@ -878,6 +942,18 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   p.stats = stats;
   p.relu = tc->relu;
   p.err = device_err_flag();
+  if (pool) {
+    PDAC_REQUIRE((128 % p.PW) == 0 && ((128 / p.PW) & 1) == 0 && p.TH == p.nacc * (128 / p.PW),
+                 "internal: pooled halo plan (PW=%d TH=%d nacc=%d)", p.PW, p.TH, p.nacc);
+    PDAC_REQUIRE(((uintptr_t)pool->ptr & 15) == 0 && pool->sW % 8 == 0 && pool->sH % 8 == 0 && pool->sN % 8 == 0,
+                 "pooled gradient view must be 16-byte aligned");
+    p.pool_c = pool->C;
+    p.pw_log2 = ilog2(p.PW);
+    p.pout = (bf16*)pool->ptr;
+    p.psN = pool->sN;
+    p.psH = pool->sH;
+    p.psW = pool->sW;
+  }
   for (int s = 0; s < tc->n_cat; ++s) PDAC_TRY(encode_view_map(&maps.a[s], &views[s], ck, p.PW, p.R, 1));
   if (tc->n_cat == 1) maps.a[1] = maps.a[0];
   {
@@ -899,11 +975,12 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     conv_halo_kernel<n, 1, 0, aff>, conv_halo_kernel<n, 2, 0, aff>, conv_halo_kernel<n, 4, 0, aff>,             \
         conv_halo_kernel<n, 1, 1, aff>, conv_halo_kernel<n, 2, 1, aff>                                          \
   }
-  static const HaloKernel table[2][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
-                                            {HALO_ROW(1, 1), HALO_ROW(2, 1), HALO_ROW(3, 1), HALO_ROW(4, 1)}};
+  static const HaloKernel table[3][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
+                                            {HALO_ROW(1, 1), HALO_ROW(2, 1), HALO_ROW(3, 1), HALO_ROW(4, 1)},
+                                            {HALO_ROW(1, 2), HALO_ROW(2, 2), HALO_ROW(3, 2), HALO_ROW(4, 2)}};
 #undef HALO_ROW
-  static bool attr_set[2][4][5] = {};
-  const int ka = p.scale ? 1 : 0;
+  static bool attr_set[3][4][5] = {};
+  const int ka = pool ? 2 : (p.scale ? 1 : 0);
   const int ki = pl.nacc - 1, kj = (ck == 16 ? 0 : (ck == 32 ? 1 : 2)) + (dual ? 3 : 0);
   HaloKernel kern = table[ka][ki][kj];
   if (!attr_set[ka][ki][kj]) {

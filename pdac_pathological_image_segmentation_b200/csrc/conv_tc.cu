@@ -1056,6 +1056,60 @@ extern "C" int pdac_conv2d_dgrad(const PdacConv* cv, const PdacView* dy, const v
   return PDAC_OK;
 }
 
+// Data gradient of a stride-1 "same" convolution whose first dx_pooled->C input channels were a nearest-neighbour x2
+// upsampling (smp UnetDecoder: F.interpolate(x, scale_factor=2) -> cat([x, skip]) -> conv): those channels' gradient is
+// wanted at half resolution, summed over each 2x2 block, and is formed in the halo kernel's epilogue from the staged
+// bf16 tile instead of being written at full resolution and read back by pdac_upsample_nearest2x_bwd (same values bit
+// for bit: the same bf16 roundings and the same summation order). *handled = 0: geometry not eligible, nothing was
+// launched and the caller runs the two-kernel form.
+extern "C" int pdac_conv2d_dgrad_pool2(const PdacConv* cv, const PdacView* dy, const void* w_packed_t,
+                                       const PdacView* dx_pooled, const PdacView* dx_rest, int* handled, void* stream) {
+  PDAC_REQUIRE(cv && dy && w_packed_t && dx_pooled && handled, "null argument");
+  *handled = 0;
+  if (cv->stride != 1) return PDAC_OK;
+  PDAC_TRY(check_dev_ptr(dx_pooled->ptr, "dx_pooled"));
+  if (dx_rest) PDAC_TRY(check_dev_ptr(dx_rest->ptr, "dx_rest"));
+  PDAC_REQUIRE(dx_pooled->N == dy->N && 2 * dx_pooled->H == dy->H && 2 * dx_pooled->W == dy->W,
+               "dgrad_pool2: dx_pooled must be (N, H/2, W/2, C) of dy's (N, H, W)");
+  PDAC_REQUIRE(!dx_rest || (dx_rest->N == dy->N && dx_rest->H == dy->H && dx_rest->W == dy->W),
+               "dgrad_pool2: dx_rest must have dy's N, H, W");
+  PDAC_REQUIRE(2 * cv->pad == (cv->R - 1) * cv->dil && 2 * cv->pad == (cv->S - 1) * cv->dil,
+               "dgrad_pool2: the convolution must keep the spatial size");
+  if ((dx_pooled->C & 7) || (dx_rest && (dx_rest->C & 7))) return PDAC_OK;
+  PdacTapConv tc;
+  memset(&tc, 0, sizeof(tc));
+  tc.n_cat = 1;
+  tc.wrows = cv->wrows;
+  tc.relu = 0;
+  tc.n_taps = cv->R * cv->S;
+  for (int r = 0; r < cv->R; ++r)
+    for (int s = 0; s < cv->S; ++s) {
+      PdacTap& t = tc.taps[r * cv->S + s];
+      t.src = 0;
+      t.dh = cv->pad - r * cv->dil;
+      t.dw = cv->pad - s * cv->dil;
+    }
+  // the full-resolution output the kernel indexes: channels [0, pooled C) are never stored through it
+  PdacView out;
+  out.N = dy->N;
+  out.H = dy->H;
+  out.W = dy->W;
+  out.C = dx_pooled->C + (dx_rest ? dx_rest->C : 0);
+  if (dx_rest) {
+    out.ptr = (bf16*)dx_rest->ptr - dx_pooled->C;
+    out.sN = dx_rest->sN;
+    out.sH = dx_rest->sH;
+    out.sW = dx_rest->sW;
+  } else {
+    out.ptr = dx_pooled->ptr;
+    out.sN = out.sH = out.sW = 0;
+  }
+  set_epi_pool(dx_pooled);
+  const int rc = conv_halo_try(&tc, 1, dy, w_packed_t, nullptr, nullptr, &out, nullptr, stream, handled);
+  set_epi_pool(nullptr);
+  return rc;
+}
+
 extern "C" int pdac_convt2x2_fwd(const PdacView* x, const void* w_packed, int wrows, const float* bias, int relu,
                                  const PdacView* out, void* stream) {
   PDAC_REQUIRE(x && w_packed && out, "null argument");

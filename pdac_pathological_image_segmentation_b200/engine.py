@@ -153,6 +153,10 @@ class Tape:
         self.grads = {}
         self.nograd = set()
         self.host_rng = False
+        # nearest x2 upsamplings: ids of their outputs (forward), and of those whose pending gradient is already the
+        # half-resolution 2x2 sum (written by the consuming conv's fused data-gradient kernel)
+        self.up2_src = set()
+        self.pooled = set()
 
     def record(self, fn, params=()):
         """fn: the layer's backward step; params: the parameters whose gradient slots that step completes (the
@@ -173,11 +177,34 @@ class Tape:
         old = self.grads.get(k)
         if old is None:
             self.grads[k] = g
+        elif k in self.pooled:        # the pending gradient is already pooled: pool this one into it
+            ops.upsample_nearest2x_bwd(g, old, out=old)
         else:
             ops.add(old, g, out=old)
 
+    def put_pooled(self, t, g):
+        """g: gradient of the x2-upsampled tensor t, already summed over the 2x2 replicas (half resolution)."""
+        if id(t) in self.nograd:
+            return
+        k = id(t)
+        old = self.grads.get(k)
+        if old is None:
+            self.grads[k] = g
+        elif k in self.pooled:
+            ops.add(old, g, out=old)
+        else:                         # a full-resolution gradient is pending: pool it into g
+            self.grads[k] = ops.upsample_nearest2x_bwd(old, g, out=g)
+        self.pooled.add(k)
+
     def pop(self, t):
         return self.grads.pop(id(t), None)
+
+    def pop_up2(self, t):
+        """-> (pending gradient of the x2-upsampled tensor t or None, whether it is already pooled)."""
+        k = id(t)
+        pooled = k in self.pooled
+        self.pooled.discard(k)
+        return self.grads.pop(k, None), pooled
 
     def backward(self, on_params_done=None):
         for fn, params in reversed(self.steps):
@@ -186,6 +213,7 @@ class Tape:
                 on_params_done(params)
         self.steps = []
         self.grads = {}
+        self.pooled = set()
 
 
 # ------------------------------------------------------------------------------------------------ layer functions
@@ -198,6 +226,18 @@ def _conv_backward(tape, m: Conv2d, srcs, dy, wp_t):
     if not any(need):
         return
     h, w = srcs[0].shape[1], srcs[0].shape[2]
+    s0 = srcs[0]
+    if (id(s0) in tape.up2_src and all(need) and len(srcs) <= 2 and m.stride == 1 and id(s0) not in tape.grads
+            and 2 * m.padding == (k - 1) * m.dilation):
+        # the first source is a nearest x2 upsampling: its gradient leaves the data-gradient kernel already summed over
+        # the 2x2 replicas, at half resolution (no full-resolution round trip through upsample_nearest2x_bwd)
+        c_rest = srcs[1].shape[3] if len(srcs) == 2 else 0
+        res = ops.conv2d_dgrad_pool2(dy, wp_t, s0.shape[3], c_rest, k, k, m.padding, m.dilation, c_real=m.cout)
+        if res is not None:
+            tape.put_pooled(s0, res[0])
+            if c_rest:
+                tape.put(srcs[1], res[1])
+            return
     if len(srcs) == 1:
         old = tape.pop(srcs[0])
         dx = ops.conv2d_dgrad(dy, wp_t, srcs[0].shape[3], (h, w), k, k, m.stride, m.padding, m.dilation, addend=old,
@@ -276,11 +316,14 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         y = ops.scale_shift_act(x, st.ss, residual, relu=relu, out=None if keep_x else x)
     training = tape.training
 
+    if up2 and tape.enabled:
+        tape.up2_src.add(id(y))
+
     def bwd():
-        dy = tape.pop(y)
+        dy, pooled = tape.pop_up2(y) if up2 else (tape.pop(y), False)
         if dy is None:
             return
-        if up2:                # gradient of the fused upsampling: sum of the four replicas
+        if up2 and not pooled:  # gradient of the fused upsampling: sum of the four replicas
             dy = ops.upsample_nearest2x_bwd(dy)
         sums = ops.new_bwd_sums(m.cout, dev)
         # without a residual the ReLU mask is recomputed from x and the forward's scale / shift: y is not re-read
@@ -358,12 +401,17 @@ def convt2x2(tape: Tape, m: ConvTranspose2d, x):
 
 def nearest2x(tape: Tape, x):
     y = ops.upsample_nearest2x_fwd(x)
+    if tape.enabled:
+        tape.up2_src.add(id(y))
 
     def bwd():
-        dy = tape.pop(y)
+        dy, pooled = tape.pop_up2(y)
         if dy is not None:
-            old = tape.pop(x)
-            tape.put(x, ops.upsample_nearest2x_bwd(dy, old, out=old))
+            if pooled:
+                tape.put(x, dy)
+            else:
+                old = tape.pop(x)
+                tape.put(x, ops.upsample_nearest2x_bwd(dy, old, out=old))
     tape.record(bwd)
     return y
 

@@ -160,6 +160,31 @@ def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None,
     return out
 
 
+fuse_up2_bwd = os.environ.get("PDAC_FUSE_UP2_BWD", "1") != "0"
+
+
+def conv2d_dgrad_pool2(dy, wpt, c_pool, c_rest, R, S, pad=0, dil=1, c_real=None):
+    """Data gradient of a stride-1 same-size conv whose first c_pool input channels were a nearest x2 upsampling:
+    -> (dx_pooled (N, H/2, W/2, c_pool) = the 2x2-summed gradient, dx_rest (N, H, W, c_rest) or None), or None when the
+    fused kernel does not take the geometry (the caller then runs conv2d_dgrad + upsample_nearest2x_bwd)."""
+    n, h, w = dy.shape[0], dy.shape[1], dy.shape[2]
+    if not fuse_up2_bwd or (h | w) & 1 or c_pool % 8 or c_rest % 8:
+        return None
+    wrows = wpt.shape[0] // (R * S)
+    assert wpt.dtype == BF16 and wpt.is_contiguous() and wpt.shape[1] == dy.shape[3]
+    cv = _conv_struct(R, S, 1, pad, dil, False, wrows)
+    pooled = empty_act(n, h // 2, w // 2, c_pool, dy.device)
+    rest = empty_act(n, h, w, c_rest, dy.device) if c_rest else None
+    handled = C.c_int(0)
+    call("pdac_conv2d_dgrad_pool2", C.byref(cv), _vp(dy), _ptr(wpt), _vp(pooled), _vp(rest), C.byref(handled), _stream(),
+         flops=2 * n * h * w * (c_real or dy.shape[3]) * (c_pool + c_rest) * R * S,
+         nbytes=_act_bytes(dy, pooled, rest),
+         tag=f"dgrad+pool {R}x{S}s1d{dil} {n}x{h}x{w} {dy.shape[3]}->{c_pool}/4+{c_rest}")
+    if not handled.value:
+        return None
+    return pooled, rest
+
+
 def conv2d_wgrad(srcs, dy, R, S, stride=1, pad=0, dil=1, out=None, oihw=False, cout_valid=0):
     """dw fp32 [R*S, dy.C, sum(src.C)] (or, with oihw=True, the state_dict layout [cout, sum(src.C), R, S]),
     accumulated into `out` if given (which must be pre-zeroed). cout_valid: real channels of a padded dy."""

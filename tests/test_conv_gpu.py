@@ -229,3 +229,56 @@ def test_stem_as_4x4_s2d():
     ops.check_device_flag()
     err = (dw - ref_dw).abs().max().item()
     assert err <= 1e-3 * ref_dw.abs().max().item() + 1e-4, f"stem wgrad err {err}"
+
+
+# ------------------------------------------------------------------ data gradient with the nearest x2 backward fused
+POOL_CASES = [
+    # N, H, W, cout (dy channels), c_pool, c_rest, dil
+    (2, 64, 64, 16, 32, 0, 1),        # last Unet block: no skip, two CTAs per SM
+    (2, 32, 32, 32, 64, 64, 1),       # 64 up + 64 skip in one 128-column tile
+    (2, 16, 16, 64, 128, 64, 1),      # pool boundary at a tile boundary (128 | 64)
+    (1, 24, 40, 128, 256, 128, 1),    # three N tiles, sizes that are no multiple of the tile
+    (2, 8, 8, 256, 512, 256, 1),      # streamed weights
+    (1, 36, 28, 32, 16, 16, 1),       # pool boundary inside a 32-column pass
+    (1, 20, 12, 16, 24, 8, 1),        # 8-channel granularity
+    (1, 32, 32, 32, 32, 32, 2),       # dilated 3x3
+    (1, 6, 130, 16, 16, 0, 1),        # wider than every tile, lower than one accumulator
+]
+
+
+@pytest.mark.parametrize("case", POOL_CASES, ids=[str(c) for c in POOL_CASES])
+def test_conv_dgrad_pool2_is_bit_identical_to_the_two_kernel_form(case):
+    """pdac_conv2d_dgrad_pool2 == pdac_conv2d_dgrad + pdac_upsample_nearest2x_bwd on the upsampled channels (smp
+    UnetDecoder: interpolate(nearest, x2) -> cat -> conv), bit for bit; and both match torch's fp32 gradient."""
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W, cout, c_pool, c_rest, dil = case
+    cin = c_pool + c_rest
+    w = _rnd(cout, cin, 3, 3, scale=0.05, seed=13)
+    dy = _rnd(N, cout, H, W, seed=14)
+    _, wpt = ops.pack_conv_weight(w.float().contiguous(), want_fwd=False, stride=1, pad=dil, cout_pad=cout)
+    dyp = _nhwc(dy)
+    full = ops.conv2d_dgrad(dyp, wpt, cin, (H, W), 3, 3, 1, dil, dil)
+    want_pool = ops.upsample_nearest2x_bwd(full[..., :c_pool])
+    res = ops.conv2d_dgrad_pool2(dyp, wpt, c_pool, c_rest, 3, 3, dil, dil)
+    ops.check_device_flag()
+    assert res is not None, "the fused kernel refused an eligible geometry"
+    pooled, rest = res
+    assert pooled.shape == (N, H // 2, W // 2, c_pool)
+    assert torch.equal(pooled.view(torch.int16), want_pool.view(torch.int16)), \
+        (pooled.float() - want_pool.float()).abs().max().item()
+    if c_rest:
+        assert rest.shape == (N, H, W, c_rest)
+        assert torch.equal(rest.view(torch.int16), full[..., c_pool:].contiguous().view(torch.int16))
+    else:
+        assert rest is None
+    ref = torch.nn.grad.conv2d_input((N, cin, H, W), w.float(), dy.float(), stride=1, padding=dil, dilation=dil)
+    ref_pool = torch.nn.functional.avg_pool2d(ref[:, :c_pool], 2) * 4
+    _close(pooled.permute(0, 3, 1, 2), ref_pool, "pooled dgrad")
+
+
+def test_conv_dgrad_pool2_declines_what_it_cannot_take():
+    from pdac_pathological_image_segmentation_b200 import ops
+    w = _rnd(16, 16, 3, 3, scale=0.05, seed=1)
+    _, wpt = ops.pack_conv_weight(w.float().contiguous(), want_fwd=False, stride=1, pad=1, cout_pad=16)
+    assert ops.conv2d_dgrad_pool2(_nhwc(_rnd(1, 16, 7, 8, seed=2)), wpt, 16, 0, 3, 3, 1, 1) is None      # odd height
+    assert ops.conv2d_dgrad_pool2(_nhwc(_rnd(1, 16, 8, 8, seed=2)), wpt, 12, 4, 3, 3, 1, 1) is None      # 8-channel groups

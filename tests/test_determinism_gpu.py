@@ -89,6 +89,34 @@ def test_identical_train_steps_are_bit_identical(size, batch):
         assert torch.equal(a, b)
 
 
+def test_fused_upsampling_backward_leaves_every_gradient_bit_identical():
+    """The decoder's nearest x2 backward formed inside the consuming conv's data-gradient kernel
+    (pdac_conv2d_dgrad_pool2) against the two-kernel form (PDAC_FUSE_UP2_BWD=0): same bf16 roundings, same summation
+    order -> the same loss and the same gradient arena bit for bit; and the fused form really ran."""
+    from pdac_pathological_image_segmentation_b200 import _lib, ops
+    from pdac_pathological_image_segmentation_b200.trainer import TrainStep
+    img, mask = _batch(2, 128, 9)
+    runs = []
+    for fuse in (True, False):
+        old = ops.fuse_up2_bwd
+        ops.fuse_up2_bwd = fuse
+        try:
+            ts = TrainStep(_unet(), lr=1e-3)
+            _lib.trace, _lib.trace_all = [], True
+            loss, _ = ts.step(img, mask)
+            names = [t[0] if t[0].startswith("pdac_") else t[5] for t in _lib.trace]
+        finally:
+            _lib.trace, _lib.trace_all = None, False
+            ops.fuse_up2_bwd = old
+        tags = [t for t in names if t.startswith("dgrad+pool")]
+        n_up2 = sum(1 for t in names if t == "pdac_upsample_nearest2x_bwd")
+        runs.append((loss.item(), ts.arena.flat.clone(), len(tags), n_up2))
+    assert runs[0][2] == 5 and runs[0][3] == 0, runs[0][2:]       # five decoder blocks, no separate pooling pass left
+    assert runs[1][2] == 0 and runs[1][3] == 5, runs[1][2:]
+    assert runs[0][0] == runs[1][0]
+    assert runs[0][1].abs().max().item() > 0 and torch.equal(runs[0][1], runs[1][1])
+
+
 def test_trainstep_gradients_equal_autograd_path_bitwise():
     """The fused harness (uint8 patches -> ... -> Adam) and the drop-in module under torch autograd + torch.optim.Adam
     launch the same kernels on the same prepared input: same loss, the same gradients bit for bit (train mode, batch
