@@ -97,6 +97,11 @@ __device__ __forceinline__ float h_bf16hi(uint32_t u) { return __uint_as_float(u
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+__device__ __forceinline__ void stg256(void* ptr, const uint32_t (&r)[8]) {  // one 32-byte sector per thread
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+               "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
@@ -141,8 +146,10 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
   __shared__ uint32_t tmem_base_slot;
   __shared__ long long s_rowoff[4][128];
   __shared__ long long s_pooloff[MODE == 2 ? (DUAL ? 2 : 4) : 1][32];
-  constexpr int AFF = MODE == 1;
+  constexpr int AFF = MODE == 1 || MODE == 4;
   constexpr int POOL = MODE == 2;
+  constexpr int DIRECT = MODE >= 3;  // register -> global epilogue of the N <= 32 layers (see the epilogue role)
+  constexpr int DSTATS = MODE == 5;  // ... of a plain N = 16 convolution in front of a BatchNorm: store + partial sums
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -436,7 +443,167 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
 #endif
     const int nacc_mod = p.nacc % p.n_wg;
     int wg_off = 0;  // (lt * nacc) % n_wg, carried incrementally
-    if (sp0 < sp_step)
+    if (DIRECT) {
+      // N = 16 / 32 (two CTAs per SM): thread m owns MMA row m, i.e. one pixel's 32 or 64 contiguous output bytes, and a
+      // warp's 32 rows are 32 consecutive pixels of an image row -> every 32-byte store below writes a whole sector and
+      // a warp writes one contiguous 1-2 KB run: no staging tile, no warpgroup barriers, a third of the instructions
+      // of the staged epilogue (which ncu / the knock-outs showed to be what bounds the 16-channel layers: 2000 cycles
+      // per accumulator and warpgroup). Three instantiations, so that none spills (the first version kept 32 statistics
+      // registers next to the generic epilogue and spilled 16 values into the loop: ncu showed 75 % of the epilogue's
+      // stall samples on the consumers of those local loads): MODE 3 generic without statistics (data gradients,
+      // bias / addend / ReLU layers), MODE 4 folded BatchNorm (inference), MODE 5 the plain N = 16 convolution in front
+      // of a training BatchNorm: lane pairs swap half of their packed row so that each lane adds 8 channels of 2 rows
+      // (16 statistics registers instead of 32).
+      float ssum[DSTATS ? 8 : 1], ssq[DSTATS ? 8 : 1];
+#pragma unroll
+      for (int i = 0; i < (DSTATS ? 8 : 1); ++i) ssum[i] = ssq[i] = 0.f;
+      const bool two = !DSTATS && p.block_n > 16;
+      if (sp0 < sp_step)
+        for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt, walk_next(wk)) {
+          const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
+          const int g = lt & 1;
+          PROF_WAIT(w_tf, mbar_wait(&tmem_full_bar[g], (lt >> 1) & 1, p.err));
+          tc_fence_after();
+          const long long obase = (long long)img * p.osN + (long long)h0 * p.osH + (long long)w0 * p.osW;
+          const long long abase = (long long)img * p.asN + (long long)h0 * p.asH + (long long)w0 * p.asW;
+          int j = wg - wg_off;
+          if (j < 0) j += p.n_wg;
+          wg_off += nacc_mod;
+          if (wg_off >= p.n_wg) wg_off -= p.n_wg;
+          if (j >= p.nacc || DBG(1)) {
+            tc_fence_before();
+            mbar_arrive(&tmem_empty_bar[g]);
+            if (DBG(1)) continue;
+          }
+          for (; j < p.nacc; j += p.n_wg) {
+            const int o = j * 128 + m;
+            const int th = (int)(((uint32_t)o * p.inv_pw) >> 20), tw = o - th * p.PW;
+            const bool valid = (tw < p.TW) && (th < p.TH) && (w0 + tw < p.W) && (h0 + th < p.H);
+            bf16* orow = p.out + obase + (long long)th * p.osH + (long long)tw * p.osW + n0;
+            const bf16* arow = p.addend + abase + (long long)th * p.asH + (long long)tw * p.asW + n0;
+            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
+            const bool last = j + p.n_wg >= p.nacc;
+            if (DSTATS) {
+              uint32_t v[16];
+              tmem_ld16(tacc, v);
+              tmem_ld_wait();
+              if (last) {
+                tc_fence_before();
+                mbar_arrive(&tmem_empty_bar[g]);
+              }
+              uint32_t r[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                r[i] = valid ? h_pack(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])) : 0u;
+              if (valid && !DBG(0)) stg256(orow, r);
+              if (!DBG(3)) {
+                // even lanes keep channels 0..7 of both rows of the pair, odd lanes channels 8..15
+                const bool odd = lane & 1;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const uint32_t give = odd ? r[i] : r[4 + i], keep = odd ? r[4 + i] : r[i];
+                  const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
+                  const float a0 = h_bf16lo(keep), a1 = h_bf16hi(keep), b0 = h_bf16lo(got), b1 = h_bf16hi(got);
+                  ssum[2 * i] += a0;
+                  ssum[2 * i] += b0;
+                  ssum[2 * i + 1] += a1;
+                  ssum[2 * i + 1] += b1;
+                  ssq[2 * i] = fmaf(a0, a0, ssq[2 * i]);
+                  ssq[2 * i] = fmaf(b0, b0, ssq[2 * i]);
+                  ssq[2 * i + 1] = fmaf(a1, a1, ssq[2 * i + 1]);
+                  ssq[2 * i + 1] = fmaf(b1, b1, ssq[2 * i + 1]);
+                }
+              }
+              continue;
+            }
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              if (hf && !two) break;
+              const int cb = hf * 16;
+              uint32_t v[16];
+              tmem_ld16(tacc + (uint32_t)cb, v);
+              tmem_ld_wait();
+              if (last && (hf || !two)) {  // last TMEM read of this warpgroup in this tile
+                tc_fence_before();
+                mbar_arrive(&tmem_empty_bar[g]);
+              }
+              float f[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+              if (AFF && p.bias && cb + 16 <= nch) {
+                const float4* sp4 = reinterpret_cast<const float4*>(p.scale + n0 + cb);
+                const float4* bp4 = reinterpret_cast<const float4*>(p.bias + n0 + cb);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float4 sv = __ldg(sp4 + i), bv = __ldg(bp4 + i);
+                  f[4 * i] = fmaf(f[4 * i], sv.x, bv.x);
+                  f[4 * i + 1] = fmaf(f[4 * i + 1], sv.y, bv.y);
+                  f[4 * i + 2] = fmaf(f[4 * i + 2], sv.z, bv.z);
+                  f[4 * i + 3] = fmaf(f[4 * i + 3], sv.w, bv.w);
+                }
+              } else {
+                if (p.scale) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    if (cb + i < nch) f[i] *= __ldg(p.scale + n0 + cb + i);
+                }
+                if (p.bias) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    if (cb + i < nch) f[i] += __ldg(p.bias + n0 + cb + i);
+                }
+              }
+              if (p.addend && valid) {
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                  if (cb + hh * 8 < nch) {
+                    const uint4 u = __ldg(reinterpret_cast<const uint4*>(arow + cb + hh * 8));
+                    const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                      f[hh * 8 + 2 * i] += h_bf16lo(uu[i]);
+                      f[hh * 8 + 2 * i + 1] += h_bf16hi(uu[i]);
+                    }
+                  }
+                }
+              }
+              if (p.relu) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+              }
+              uint32_t r[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) r[i] = h_pack(f[2 * i], f[2 * i + 1]);
+              if (valid && !DBG(0)) {
+                if (cb + 16 <= nch)
+                  stg256(orow + cb, r);
+                else if (cb + 8 <= nch)
+                  *reinterpret_cast<uint4*>(orow + cb) = make_uint4(r[0], r[1], r[2], r[3]);
+              }
+            }
+          }
+        }
+      if (DSTATS && p.stats) {
+        // fixed order: lanes of equal parity by xor-shuffles, then the warp's slot (added over the warps after the CTA
+        // barrier); lane 0 ends with channels 0..7, lane 1 with channels 8..15
+        float* wslot = reinterpret_cast<float*>(smem_stg + (size_t)wg * 128 * spitch) + q * 256;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float a = ssum[i], b = ssq[i];
+#pragma unroll
+          for (int o = 16; o >= 2; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+          }
+          const int chn = (lane & 1) * 8 + i;
+          if (lane < 2 && chn < nch) {
+            wslot[chn] = a;
+            wslot[128 + chn] = b;
+          }
+        }
+      }
+    }
+    if (!DIRECT && sp0 < sp_step)
       for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt, walk_next(wk)) {
         const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
         const int g = lt & 1;
@@ -624,7 +791,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
     // cudnn.deterministic, train_main.py:40): lanes sharing a channel column -> one lane per column -> this warp's
     // slot in the (now idle) staging area -> after the final CTA barrier one thread per channel adds the warps'
     // slots in index order and stores the CTA's row of the [rows][2][Cout] partial table (no atomics anywhere).
-    if (p.stats && vec) {
+    if (!DIRECT && p.stats && vec) {
       asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // the last tile's staging has been consumed
       float* wslot = reinterpret_cast<float*>(smem_stg + (size_t)wg * 128 * spitch) + q * 256;
 #pragma unroll
@@ -975,12 +1142,29 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     conv_halo_kernel<n, 1, 0, aff>, conv_halo_kernel<n, 2, 0, aff>, conv_halo_kernel<n, 4, 0, aff>,             \
         conv_halo_kernel<n, 1, 1, aff>, conv_halo_kernel<n, 2, 1, aff>                                          \
   }
-  static const HaloKernel table[3][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
+  // the direct epilogue (modes 3, 4) exists for the two-CTAs-per-SM variants only
+#define HALO_ROW_D(n, mode) \
+  { nullptr, nullptr, nullptr, conv_halo_kernel<n, 1, 1, mode>, conv_halo_kernel<n, 2, 1, mode> }
+  static const HaloKernel table[6][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
                                             {HALO_ROW(1, 1), HALO_ROW(2, 1), HALO_ROW(3, 1), HALO_ROW(4, 1)},
-                                            {HALO_ROW(1, 2), HALO_ROW(2, 2), HALO_ROW(3, 2), HALO_ROW(4, 2)}};
+                                            {HALO_ROW(1, 2), HALO_ROW(2, 2), HALO_ROW(3, 2), HALO_ROW(4, 2)},
+                                            {HALO_ROW_D(1, 3), HALO_ROW_D(2, 3), HALO_ROW_D(3, 3), HALO_ROW_D(4, 3)},
+                                            {HALO_ROW_D(1, 4), HALO_ROW_D(2, 4), HALO_ROW_D(3, 4), HALO_ROW_D(4, 4)},
+                                            {HALO_ROW_D(1, 5), HALO_ROW_D(2, 5), HALO_ROW_D(3, 5), HALO_ROW_D(4, 5)}};
 #undef HALO_ROW
-  static bool attr_set[3][4][5] = {};
-  const int ka = pool ? 2 : (p.scale ? 1 : 0);
+#undef HALO_ROW_D
+  static bool attr_set[6][4][5] = {};
+  // Direct register -> global epilogue: N <= 32 with two CTAs per SM, 32-byte aligned output pixels; the per-thread
+  // BatchNorm sums fit the register budget for N = 16 only. PDAC_HALO_DIRECT=0 keeps the staged epilogue.
+  static int direct_ok = -1;
+  if (direct_ok < 0) {
+    const char* e = getenv("PDAC_HALO_DIRECT");
+    direct_ok = (e && e[0] == '0') ? 0 : 1;
+  }
+  const bool plain = !bias && !addend && !p.scale && !tc->relu;
+  const bool direct = direct_ok && dual && !pool && (cout & 7) == 0 && (!stats || (cout == 16 && plain)) &&
+                      ((uintptr_t)out->ptr & 31) == 0 && out->sW % 16 == 0 && out->sH % 16 == 0 && out->sN % 16 == 0;
+  const int ka = pool ? 2 : (direct ? (stats ? 5 : (p.scale ? 4 : 3)) : (p.scale ? 1 : 0));
   const int ki = pl.nacc - 1, kj = (ck == 16 ? 0 : (ck == 32 ? 1 : 2)) + (dual ? 3 : 0);
   HaloKernel kern = table[ka][ki][kj];
   if (!attr_set[ka][ki][kj]) {
