@@ -444,7 +444,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
     const int nacc_mod = p.nacc % p.n_wg;
     int wg_off = 0;  // (lt * nacc) % n_wg, carried incrementally
     if (DIRECT) {
-      // N = 16 / 32 (two CTAs per SM): thread m owns MMA row m, i.e. one pixel's 32 or 64 contiguous output bytes, and a
+      // Thread m owns MMA row m, i.e. one pixel's contiguous output bytes (32 for N = 16 ... 256 for N = 128), and a
       // warp's 32 rows are 32 consecutive pixels of an image row -> every 32-byte store below writes a whole sector and
       // a warp writes one contiguous 1-2 KB run: no staging tile, no warpgroup barriers, a third of the instructions
       // of the staged epilogue (which ncu / the knock-outs showed to be what bounds the 16-channel layers: 2000 cycles
@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
       float ssum[DSTATS ? 8 : 1], ssq[DSTATS ? 8 : 1];
 #pragma unroll
       for (int i = 0; i < (DSTATS ? 8 : 1); ++i) ssum[i] = ssq[i] = 0.f;
-      const bool two = !DSTATS && p.block_n > 16;
+      const int nchunk = DSTATS ? 1 : (nch + 15) >> 4;  // 16-column chunks of an accumulator that hold real channels
       if (sp0 < sp_step)
         for (int sp = sp0; sp < p.tiles_sp; sp += sp_step, ++lt, walk_next(wk)) {
           const int img = wk.img, w0 = wk.tw * p.TW, h0 = wk.th * p.TH;
@@ -516,14 +516,13 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
               }
               continue;
             }
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf) {
-              if (hf && !two) break;
-              const int cb = hf * 16;
+#pragma unroll 1
+            for (int ck16 = 0; ck16 < nchunk; ++ck16) {
+              const int cb = ck16 * 16;
               uint32_t v[16];
               tmem_ld16(tacc + (uint32_t)cb, v);
               tmem_ld_wait();
-              if (last && (hf || !two)) {  // last TMEM read of this warpgroup in this tile
+              if (last && ck16 == nchunk - 1) {  // last TMEM read of this warpgroup in this tile
                 tc_fence_before();
                 mbar_arrive(&tmem_empty_bar[g]);
               }
@@ -862,7 +861,7 @@ struct HaloPlan {
 // Picks the tile. Cost model (cycles per image, per SM share): MMA issue = tiles * nacc * taps * K16-steps * max(N/2, 10)
 // against bytes moved (halo in + tile out) at ~40 B/cycle/SM; the larger of the two plus a per-tile overhead.
 static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int ck, int eh, int ew, int has_addend,
-                      int dual, int pool, HaloPlan* best) {
+                      int dual, int pool, int no_staging, HaloPlan* best) {
   const int pitch = ck * 2;
   // dual: two CTAs per SM, each with half of the shared memory (228 KB per SM, 1 KB reserved + ~6.5 KB static per CTA)
   // and half of the tensor memory
@@ -871,7 +870,8 @@ static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int
   const int max_nacc = tmem_half / N < 4 ? tmem_half / N : 4;
   if (max_nacc < 1) return false;
   const long long w_bytes = (long long)n_taps * n_chunks * N * pitch;
-  const int stg_wg = 128 * ((N < 64 ? N : 64) * 2 + 16);  // staging bytes per epilogue warpgroup
+  // staging bytes per epilogue warpgroup (none with the direct register -> global epilogue)
+  const int stg_wg = no_staging ? 0 : 128 * ((N < 64 ? N : 64) * 2 + 16);
   best->cost = 1e30;
   // tuning overrides (debug): PDAC_HALO_TW / PDAC_HALO_NACC / PDAC_HALO_SA / PDAC_HALO_WG
   static int f_tw = -1, f_nacc = -1, f_sa = -1, f_wg = -1;
@@ -1015,13 +1015,26 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
         tc->relu)
       return PDAC_OK;
   }
+  // Direct register -> global epilogue (no staging tile): 32-byte aligned output pixels; without BatchNorm sums for any
+  // N, with them for the plain N = 16 convolution of the two-CTAs-per-SM kernels (the per-thread sums fit the register
+  // budget there only). PDAC_HALO_DIRECT=0 keeps the staged epilogue.
+  static int direct_ok = -1;
+  if (direct_ok < 0) {
+    const char* e = getenv("PDAC_HALO_DIRECT");
+    direct_ok = (e && e[0] == '0') ? 0 : 1;
+  }
+  const bool aligned32 = ((uintptr_t)out->ptr & 31) == 0 && out->sW % 16 == 0 && out->sH % 16 == 0 && out->sN % 16 == 0;
+  const bool plain = !bias && !addend && !epi_scale() && !tc->relu;
+  const bool direct_ns = direct_ok && !pool && (cout & 7) == 0 && aligned32 && !stats;
+  const bool direct_st = direct_ok && !pool && cout == 16 && plain && aligned32 && stats;
   int dual = dual_ok && ck <= 32 && block_n <= 32;
   if (dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1,
-                         pool != nullptr, &pl))
+                         pool != nullptr, direct_ns, &pl))
     dual = 0;
   if (!dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 0,
-                          pool != nullptr, &pl))
+                          pool != nullptr, direct_ns, &pl))
     return PDAC_OK;
+  const bool direct = direct_ns || (direct_st && dual);
 
   {
     static int dbg = -1;
@@ -1030,9 +1043,9 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
       dbg = (e && e[0] == '1') ? 1 : 0;
     }
     if (dbg)
-      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d dual=%d cost=%.0f\n",
+      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d dual=%d direct=%d cost=%.0f\n",
               out->N, out->H, out->W, n_chunks, ck, block_n, tc->n_taps, pl.TW, pl.TH, pl.nacc, pl.sa, pl.sb,
-              pl.b_resident, pl.n_wg, dual, pl.cost);
+              pl.b_resident, pl.n_wg, dual, (int)direct, pl.cost);
   }
   HaloMaps maps;
   HaloParams p;
@@ -1130,7 +1143,8 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     PDAC_TRY(encode_tiled_bf16(&maps.w, w_packed, 2, dims, strides, box, p.pitch));
   }
   const size_t b_bytes = (size_t)(p.b_resident ? p.n_taps * p.n_chunks : p.sb * p.tap_S) * p.b_sub;
-  const size_t smem = (size_t)p.sa * p.a_buf + b_bytes + (size_t)p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16) + 1024;
+  const size_t smem = (size_t)p.sa * p.a_buf + b_bytes +
+                      (direct_ns ? 0 : (size_t)p.n_wg * 128 * ((block_n < 64 ? block_n : 64) * 2 + 16)) + 1024;
   PDAC_REQUIRE(smem <= (size_t)(dual ? 105 : 221) * 1024, "internal: halo conv shared memory plan (%zu bytes)", smem);
   int per_n = (dual ? 2 : 1) * num_sms() / p.tiles_c;
   if (per_n < 1) per_n = 1;
@@ -1142,28 +1156,18 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     conv_halo_kernel<n, 1, 0, aff>, conv_halo_kernel<n, 2, 0, aff>, conv_halo_kernel<n, 4, 0, aff>,             \
         conv_halo_kernel<n, 1, 1, aff>, conv_halo_kernel<n, 2, 1, aff>                                          \
   }
-  // the direct epilogue (modes 3, 4) exists for the two-CTAs-per-SM variants only
+  // the statistics variant of the direct epilogue (mode 5) exists for the two-CTAs-per-SM kernels only
 #define HALO_ROW_D(n, mode) \
   { nullptr, nullptr, nullptr, conv_halo_kernel<n, 1, 1, mode>, conv_halo_kernel<n, 2, 1, mode> }
   static const HaloKernel table[6][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
                                             {HALO_ROW(1, 1), HALO_ROW(2, 1), HALO_ROW(3, 1), HALO_ROW(4, 1)},
                                             {HALO_ROW(1, 2), HALO_ROW(2, 2), HALO_ROW(3, 2), HALO_ROW(4, 2)},
-                                            {HALO_ROW_D(1, 3), HALO_ROW_D(2, 3), HALO_ROW_D(3, 3), HALO_ROW_D(4, 3)},
-                                            {HALO_ROW_D(1, 4), HALO_ROW_D(2, 4), HALO_ROW_D(3, 4), HALO_ROW_D(4, 4)},
+                                            {HALO_ROW(1, 3), HALO_ROW(2, 3), HALO_ROW(3, 3), HALO_ROW(4, 3)},
+                                            {HALO_ROW(1, 4), HALO_ROW(2, 4), HALO_ROW(3, 4), HALO_ROW(4, 4)},
                                             {HALO_ROW_D(1, 5), HALO_ROW_D(2, 5), HALO_ROW_D(3, 5), HALO_ROW_D(4, 5)}};
 #undef HALO_ROW
 #undef HALO_ROW_D
   static bool attr_set[6][4][5] = {};
-  // Direct register -> global epilogue: N <= 32 with two CTAs per SM, 32-byte aligned output pixels; the per-thread
-  // BatchNorm sums fit the register budget for N = 16 only. PDAC_HALO_DIRECT=0 keeps the staged epilogue.
-  static int direct_ok = -1;
-  if (direct_ok < 0) {
-    const char* e = getenv("PDAC_HALO_DIRECT");
-    direct_ok = (e && e[0] == '0') ? 0 : 1;
-  }
-  const bool plain = !bias && !addend && !p.scale && !tc->relu;
-  const bool direct = direct_ok && dual && !pool && (cout & 7) == 0 && (!stats || (cout == 16 && plain)) &&
-                      ((uintptr_t)out->ptr & 31) == 0 && out->sW % 16 == 0 && out->sH % 16 == 0 && out->sN % 16 == 0;
   const int ka = pool ? 2 : (direct ? (stats ? 5 : (p.scale ? 4 : 3)) : (p.scale ? 1 : 0));
   const int ki = pl.nacc - 1, kj = (ck == 16 ? 0 : (ck == 32 ? 1 : 2)) + (dual ? 3 : 0);
   HaloKernel kern = table[ka][ki][kj];
