@@ -57,6 +57,13 @@ struct HaloParams {
   // to `out` (whose pointer the host has moved back by pool_c channels). PW is a power of two (pw_log2) that divides
   // 128 with an even quotient, so every accumulator holds whole pixel-row pairs.
   int pool_c, pw_log2;
+  // Tap stacking (direct epilogue, N = 16, one K chunk): the three taps of a kernel row share ONE MMA whose B operand is
+  // their three weight tiles (contiguous in shared memory: N' = 3 N) — the 4 KB pixel tile, whose shared-memory read is
+  // what an MMA costs at small N (32 of its 32 + N/4 cycles), is read once per kernel row instead of once per tap.
+  // Accumulator column block s then holds the products of tap (r, s) for the pixel stack_d[s] raster positions to the
+  // left, and the epilogue adds the three blocks across lanes (PW is 16 or 32: an image row never leaves its warp).
+  int stack, acc_cols, issue_S, b_tap_mul;
+  int stack_d[3];
   bf16* pout;
   long long psN, psH, psW;
 };
@@ -313,12 +320,12 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
       const uint32_t b_lo0 = (smem_u32(smem_b) >> 4) | lbo_lo;
       const uint32_t a_lo0 = (smem_u32(smem_a) >> 4) | lbo_lo;
       const uint32_t a_buf16 = (uint32_t)p.a_buf >> 4, b_sub16 = (uint32_t)p.b_sub >> 4;
-      const uint32_t acc_step = (uint32_t)p.block_n;
+      const uint32_t acc_step = (uint32_t)p.acc_cols;
       const uint32_t j_step = 128u * pix16;
       const uint32_t tap0 = (uint32_t)p.tap_base * pix16;
       const uint32_t step_r = (uint32_t)(p.tap_step_r * (int)pix16), step_s = (uint32_t)(p.tap_step_s * (int)pix16);
-      const int TR = p.tap_R, TS = p.tap_S, n_chunks = p.n_chunks, sa = p.sa, sb = p.sb;
-      const uint32_t b_tap16 = (uint32_t)n_chunks * b_sub16;
+      const int TR = p.tap_R, TS = p.issue_S, n_chunks = p.n_chunks, sa = p.sa, sb = p.sb;
+      const uint32_t b_tap16 = (uint32_t)(p.b_tap_mul * n_chunks) * b_sub16;
       int stage = 0, bstage = 0, lt = 0;
       uint32_t phase = 0, bphase = 0;
       PROF_DECL(w_te);
@@ -481,12 +488,28 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
             const bool valid = (tw < p.TW) && (th < p.TH) && (w0 + tw < p.W) && (h0 + th < p.H);
             bf16* orow = p.out + obase + (long long)th * p.osH + (long long)tw * p.osW + n0;
             const bf16* arow = p.addend + abase + (long long)th * p.asH + (long long)tw * p.asW + n0;
-            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
+            const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.acc_cols);
             const bool last = j + p.n_wg >= p.nacc;
             if (DSTATS) {
               uint32_t v[16];
               tmem_ld16(tacc, v);
               tmem_ld_wait();
+              if (p.stack) {  // add the other two taps of the kernel row, each from the lane stack_d[s] to the right
+                if (p.stack_d[0]) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) v[i] = __shfl_down_sync(0xffffffffu, v[i], p.stack_d[0]);
+                }
+#pragma unroll
+                for (int sl = 1; sl < 3; ++sl) {
+                  uint32_t u[16];
+                  tmem_ld16(tacc + (uint32_t)(sl * 16), u);
+                  tmem_ld_wait();
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    v[i] = __float_as_uint(__uint_as_float(v[i]) +
+                                           __uint_as_float(__shfl_down_sync(0xffffffffu, u[i], p.stack_d[sl])));
+                }
+              }
               if (last) {
                 tc_fence_before();
                 mbar_arrive(&tmem_empty_bar[g]);
@@ -522,6 +545,22 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
               uint32_t v[16];
               tmem_ld16(tacc + (uint32_t)cb, v);
               tmem_ld_wait();
+              if (p.stack) {  // N = 16: one chunk; see DSTATS above
+                if (p.stack_d[0]) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) v[i] = __shfl_down_sync(0xffffffffu, v[i], p.stack_d[0]);
+                }
+#pragma unroll
+                for (int sl = 1; sl < 3; ++sl) {
+                  uint32_t u[16];
+                  tmem_ld16(tacc + (uint32_t)(sl * 16), u);
+                  tmem_ld_wait();
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    v[i] = __float_as_uint(__uint_as_float(v[i]) +
+                                           __uint_as_float(__shfl_down_sync(0xffffffffu, u[i], p.stack_d[sl])));
+                }
+              }
               if (last && ck16 == nchunk - 1) {  // last TMEM read of this warpgroup in this tile
                 tc_fence_before();
                 mbar_arrive(&tmem_empty_bar[g]);
@@ -861,13 +900,14 @@ struct HaloPlan {
 // Picks the tile. Cost model (cycles per image, per SM share): MMA issue = tiles * nacc * taps * K16-steps * max(N/2, 10)
 // against bytes moved (halo in + tile out) at ~40 B/cycle/SM; the larger of the two plus a per-tile overhead.
 static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int ck, int eh, int ew, int has_addend,
-                      int dual, int pool, int no_staging, HaloPlan* best) {
+                      int dual, int pool, int no_staging, int stack, HaloPlan* best) {
   const int pitch = ck * 2;
   // dual: two CTAs per SM, each with half of the shared memory (228 KB per SM, 1 KB reserved + ~6.5 KB static per CTA)
   // and half of the tensor memory
   const long long kSmemBudget = dual ? 104 * 1024 : pdac::kSmemBudget;
   const int tmem_half = dual ? 128 : 256;
-  const int max_nacc = tmem_half / N < 4 ? tmem_half / N : 4;
+  const int ncols = stack ? 3 * N : N;  // accumulator columns (tap stacking: the three taps of a kernel row side by side)
+  const int max_nacc = tmem_half / ncols < 4 ? tmem_half / ncols : 4;
   if (max_nacc < 1) return false;
   const long long w_bytes = (long long)n_taps * n_chunks * N * pitch;
   // staging bytes per epilogue warpgroup (none with the direct register -> global epilogue)
@@ -884,13 +924,15 @@ static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int
   }
   // pool: the halo pitch is a power of two that divides 128 into an even number of pixel rows per accumulator (every
   // 2x2 block then lies inside one accumulator's staging tile); the tile is nacc * 128 / PW rows high
-  const int tws[5] = {pool ? 16 - ew : 16, pool ? 32 - ew : 32, pool ? 64 - ew : 64, pool ? 0 : 128, pool ? 0 : W};
+  // stack: an image row of the halo raster must not leave its warp (PW = 16 or 32)
+  const int tws[5] = {pool || stack ? 16 - ew : 16, pool || stack ? 32 - ew : 32, stack ? 0 : (pool ? 64 - ew : 64),
+                      pool || stack ? 0 : 128, pool || stack ? 0 : W};
   for (int ti = 0; ti < 5; ++ti) {
     int TW = tws[ti];
     if (TW <= 0) continue;
-    if (TW > W && !pool) TW = W;
+    if (TW > W && !pool && !stack) TW = W;
     if (TW + ew > 256) continue;
-    if (f_tw && TW != f_tw && !pool) continue;
+    if (f_tw && TW != f_tw && !pool && !stack) continue;
     const int PW = TW + ew;
     for (int nacc = 1; nacc <= max_nacc; ++nacc) {
       int TH;
@@ -933,7 +975,9 @@ static bool plan_halo(int H, int W, int N, int n_taps, int ts, int n_chunks, int
         if (f_sa && sa > f_sa) sa = f_sa;
         if (sa < 2) continue;
         const int tiles = ceil_div(W, TW) * ceil_div(H, TH);
-        const double mma_cyc = (double)tiles * nacc * n_taps * n_chunks * (ck / 16) * (32 + N / 4 > 40 ? 32 + N / 4 : 40);  // measured: ~32 + N/4 cycles per M=128 K=16 MMA
+        // measured: ~32 + N/4 cycles per M=128 K=16 MMA (the shared-memory reads of its operands)
+        const double mma_cyc = stack ? (double)tiles * nacc * (n_taps / 3) * n_chunks * (ck / 16) * (32 + 3 * N / 4)
+                                     : (double)tiles * nacc * n_taps * n_chunks * (ck / 16) * (32 + N / 4 > 40 ? 32 + N / 4 : 40);
         double bytes = (double)tiles * R * PW * n_chunks * pitch + (double)H * W * N * 2 * (has_addend ? 2 : 1);
         if (!res) bytes += (double)tiles * w_bytes;
         const double mem_cyc = bytes / 40.0;
@@ -1029,12 +1073,32 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   const bool direct_st = direct_ok && !pool && cout == 16 && plain && aligned32 && stats;
   int dual = dual_ok && ck <= 32 && block_n <= 32;
   if (dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1,
-                         pool != nullptr, direct_ns, &pl))
+                         pool != nullptr, direct_ns, 0, &pl))
     dual = 0;
   if (!dual && !plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 0,
-                          pool != nullptr, direct_ns, &pl))
+                          pool != nullptr, direct_ns, 0, &pl))
     return PDAC_OK;
   const bool direct = direct_ns || (direct_st && dual);
+  // Tap stacking (see HaloParams::stack): direct epilogue, N = 16, a single K chunk, 3 taps per kernel row, resident
+  // weights; taken when the cost model prefers its plan. PDAC_HALO_STACK=0 disables.
+  static int stack_ok = -1;
+  if (stack_ok < 0) {
+    const char* e = getenv("PDAC_HALO_STACK");
+    stack_ok = (e && e[0] == '0') ? 0 : 1;
+  }
+  bool stack = false;
+  // ck >= 32 only: with a 16-channel source the layer is HBM-bound already and the smaller stacked tile costs more than
+  // the MMAs it saves (measured: 16 -> 16 @512^2 0.213 -> 0.283 ms, 32 -> 16 0.392 -> 0.330 ms)
+  if (stack_ok && direct && dual && block_n == 16 && n_chunks == 1 && ck >= 32 && tap_s == 3 && ew <= 14 &&
+      pl.b_resident) {
+    HaloPlan ps = {0, 0, 0, 0, 0, 0, 0, 0.0};
+    if (plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1, 0, direct_ns, 1,
+                  &ps) &&
+        ps.b_resident && ps.cost < pl.cost) {
+      pl = ps;
+      stack = true;
+    }
+  }
 
   {
     static int dbg = -1;
@@ -1043,9 +1107,9 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
       dbg = (e && e[0] == '1') ? 1 : 0;
     }
     if (dbg)
-      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d dual=%d direct=%d cost=%.0f\n",
+      fprintf(stderr, "[conv_halo] %dx%dx%d K=%dx%d N=%d taps=%d: TW=%d TH=%d nacc=%d sa=%d sb=%d resident=%d n_wg=%d dual=%d direct=%d stack=%d cost=%.0f\n",
               out->N, out->H, out->W, n_chunks, ck, block_n, tc->n_taps, pl.TW, pl.TH, pl.nacc, pl.sa, pl.sb,
-              pl.b_resident, pl.n_wg, dual, (int)direct, pl.cost);
+              pl.b_resident, pl.n_wg, dual, (int)direct, (int)stack, pl.cost);
   }
   HaloMaps maps;
   HaloParams p;
@@ -1079,13 +1143,27 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     for (int t = 0; t < tc->n_taps; ++t)
       if (shift(t) != p.tap_base + (t / S) * p.tap_step_r + (t % S) * p.tap_step_s) return PDAC_OK;
   }
+  p.acc_cols = block_n;
+  p.issue_S = p.tap_S;
+  p.b_tap_mul = 1;
+  if (stack) {
+    const int lo = p.tap_step_s < 0 ? 2 * p.tap_step_s : 0;  // the leftmost tap of a kernel row
+    for (int sidx = 0; sidx < 3; ++sidx) p.stack_d[sidx] = sidx * p.tap_step_s - lo;
+    PDAC_REQUIRE(p.stack_d[0] >= 0 && p.stack_d[2] >= 0 && p.stack_d[0] + p.stack_d[2] <= ew && (p.PW == 16 || p.PW == 32),
+                 "internal: stacked halo plan (PW=%d step=%d)", p.PW, p.tap_step_s);
+    p.tap_base += lo;
+    p.stack = 1;
+    p.acc_cols = 3 * block_n;
+    p.issue_S = 1;
+    p.b_tap_mul = 3;
+  }
   p.pitch = ck * 2;
   p.layout_type = swizzle_layout_type(p.pitch);
-  p.idesc = make_idesc_bf16(128, block_n, 0, 0);
+  p.idesc = make_idesc_bf16(128, p.acc_cols, 0, 0);
   p.block_n = block_n;
   p.tiles_c = ceil_div(cout, block_n);
   p.wrows = tc->wrows;
-  p.tmem_cols = pow2_ceil(2 * pl.nacc * block_n < 32 ? 32 : 2 * pl.nacc * block_n);
+  p.tmem_cols = pow2_ceil(2 * pl.nacc * p.acc_cols < 32 ? 32 : 2 * pl.nacc * p.acc_cols);
   p.tiles_w = ceil_div(out->W, pl.TW);
   p.tiles_h = ceil_div(out->H, pl.TH);
   p.tiles_sp = p.tiles_w * p.tiles_h * out->N;
