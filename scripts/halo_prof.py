@@ -18,12 +18,18 @@ for i in range(0, len(args), 4):
     wp, _ = ops.pack_conv_weight(w, want_dgrad=False, cout_pad=cout)
     stats = ops.new_stats(cout, torch.device("cuda"))
     out = ops.empty_act(B, hw, hw, cout, "cuda")
+    if os.environ.get("HALO_OP") == "pool":      # data gradient CIN -> COUT channels, all of them 2x2-pooled
+        wt = torch.randn(cin, cout, 3, 3, device="cuda") * 0.05
+        _, wpt = ops.pack_conv_weight(wt, want_fwd=False, stride=1, pad=1, cout_pad=cin)
+        run = lambda: ops.conv2d_dgrad_pool2(xs[0], wpt, cout, 0, 3, 3, 1, 1)
+    else:
+        run = lambda: ops.conv2d_fwd(xs, wp, cout, 3, 3, 1, 1, 1, stats=stats, out=out)
     for _ in range(3):
-        ops.conv2d_fwd(xs, wp, cout, 3, 3, 1, 1, 1, stats=stats, out=out)
+        run()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    ops.conv2d_fwd(xs, wp, cout, 3, 3, 1, 1, 1, stats=stats, out=out)
+    run()
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     buf = (C.c_longlong * (160 * 16))()
