@@ -47,43 +47,76 @@ static int blocks_for(long long n) {
   const int n = (int)(r_ / (Hd));
 
 // ------------------------------------------------------------------------------------------------ maxpool 3x3 s2 p1
+// Packed bf16x2 arithmetic throughout: the first version unpacked every tap to fp32 and tracked value and index with a
+// compare + two selects per element (~400 instructions per thread, instruction-bound at 2.5 TB/s). Here the maximum is
+// 8 HMNMX2 per 32-bit word and the arg-max is "the first tap equal to the maximum" (one compare-to-mask and one LOP3 per
+// word and tap, walked backwards so the first match wins) — torch's `val > maxval` scan keeps the first maximum too.
+// NaNs (torch: the LAST NaN tap wins) take a scalar path.
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(V4 x, V4 y, uint8_t* __restrict__ idx) {
   const int cg = x.C / 8;
   const long long total = (long long)y.N * y.H * y.W * cg;
   PIX_LOOP(total) {
     DECODE(e, cg, y.W, y.H)
-    float best[8];
-    int bi[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      best[i] = -INFINITY;
-      bi[i] = 4;
-    }
+    uint4 v[9];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
       const int ih = 2 * h - 1 + r;
-      if (ih < 0 || ih >= x.H) continue;
 #pragma unroll
       for (int s = 0; s < 3; ++s) {
         const int iw = 2 * w - 1 + s;
-        if (iw < 0 || iw >= x.W) continue;
-        const F8 v = unpack8(ld16(x.at(n, ih, iw) + g * 8));
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          if (v.v[i] > best[i] || v.v[i] != v.v[i]) {
-            best[i] = v.v[i];
-            bi[i] = r * 3 + s;
-          }
+        const bool ok = ih >= 0 && ih < x.H && iw >= 0 && iw < x.W;
+        v[r * 3 + s] = ok ? ld16(x.at(n, ih, iw) + g * 8) : make_uint4(0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u);
       }
     }
-    F8 o;
+    uint32_t m[4], ip[4];
+    bool any_nan = false;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o.v[i] = best[i];
-    st16(y.at(n, h, w) + g * 8, pack8(o));
+    for (int k = 0; k < 4; ++k) {
+      __nv_bfloat162 mm = *reinterpret_cast<const __nv_bfloat162*>(&(&v[0].x)[k]);
+#pragma unroll
+      for (int t = 1; t < 9; ++t) mm = __hmax2_nan(mm, *reinterpret_cast<const __nv_bfloat162*>(&(&v[t].x)[k]));
+      m[k] = *reinterpret_cast<const uint32_t*>(&mm);
+      any_nan = any_nan || __hisnan(mm.x) || __hisnan(mm.y);
+      uint32_t id = 0x00040004u;
+#pragma unroll
+      for (int t = 8; t >= 0; --t) {
+        const uint32_t eq = __heq2_mask(*reinterpret_cast<const __nv_bfloat162*>(&(&v[t].x)[k]), mm);
+        id = (id & ~eq) | ((uint32_t)t * 0x00010001u & eq);
+      }
+      ip[k] = id;
+    }
+    if (any_nan) {  // rare: redo this vector the way torch scans it
+      float best[8];
+      int bi[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        best[i] = -INFINITY;
+        bi[i] = 4;
+      }
+      for (int t = 0; t < 9; ++t) {
+        const int ih = 2 * h - 1 + t / 3, iw = 2 * w - 1 + t % 3;
+        if (ih < 0 || ih >= x.H || iw < 0 || iw >= x.W) continue;
+        const F8 f = unpack8(v[t]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (f.v[i] > best[i] || f.v[i] != f.v[i]) {
+            best[i] = f.v[i];
+            bi[i] = t;
+          }
+      }
+      F8 o;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o.v[i] = best[i];
+      const uint4 pk = pack8(o);
+      m[0] = pk.x, m[1] = pk.y, m[2] = pk.z, m[3] = pk.w;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ip[k] = (uint32_t)bi[2 * k] | ((uint32_t)bi[2 * k + 1] << 16);
+    }
+    st16(y.at(n, h, w) + g * 8, make_uint4(m[0], m[1], m[2], m[3]));
     if (idx) {
-      uint2 p;
-      p.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
-      p.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+      uint2 p;  // byte 2k = low half of ip[k], byte 2k + 1 = high half
+      p.x = __byte_perm(ip[0], ip[1], 0x6420);
+      p.y = __byte_perm(ip[2], ip[3], 0x6420);
       *reinterpret_cast<uint2*>(idx + (((long long)n * y.H + h) * y.W + w) * x.C + g * 8) = p;
     }
   }
