@@ -155,8 +155,9 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
   __shared__ long long s_pooloff[MODE == 2 ? (DUAL ? 2 : 4) : 1][32];
   constexpr int AFF = MODE == 1 || MODE == 4;
   constexpr int POOL = MODE == 2;
-  constexpr int DIRECT = MODE >= 3;  // register -> global epilogue of the N <= 32 layers (see the epilogue role)
-  constexpr int DSTATS = MODE == 5;  // ... of a plain N = 16 convolution in front of a BatchNorm: store + partial sums
+  constexpr int DIRECT = MODE >= 3 && MODE <= 5;  // register -> global epilogue (see the epilogue role)
+  constexpr int DSTATS = MODE == 5;
+  constexpr int SSTACK = MODE == 7;  // staged epilogue (BatchNorm sums) of a tap-stacked N <= 32 layer  // ... of a plain N = 16 convolution in front of a BatchNorm: store + partial sums
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -272,8 +273,9 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
         mbar_expect_tx(&full_b[0], (uint32_t)b_bytes);
         for (int t = 0; t < p.n_taps; ++t)
           for (int c = 0; c < p.n_chunks; ++c)
-            tma_load_2d(smem_b + (size_t)(t * p.n_chunks + c) * p.b_sub, &maps.w, &full_b[0], c * p.ck,
-                        t * p.wrows + n0);
+            // tap stacking: the three taps of a kernel row lie side by side per (row, chunk) = one N' = 3 N operand
+            tma_load_2d(smem_b + (size_t)(p.stack ? ((t / 3) * p.n_chunks + c) * 3 + t % 3 : t * p.n_chunks + c) * p.b_sub,
+                        &maps.w, &full_b[0], c * p.ck, t * p.wrows + n0);
       } else {
         int stage = 0;
         uint32_t phase = 0;
@@ -353,7 +355,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
             const long long t_ld0 = clock64();
 #endif
             if (leader) {
-              uint32_t b_lo = b_lo0 + (uint32_t)c * b_sub16;
+              uint32_t b_lo = b_lo0 + (uint32_t)(c * p.b_tap_mul) * b_sub16;
               uint32_t acc = c ? 1u : 0u;
               uint32_t a_row = a_stage;
               for (int r = 0; r < TR; ++r, a_row += step_r) {
@@ -545,7 +547,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
               uint32_t v[16];
               tmem_ld16(tacc + (uint32_t)cb, v);
               tmem_ld_wait();
-              if (p.stack) {  // N = 16: one chunk; see DSTATS above
+              if (p.stack) {  // see DSTATS above; slot s of a stacked accumulator starts at column s * N
                 if (p.stack_d[0]) {
 #pragma unroll
                   for (int i = 0; i < 16; ++i) v[i] = __shfl_down_sync(0xffffffffu, v[i], p.stack_d[0]);
@@ -553,7 +555,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
 #pragma unroll
                 for (int sl = 1; sl < 3; ++sl) {
                   uint32_t u[16];
-                  tmem_ld16(tacc + (uint32_t)(sl * 16), u);
+                  tmem_ld16(tacc + (uint32_t)(sl * p.block_n + cb), u);
                   tmem_ld_wait();
 #pragma unroll
                   for (int i = 0; i < 16; ++i)
@@ -676,7 +678,7 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                                   : -1;
           }
           const uint32_t tacc =
-              tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.block_n);
+              tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((g * p.nacc + j) * p.acc_cols);
 #pragma unroll
           for (int pass = 0; pass < NPASS; ++pass) {
             const int c0 = pass * 64;
@@ -687,6 +689,22 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
                 uint32_t v[16];
                 tmem_ld16(tacc + (uint32_t)(c0 + c), v);
                 tmem_ld_wait();
+                if (SSTACK) {  // N <= 32: add the other two taps of the kernel row from the lanes to the right
+                  if (p.stack_d[0]) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = __shfl_down_sync(0xffffffffu, v[i], p.stack_d[0]);
+                  }
+#pragma unroll
+                  for (int sl = 1; sl < 3; ++sl) {
+                    uint32_t u[16];
+                    tmem_ld16(tacc + (uint32_t)(sl * p.block_n + c), u);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                      v[i] = __float_as_uint(__uint_as_float(v[i]) +
+                                             __uint_as_float(__shfl_down_sync(0xffffffffu, u[i], p.stack_d[sl])));
+                  }
+                }
                 float f[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
@@ -1088,12 +1106,15 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   }
   bool stack = false;
   // ck >= 32 only: with a 16-channel source the layer is HBM-bound already and the smaller stacked tile costs more than
-  // the MMAs it saves (measured: 16 -> 16 @512^2 0.213 -> 0.283 ms, 32 -> 16 0.392 -> 0.330 ms)
-  if (stack_ok && direct && dual && block_n == 16 && n_chunks == 1 && ck >= 32 && tap_s == 3 && ew <= 14 &&
-      pl.b_resident) {
+  // the MMAs it saves (measured: 16 -> 16 @512^2 0.213 -> 0.283 ms, 32 -> 16 0.392 -> 0.330 ms). Direct epilogues take it
+  // as they are; a layer with BatchNorm sums that is not the N = 16 direct case gets the staged variant (mode 7).
+  // (two CTAs per SM with N = 32, i.e. the 32 -> 32 layers: TMEM holds one stacked accumulator per tile stage only, and
+  // the 128-row tile made both the forward, 0.163 -> 0.194 ms, and the data gradient, 0.119 -> 0.160 ms, slower)
+  if (stack_ok && !pool && (cout & 7) == 0 && block_n <= 32 && ck >= 32 && tap_s == 3 && ew <= 14 && pl.b_resident &&
+      (direct || !epi_scale()) && !(dual && block_n == 32)) {
     HaloPlan ps = {0, 0, 0, 0, 0, 0, 0, 0.0};
-    if (plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, 1, 0, direct_ns, 1,
-                  &ps) &&
+    if (plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, dual, 0, direct_ns,
+                  1, &ps) &&
         ps.b_resident && ps.cost < pl.cost) {
       pl = ps;
       stack = true;
@@ -1237,18 +1258,21 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   // the statistics variant of the direct epilogue (mode 5) exists for the two-CTAs-per-SM kernels only
 #define HALO_ROW_D(n, mode) \
   { nullptr, nullptr, nullptr, conv_halo_kernel<n, 1, 1, mode>, conv_halo_kernel<n, 2, 1, mode> }
-  static const HaloKernel table[6][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
+  static const HaloKernel table[8][4][5] = {{HALO_ROW(1, 0), HALO_ROW(2, 0), HALO_ROW(3, 0), HALO_ROW(4, 0)},
                                             {HALO_ROW(1, 1), HALO_ROW(2, 1), HALO_ROW(3, 1), HALO_ROW(4, 1)},
                                             {HALO_ROW(1, 2), HALO_ROW(2, 2), HALO_ROW(3, 2), HALO_ROW(4, 2)},
                                             {HALO_ROW(1, 3), HALO_ROW(2, 3), HALO_ROW(3, 3), HALO_ROW(4, 3)},
                                             {HALO_ROW(1, 4), HALO_ROW(2, 4), HALO_ROW(3, 4), HALO_ROW(4, 4)},
-                                            {HALO_ROW_D(1, 5), HALO_ROW_D(2, 5), HALO_ROW_D(3, 5), HALO_ROW_D(4, 5)}};
+                                            {HALO_ROW_D(1, 5), HALO_ROW_D(2, 5), HALO_ROW_D(3, 5), HALO_ROW_D(4, 5)},
+                                            {{}, {}, {}, {}},
+                                            {HALO_ROW(1, 7), HALO_ROW(2, 7), HALO_ROW(3, 7), HALO_ROW(4, 7)}};
 #undef HALO_ROW
 #undef HALO_ROW_D
-  static bool attr_set[6][4][5] = {};
-  const int ka = pool ? 2 : (direct ? (stats ? 5 : (p.scale ? 4 : 3)) : (p.scale ? 1 : 0));
+  static bool attr_set[8][4][5] = {};
+  const int ka = pool ? 2 : (direct ? (stats ? 5 : (p.scale ? 4 : 3)) : (stack ? 7 : (p.scale ? 1 : 0)));
   const int ki = pl.nacc - 1, kj = (ck == 16 ? 0 : (ck == 32 ? 1 : 2)) + (dual ? 3 : 0);
   HaloKernel kern = table[ka][ki][kj];
+  PDAC_REQUIRE(kern != nullptr, "internal: no halo kernel for mode %d (nacc %d, variant %d)", ka, pl.nacc, kj);
   if (!attr_set[ka][ki][kj]) {
     PDAC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((dual ? 105 : 221) * 1024)));
     if (dual)
