@@ -1110,7 +1110,13 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   // as they are; a layer with BatchNorm sums that is not the N = 16 direct case gets the staged variant (mode 7).
   // (two CTAs per SM with N = 32, i.e. the 32 -> 32 layers: TMEM holds one stacked accumulator per tile stage only, and
   // the 128-row tile made both the forward, 0.163 -> 0.194 ms, and the data gradient, 0.119 -> 0.160 ms, slower)
-  if (stack_ok && !pool && (cout & 7) == 0 && block_n <= 32 && ck >= 32 && tap_s == 3 && ew <= 14 && pl.b_resident &&
+  static int stack_maxn = -1;  // experiment switch: PDAC_HALO_STACK_MAXN (default 32)
+  if (stack_maxn < 0) {
+    const char* e = getenv("PDAC_HALO_STACK_MAXN");
+    stack_maxn = e ? atoi(e) : 32;
+  }
+  if (stack_ok && !pool && (cout & 7) == 0 && block_n <= stack_maxn && 3 * block_n <= 256 && ck >= 32 && tap_s == 3 &&
+      ew <= 14 && pl.b_resident &&
       (direct || !epi_scale()) && !(dual && block_n == 32)) {
     HaloPlan ps = {0, 0, 0, 0, 0, 0, 0, 0.0};
     if (plan_halo(out->H, out->W, block_n, tc->n_taps, tap_s, n_chunks, ck, eh, ew, addend != nullptr, dual, 0, direct_ns,
