@@ -169,29 +169,27 @@ struct PackItem {
 struct PackBatch {
   PackItem it[kPackBatch];
 };
+// One thread per (row, k) pair of a packed matrix: it reads the R*S taps of its (o, i) weight, which are contiguous in
+// the state_dict layout, and writes one element into each tap plane. (The first version walked the packed elements and
+// gathered every tap plane separately: nine passes over the fp32 weights through L2 with 36-byte strides, 0.2 ms per
+// step for 57 MB of parameters.)
 __global__ void __launch_bounds__(256) pack_conv_weight_batched_kernel(const __grid_constant__ PackBatch b) {
   const PackItem& d = b.it[blockIdx.y];
-  const long long nf = d.wf ? (long long)d.RS * d.wrows_f * d.kf : 0;
-  const long long nt = d.wt ? (long long)d.RS * d.wrows_t * d.kt : 0;
+  const long long nf = d.wf ? (long long)d.wrows_f * d.kf : 0;
+  const long long nt = d.wt ? (long long)d.wrows_t * d.kt : 0;
+  const long long plane_f = (long long)d.wrows_f * d.kf, plane_t = (long long)d.wrows_t * d.kt;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < nf + nt; e += (long long)gridDim.x * blockDim.x) {
-    if (e < nf) {
-      const int i = (int)(e % d.kf);
-      const long long r = e / d.kf;
-      const int o = (int)(r % d.wrows_f);
-      const int t = (int)(r / d.wrows_f);
-      const float v = (o < d.O && i < d.I) ? d.w[((long long)o * d.I + i) * d.RS + t] : 0.f;
-      d.wf[e] = __float2bfloat16(v);
-    } else {
+    if (e < nf) {  // forward matrix [tap][o][i]
+      const int i = (int)(e % d.kf), o = (int)(e / d.kf);
+      const bool ok = o < d.O && i < d.I;
+      const float* src = d.w + ((long long)o * d.I + i) * d.RS;
+      for (int t = 0; t < d.RS; ++t) d.wf[t * plane_f + e] = __float2bfloat16(ok ? src[t] : 0.f);
+    } else {  // data-gradient matrix [tap position][i][o]
       const long long e2 = e - nf;
-      const int o = (int)(e2 % d.kt);
-      const long long r = e2 / d.kt;
-      const int i = (int)(r % d.wrows_t);
-      const int tp = (int)(r / d.wrows_t);
-      int t = 0;
-      for (int k = 0; k < d.RS; ++k)
-        if (d.pos[k] == tp) t = k;
-      const float v = (o < d.O && i < d.I) ? d.w[((long long)o * d.I + i) * d.RS + t] : 0.f;
-      d.wt[e2] = __float2bfloat16(v);
+      const int o = (int)(e2 % d.kt), i = (int)(e2 / d.kt);
+      const bool ok = o < d.O && i < d.I;
+      const float* src = d.w + ((long long)o * d.I + i) * d.RS;
+      for (int t = 0; t < d.RS; ++t) d.wt[d.pos[t] * plane_t + e2] = __float2bfloat16(ok ? src[t] : 0.f);
     }
   }
 }
@@ -365,7 +363,7 @@ extern "C" int pdac_pack_conv_weights_batched(const PdacPackDesc* descs, int n, 
       it.kt = d.kt;
       s2_tap_positions(d.R, d.S, d.s2_pad, it.pos);
     }
-    pack_conv_weight_batched_kernel<<<dim3(96, m), 256, 0, (cudaStream_t)stream>>>(b);
+    pack_conv_weight_batched_kernel<<<dim3(2 * num_sms(), m), 256, 0, (cudaStream_t)stream>>>(b);
     PDAC_LAUNCH_CHECK("pack_conv_weight_batched");
   }
   return PDAC_OK;
