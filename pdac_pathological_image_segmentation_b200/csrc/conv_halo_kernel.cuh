@@ -12,8 +12,17 @@
 // overlaps the main loop of tile i+1. Weights stay resident in shared memory for the whole (persistent) CTA when they
 // fit, otherwise they stream through their own ring, each stage reused by the nacc accumulators of the tile.
 //
-// Roles: warp 0 = A (halo) TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..9 = two epilogue warpgroups
-// (accumulators of a tile alternate between them), warp 10 = weight TMA producer.
+// Roles: warp 0 = A (halo) TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2.. = two or four epilogue
+// warpgroups (accumulators of a tile are dealt round-robin), last warp = weight TMA producer.
+//
+// MODE picks the epilogue (separate instantiations: each sits at the register limit of its launch bounds):
+//   0 staged (TMEM -> registers -> bf16 staging tile -> 16-byte coalesced stores + BatchNorm partial sums)
+//   1 staged, folded-BatchNorm inference (per-channel scale / shift)
+//   2 staged, the leading channels summed over 2 x 2 pixel blocks (data gradient in front of a nearest x2 upsampling)
+//   3 direct (TMEM -> registers -> 32-byte stores, no staging, no barriers): every launch without BatchNorm sums
+//   4 direct, folded-BatchNorm inference
+//   5 direct + BatchNorm sums of the plain N = 16 convolution (lane pairs split the channels: 16 sum registers)
+//   7 staged + tap stacking (N <= 32 with BatchNorm sums); modes 3-5 take stacking through HaloParams::stack
 //
 // This header holds the device code; it is compiled in four translation units (conv_halo_k0..k3.cu, one group of
 // epilogue modes each) so that `make -j` builds them in parallel, and conv_halo.cu (host planner + launch) looks the
