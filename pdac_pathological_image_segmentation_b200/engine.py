@@ -157,6 +157,20 @@ class Tape:
         # half-resolution 2x2 sum (written by the consuming conv's fused data-gradient kernel)
         self.up2_src = set()
         self.pooled = set()
+        # BatchNorm partial-sum tables of the conv epilogues: the trainer hands over ONE zeroed buffer per step (sized
+        # from the previous step's demand) instead of ~30 separate fills; without it every table is its own torch.zeros
+        self.stats_pool = None
+        self.stats_used = 0
+
+    def new_stats(self, c, device):
+        """Zeroed [STAT_ROWS, 2, c] table (ops.new_stats), carved from the step's pool while it lasts."""
+        n = ops.STAT_ROWS * 2 * c
+        off = self.stats_used
+        self.stats_used += n
+        pool = self.stats_pool
+        if pool is not None and off + n <= pool.numel() and pool.device == torch.device(device):
+            return pool[off:off + n].view(ops.STAT_ROWS, 2, c)
+        return ops.new_stats(c, device)
 
     def record(self, fn, params=()):
         """fn: the layer's backward step; params: the parameters whose gradient slots that step completes (the
@@ -303,7 +317,7 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
         y = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, relu=relu, bias=st.ss[1],
                            addend=residual, scale=st.ss[0], out=out)
         return ops.upsample_nearest2x_fwd(y) if up2 else y
-    stats = ops.new_stats(m.cout, dev) if tape.training else None
+    stats = tape.new_stats(m.cout, dev) if tape.training else None
     x = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
     keep_x = tape.enabled
@@ -350,7 +364,7 @@ def stem(tape: Tape, m: Conv2d, bn: BatchNorm2d, z):
     if not tape.training and not tape.enabled:
         st = _bn_prepare(tape, bn, None, 1, dev)
         return ops.stem_conv_fwd(z, wp, m.cout, scale=st.ss[0], shift=st.ss[1], relu=True)
-    stats = ops.new_stats(m.cout, dev) if tape.training else None
+    stats = tape.new_stats(m.cout, dev) if tape.training else None
     x = ops.stem_conv_fwd(z, wp, m.cout, stats=stats)
     st = _bn_prepare(tape, bn, stats, x.shape[0] * x.shape[1] * x.shape[2], dev)
     y = ops.scale_shift_act(x, st.ss, None, relu=True, out=None if tape.enabled else x)

@@ -94,6 +94,7 @@ class TrainStep:
         self.overlap = bool(overlap) and os.environ.get("PDAC_DDP_OVERLAP", "1") != "0"
         self._g_key = None
         self._host_rng = False
+        self._stats_need = 0      # floats of BatchNorm partial-sum tables the last step asked for
         self._comm_in_graph = True
         self.params = model._trainable()
         dev = self.params[0].device
@@ -170,7 +171,10 @@ class TrainStep:
         else:
             z, mask = ops.stem_prep_u8(img_u8, mask_u8, aug)
         tape = Tape(model._packs, model.training, self.arena, step_dev=self.step_dev, base_seed=self._seed)
+        if self._stats_need:      # one memset for all BatchNorm partial-sum tables of the step
+            tape.stats_pool = torch.zeros(self._stats_need, dtype=torch.float32, device=self.device)
         logits, feed = model._run(tape, z)
+        self._stats_need = tape.stats_used
         self._host_rng = bool(getattr(tape, "host_rng", False))
         if logits.shape[1] != 1:
             raise RuntimeError("TrainStep implements the reference's 1-class sigmoid/Dice step (train_worker.py:150-182)")
