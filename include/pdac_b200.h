@@ -121,6 +121,11 @@ int pdac_conv2d_fwd(const PdacConv* cv, int n_src, const PdacView* src, const vo
                     const PdacView* addend, const PdacView* out, float* stats, void* stream);
 int pdac_conv2d_fwd_affine(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed, const float* scale,
                            const float* shift, const PdacView* addend, const PdacView* out, void* stream);
+/* The same (without addend) stored nearest-neighbour x2 upsampled into out2x (N, 2Ho, 2Wo, Cout): inference form of an
+ * smp decoder block's last Conv2dReLU in front of the next block's F.interpolate(x, scale_factor=2, mode="nearest").
+ * *handled = 0 (and PDAC_OK): not eligible, nothing launched — run pdac_conv2d_fwd_affine + pdac_upsample_nearest2x_fwd. */
+int pdac_conv2d_fwd_affine_up2(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed,
+                               const float* scale, const float* shift, const PdacView* out2x, int* handled, void* stream);
 /* dx = conv_transpose(dy, w) (+ addend): the data gradient of the conv described by cv. w_packed_t:
  * [R*S*wrows][Cout] with row (r*S+s)*wrows + cin (taps un-flipped: the library derives the offsets). For
  * stride 2 the four output parity classes are separate launches; classes no tap reaches get addend or zero. */

@@ -54,6 +54,7 @@ SIGNATURES = {
     "pdac_tapconv_wgrad": [C.POINTER(PdacTapConv), _i, _VP, _VP, _p, C.c_int64, C.c_int64, C.c_int64, _i, _p, _ll, _p],
     "pdac_conv2d_fwd": [C.POINTER(PdacConv), _i, _VP, _p, _p, _VP, _VP, _p, _p],
     "pdac_conv2d_fwd_affine": [C.POINTER(PdacConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
+    "pdac_conv2d_fwd_affine_up2": [C.POINTER(PdacConv), _i, _VP, _p, _p, _p, _VP, C.POINTER(C.c_int), _p],
     "pdac_tapconv_fwd_affine": [C.POINTER(PdacTapConv), _i, _VP, _p, _p, _p, _VP, _VP, _p],
     "pdac_conv2d_dgrad": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, _p],
     "pdac_conv2d_dgrad_pool2": [C.POINTER(PdacConv), _VP, _p, _VP, _VP, C.POINTER(C.c_int), _p],

@@ -27,6 +27,9 @@ const float* epi_scale() { return g_epi_scale; }
 static thread_local const PdacView* g_epi_pool = nullptr;
 void set_epi_pool(const PdacView* pooled) { g_epi_pool = pooled; }
 const PdacView* epi_pool() { return g_epi_pool; }
+static thread_local const PdacView* g_epi_up2 = nullptr;
+void set_epi_up2(const PdacView* full) { g_epi_up2 = full; }
+const PdacView* epi_up2() { return g_epi_up2; }
 
 static thread_local int g_last_kernel = 0;
 void note_kernel(int id) { g_last_kernel = id; }

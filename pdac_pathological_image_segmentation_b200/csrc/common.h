@@ -54,6 +54,10 @@ const float* epi_scale();
 // the 2x2 sum of a nearest-neighbour x2 upsampling's gradient, formed in the halo kernel's epilogue).
 void set_epi_pool(const PdacView* pooled);
 const PdacView* epi_pool();
+// Full-resolution (2H x 2W) destination of the next tap convolution when its output is to be stored nearest-neighbour
+// x2 upsampled (set by pdac_conv2d_fwd_affine_up2; the halo kernel's direct epilogue stores every pixel four times).
+void set_epi_up2(const PdacView* full);
+const PdacView* epi_up2();
 
 // Deterministic cross-block reductions (no floating-point atomics): out[c] (+)= sum over rows 0..n_rows-1 of
 // rows[r][c], added in a fixed order (bn.cu).

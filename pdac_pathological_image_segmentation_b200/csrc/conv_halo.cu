@@ -187,7 +187,9 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
     const char* e = getenv("PDAC_HALO_DIRECT");
     direct_ok = (e && e[0] == '0') ? 0 : 1;
   }
-  const bool aligned32 = ((uintptr_t)out->ptr & 31) == 0 && out->sW % 16 == 0 && out->sH % 16 == 0 && out->sN % 16 == 0;
+  const PdacView* up2 = epi_up2();  // `out` = the even pixels of this (2H, 2W) tensor
+  const bool aligned32 = ((uintptr_t)out->ptr & 31) == 0 && out->sW % 16 == 0 && out->sH % 16 == 0 && out->sN % 16 == 0 &&
+                         (!up2 || (up2->sW % 16 == 0 && up2->sH % 16 == 0));
   const bool plain = !bias && !addend && !epi_scale() && !tc->relu;
   const bool direct_ns = direct_ok && !pool && (cout & 7) == 0 && aligned32 && !stats;
   const bool direct_st = direct_ok && !pool && cout == 16 && plain && aligned32 && stats;
@@ -199,6 +201,7 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
                           pool != nullptr, direct_ns, 0, &pl))
     return PDAC_OK;
   const bool direct = direct_ns || (direct_st && dual);
+  if (up2 && !direct_ns) return PDAC_OK;  // the replicated stores exist in the statistics-free direct epilogue only
   // Tap stacking (see HaloParams::stack): direct epilogue, N = 16, a single K chunk, 3 taps per kernel row, resident
   // weights; taken when the cost model prefers its plan. PDAC_HALO_STACK=0 disables.
   static int stack_ok = -1;
@@ -329,6 +332,11 @@ int conv_halo_try(const PdacTapConv* tc, int n_views, const PdacView* views, con
   p.stats = stats;
   p.relu = tc->relu;
   p.err = device_err_flag();
+  if (up2) {
+    p.up2 = 1;
+    p.up_dh = up2->sH;
+    p.up_dw = up2->sW;
+  }
   if (pool) {
     PDAC_REQUIRE((128 % p.PW) == 0 && ((128 / p.PW) & 1) == 0 && p.TH == p.nacc * (128 / p.PW),
                  "internal: pooled halo plan (PW=%d TH=%d nacc=%d)", p.PW, p.TH, p.nacc);

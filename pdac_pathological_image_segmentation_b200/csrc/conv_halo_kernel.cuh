@@ -79,6 +79,10 @@ struct HaloParams {
   // left, and the epilogue adds the three blocks across lanes (PW is 16 or 32: an image row never leaves its warp).
   int stack, acc_cols, issue_S, b_tap_mul;
   int stack_d[3];
+  // direct epilogue only: store every output pixel to the 2 x 2 block it becomes under a nearest x2 upsampling (`out`
+  // then addresses the even pixels of the (2H, 2W) tensor: osH / osW are twice its strides, up_dh / up_dw its own)
+  int up2;
+  long long up_dh, up_dw;
   bf16* pout;
   long long psN, psH, psW;
 };
@@ -630,10 +634,22 @@ __global__ void __launch_bounds__(DUAL ? kHaloThreadsDual : kHaloThreads, DUAL ?
 #pragma unroll
               for (int i = 0; i < 8; ++i) r[i] = h_pack(f[2 * i], f[2 * i + 1]);
               if (valid && !DBG(0)) {
-                if (cb + 16 <= nch)
+                if (cb + 16 <= nch) {
                   stg256(orow + cb, r);
-                else if (cb + 8 <= nch)
-                  *reinterpret_cast<uint4*>(orow + cb) = make_uint4(r[0], r[1], r[2], r[3]);
+                  if (p.up2) {
+                    stg256(orow + cb + p.up_dw, r);
+                    stg256(orow + cb + p.up_dh, r);
+                    stg256(orow + cb + p.up_dh + p.up_dw, r);
+                  }
+                } else if (cb + 8 <= nch) {
+                  const uint4 r4 = make_uint4(r[0], r[1], r[2], r[3]);
+                  *reinterpret_cast<uint4*>(orow + cb) = r4;
+                  if (p.up2) {
+                    *reinterpret_cast<uint4*>(orow + cb + p.up_dw) = r4;
+                    *reinterpret_cast<uint4*>(orow + cb + p.up_dh) = r4;
+                    *reinterpret_cast<uint4*>(orow + cb + p.up_dh + p.up_dw) = r4;
+                  }
+                }
               }
             }
           }

@@ -1040,6 +1040,35 @@ extern "C" int pdac_conv2d_fwd_affine(const PdacConv* cv, int n_src, const PdacV
   return rc;
 }
 
+// conv + folded BatchNorm (+ ReLU) stored nearest-neighbour x2 upsampled: inference form of smp's decoder block output
+// in front of the next block's F.interpolate(scale_factor=2, mode="nearest"). out2x is (N, 2Ho, 2Wo, Cout). *handled = 0:
+// not eligible for the halo kernel's direct epilogue, nothing launched (run the conv and pdac_upsample_nearest2x_fwd).
+extern "C" int pdac_conv2d_fwd_affine_up2(const PdacConv* cv, int n_src, const PdacView* src, const void* w_packed,
+                                          const float* scale, const float* shift, const PdacView* out2x, int* handled,
+                                          void* stream) {
+  PDAC_REQUIRE(cv && src && w_packed && scale && shift && out2x && handled, "conv2d_fwd_affine_up2: null argument");
+  *handled = 0;
+  if (cv->stride != 1 || n_src < 1 || n_src > 2 || (out2x->H & 1) || (out2x->W & 1)) return PDAC_OK;
+  PDAC_TRY(check_dev_ptr(out2x->ptr, "out2x"));
+  PdacTapConv tc;
+  PdacView views[4];
+  int nv = 0;
+  memset(&tc, 0, sizeof(tc));
+  PDAC_TRY(build_fwd_taps(cv, n_src, src, &tc, views, &nv));
+  PdacView out = *out2x;  // the even pixels
+  out.H = out2x->H / 2;
+  out.W = out2x->W / 2;
+  out.sH = 2 * out2x->sH;
+  out.sW = 2 * out2x->sW;
+  if (out.H != src[0].H || out.W != src[0].W || out.N != src[0].N) return PDAC_OK;  // spatial-size-preserving convs only
+  set_epi_scale(scale);
+  set_epi_up2(out2x);
+  const int rc = conv_halo_try(&tc, nv, views, w_packed, shift, nullptr, &out, nullptr, stream, handled);
+  set_epi_up2(nullptr);
+  set_epi_scale(nullptr);
+  return rc;
+}
+
 extern "C" int pdac_tapconv_fwd_affine(const PdacTapConv* tc, int n_views, const PdacView* views, const void* w_packed,
                                        const float* scale, const float* shift, const PdacView* addend,
                                        const PdacView* out, void* stream) {

@@ -89,6 +89,25 @@ class PackCache:
             return ops.conv_pack_recipe(m.weight.detach(), wp_f, wp_t, stride=m.stride, pad=m.padding, cout_pad=cpad)
         return self._get((id(m), want_dgrad), (m.weight, m.bias), build, redo)
 
+    def bn_eval(self, bn: BatchNorm2d, compute):
+        """Eval-mode BatchNorm as (scale / shift, mean / invstd) tensors, computed once per parameter version instead of by
+        one bn_prepare launch per layer and forward (30 launches, 0.2 of the 5.5 ms of a whole-slide inference batch).
+        compute(ss, mi) fills the two [2, C] tensors. Training-mode statistics updates drop the entry (drop_bn)."""
+        def build():
+            c = bn.num_features
+            dev = bn.weight.device
+            val = (torch.empty((2, c), dtype=F32, device=dev), torch.empty((2, c), dtype=F32, device=dev))
+            compute(*val)
+            return val
+
+        def redo(val):
+            compute(*val)
+            return None
+        return self._get(("bn", id(bn)), (bn.weight, bn.bias, bn.running_mean, bn.running_var), build, redo)
+
+    def drop_bn(self, bn: BatchNorm2d):
+        self._c.pop(("bn", id(bn)), None)
+
     def convt(self, m: ConvTranspose2d):
         def build():
             wp_f, wp_t = ops.pack_convt_weight(m.weight.detach().contiguous())
@@ -292,6 +311,14 @@ class _BNState:
 def _bn_prepare(tape, bn: BatchNorm2d, stats, count, device):
     st = _BNState()
     c = bn.num_features
+    if not tape.training:      # running statistics: a pure function of the module's parameters and buffers -> cached
+        def compute(ss, mi):
+            ops.bn_prepare(None, 1, bn.weight.detach(), bn.bias.detach(), bn.eps, bn.momentum, False,
+                           bn.running_mean, bn.running_var, ss, mi, num_batches_tracked=None)
+        st.ss, st.mi = tape.packs.bn_eval(bn, compute)
+        st.count = count
+        return st
+    tape.packs.drop_bn(bn)     # this call updates the running statistics through raw pointers
     st.ss = torch.empty((2, c), dtype=F32, device=device)
     st.mi = torch.empty((2, c), dtype=F32, device=device)
     st.count = count
@@ -314,6 +341,11 @@ def conv_bn_act(tape: Tape, m: Conv2d, bn: BatchNorm2d, srcs, relu=True, residua
     if not tape.training and not tape.enabled:
         # inference: BatchNorm is a per-channel affine map -> folded (with the residual and the ReLU) into the conv epilogue
         st = _bn_prepare(tape, bn, None, 1, dev)
+        if up2 and residual is None and out is None and m.stride == 1:
+            # the next decoder block's upsampling written by this conv's epilogue (every pixel stored four times)
+            y2 = ops.conv2d_fwd_affine_up2(srcs, wp_f, m.cout, k, k, m.padding, m.dilation, relu, st.ss[0], st.ss[1])
+            if y2 is not None:
+                return y2
         y = ops.conv2d_fwd(srcs, wp_f, m.cout, k, k, m.stride, m.padding, m.dilation, relu=relu, bias=st.ss[1],
                            addend=residual, scale=st.ss[0], out=out)
         return ops.upsample_nearest2x_fwd(y) if up2 else y

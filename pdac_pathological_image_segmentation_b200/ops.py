@@ -161,6 +161,26 @@ def conv2d_dgrad(dy, wpt, cin, in_hw, R, S, stride=1, pad=0, dil=1, addend=None,
 
 
 fuse_up2_bwd = os.environ.get("PDAC_FUSE_UP2_BWD", "1") != "0"
+fuse_up2_infer = os.environ.get("PDAC_FUSE_UP2_INFER", "1") != "0"
+
+
+def conv2d_fwd_affine_up2(srcs, wp, cout, R, S, pad, dil, relu, scale, shift):
+    """[relu](conv(cat(srcs)) * scale + shift) stored nearest-neighbour x2 upsampled -> (N, 2H, 2W, cout), or None when
+    the fused kernel does not take the layer (the caller then runs conv2d_fwd + upsample_nearest2x_fwd)."""
+    x0 = srcs[0]
+    ktot = sum(s.shape[3] for s in srcs)
+    if not fuse_up2_infer or cout % 8 or (R - 1) * dil != 2 * pad or (S - 1) * dil != 2 * pad:
+        return None
+    wrows = wp.shape[0] // (R * S)
+    assert wp.dtype == BF16 and wp.is_contiguous() and wp.shape[1] == ktot
+    out = empty_act(x0.shape[0], 2 * x0.shape[1], 2 * x0.shape[2], cout, x0.device)
+    cv = _conv_struct(R, S, 1, pad, dil, relu, wrows)
+    views = (PdacView * len(srcs))(*[view(s) for s in srcs])
+    handled = C.c_int(0)
+    call("pdac_conv2d_fwd_affine_up2", C.byref(cv), len(srcs), views, _ptr(wp), _ptr(scale), _ptr(shift), _vp(out),
+         C.byref(handled), _stream(), flops=2 * x0.shape[0] * x0.shape[1] * x0.shape[2] * cout * ktot * R * S,
+         nbytes=_act_bytes(out, *srcs), tag=f"fwd+bn+up2 {R}x{S}s1d{dil} {x0.shape[0]}x{x0.shape[1]}x{x0.shape[2]} {ktot}->{cout}")
+    return out if handled.value else None
 
 
 def conv2d_dgrad_pool2(dy, wpt, c_pool, c_rest, R, S, pad=0, dil=1, c_real=None):

@@ -283,3 +283,40 @@ def test_conv_dgrad_pool2_declines_what_it_cannot_take():
     _, wpt = ops.pack_conv_weight(w.float().contiguous(), want_fwd=False, stride=1, pad=1, cout_pad=16)
     assert ops.conv2d_dgrad_pool2(_nhwc(_rnd(1, 16, 7, 8, seed=2)), wpt, 16, 0, 3, 3, 1, 1) is None      # odd height
     assert ops.conv2d_dgrad_pool2(_nhwc(_rnd(1, 16, 8, 8, seed=2)), wpt, 12, 4, 3, 3, 1, 1) is None      # 8-channel groups
+
+
+# ------------------------------------------------------------------ inference: conv + folded BatchNorm stored x2 upsampled
+UP2_CASES = [
+    # N, H, W, [cins], cout
+    (2, 16, 16, [64], 32),
+    (2, 32, 32, [32], 16),        # two CTAs per SM, tap stacking
+    (1, 64, 64, [16], 16),
+    (2, 16, 16, [128, 64], 64),   # concatenated sources
+    (1, 10, 12, [64], 64),        # partial tiles
+    (1, 16, 16, [256], 256),      # two N tiles
+    (1, 8, 8, [512, 256], 256),   # streamed weights
+]
+
+
+@pytest.mark.parametrize("case", UP2_CASES, ids=[str(c) for c in UP2_CASES])
+def test_conv_affine_up2_equals_conv_then_nearest_upsampling(case):
+    """pdac_conv2d_fwd_affine_up2 (smp decoder block output in front of F.interpolate(scale_factor=2, 'nearest'), eval
+    mode) == pdac_conv2d_fwd_affine followed by pdac_upsample_nearest2x_fwd, bit for bit."""
+    from pdac_pathological_image_segmentation_b200 import ops
+    N, H, W, cins, cout = case
+    cin = sum(cins)
+    xs = [_nhwc(_rnd(N, c, H, W, seed=21 + i)) for i, c in enumerate(cins)]
+    w = _rnd(cout, cin, 3, 3, scale=0.05, seed=23)
+    g = torch.Generator().manual_seed(24)
+    ss = torch.stack([0.5 + torch.rand(cout, generator=g), 0.2 * torch.randn(cout, generator=g)]).to(DEV)
+    wp, _ = ops.pack_conv_weight(w.float().contiguous(), want_dgrad=False, cout_pad=cout)
+    y = ops.conv2d_fwd(xs, wp, cout, 3, 3, 1, 1, 1, relu=True, bias=ss[1], scale=ss[0])
+    want = ops.upsample_nearest2x_fwd(y)
+    got = ops.conv2d_fwd_affine_up2(xs, wp, cout, 3, 3, 1, 1, True, ss[0], ss[1])
+    ops.check_device_flag()
+    assert got is not None, "the fused kernel refused an eligible layer"
+    assert got.shape == (N, 2 * H, 2 * W, cout)
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+    ref = F.relu(F.conv2d(torch.cat([x.permute(0, 3, 1, 2) for x in xs], 1).float(), w.float(), padding=1)
+                 * ss[0].view(1, -1, 1, 1) + ss[1].view(1, -1, 1, 1))
+    _close(got.permute(0, 3, 1, 2), F.interpolate(ref, scale_factor=2, mode="nearest"), "conv + bn + up2")
