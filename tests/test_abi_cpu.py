@@ -147,3 +147,29 @@ def test_reference_checkpoint_file_round_trip(tmp_path):
         assert "module." + k == k2 and torch.equal(v, v2), k
     torch.optim.Adam(ours.parameters(), lr=1e-4).load_state_dict(loaded["optimizer"])
     assert loaded["epoch"] == 7 and loaded["previous_best"] == 0.5
+
+
+def test_ctypes_signatures_have_the_declared_number_of_arguments():
+    """Every prototype in include/pdac_b200.h against the ctypes table: same number of parameters, pointer parameters
+    bound as pointers and integer / floating ones as scalars (a wrong count or kind corrupts the call silently)."""
+    import ctypes as C
+    from pdac_pathological_image_segmentation_b200 import _lib
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    protos = dict(re.findall(r"\bint\s+(pdac_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S))
+    checked = 0
+    for name, argtypes in _lib.SIGNATURES.items():
+        assert name in protos, f"{name} bound in _lib.py but not declared as `int {name}(...)` in the header"
+        params = [p.strip() for p in protos[name].replace("\n", " ").split(",") if p.strip() and p.strip() != "void"]
+        assert len(params) == len(argtypes), f"{name}: header has {len(params)} parameters, ctypes binds {len(argtypes)}"
+        for i, (decl, ct) in enumerate(zip(params, argtypes)):
+            is_ptr_decl = "*" in decl
+            is_ptr_ct = ct in (C.c_void_p, C.c_char_p) or hasattr(ct, "contents") or ct.__name__.startswith("LP_")
+            assert is_ptr_decl == is_ptr_ct, f"{name} argument {i} `{decl}` bound as {ct.__name__}"
+            if not is_ptr_decl:
+                want_float = decl.split()[0] in ("float", "double")
+                assert (ct in (C.c_float, C.c_double)) == want_float, f"{name} argument {i} `{decl}` bound as {ct.__name__}"
+                if want_float:
+                    assert (ct is C.c_double) == decl.startswith("double"), f"{name} argument {i} `{decl}` bound as {ct.__name__}"
+        checked += 1
+    assert checked >= 55
